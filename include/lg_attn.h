@@ -1,0 +1,78 @@
+/* lg_attn.h — C-ABI of the B200-native (sm_100a) LightGlue fused attention (head_dim 64).
+ *
+ * Drop-in boundary for the hot path of qdLMF/LightGlue-with-FlashAttentionV2-TensorRT.
+ * The reference exports no extern "C" symbol: its TensorRT plugin `enqueue`
+ * (lightglue_attention_plugin/lightglue_attention_plugin.cpp:114-270) calls C++-mangled
+ * launchers in namespace AttentionHeadDim64
+ * (attention_headdim_64_fp16in_fp16out.cuh:17-57, attention_headdim_64_fp16in_fp32out.cuh:17-75).
+ * The functions below are what a C / ctypes / cgo binding of that path binds instead; the
+ * plugin translation unit in this repo calls them from `enqueue`.
+ *
+ * Conventions
+ *   - all tensors are contiguous row-major [batch, heads, rows, 64] (TensorRT kLINEAR),
+ *     device pointers unless a function says "host";
+ *   - O = softmax(Q K^T / 8) V per (batch, head)  (lightglue_pytorch_no_plugin/lightglue.py:82-85);
+ *   - n_q (rows of Q and O) and n_kv (rows of K and V) are independent, any value >= 1;
+ *   - functions taking a stream only enqueue work: no allocation, no synchronisation,
+ *     legal inside CUDA stream capture;
+ *   - return value: 0 on success, otherwise a cudaError_t / LG_ATTN_E* code (never aborts).
+ */
+#ifndef LG_ATTN_H_
+#define LG_ATTN_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LG_ATTN_HEAD_DIM 64
+
+/* io_dtype: what the caller's buffers hold. Compute is always FP16 operands, FP32 accumulate. */
+enum lg_attn_io_dtype {
+    LG_ATTN_F16_F16 = 0, /* Q,K,V half  -> O half   : plugin kHALF branch  (…plugin.cpp:177-221; kernel …fp16out.cu:253-733) */
+    LG_ATTN_F32_F32 = 1, /* Q,K,V float -> O float  : plugin kFLOAT branch (…plugin.cpp:222-267; convert …fp32out.cu:706-804) */
+    LG_ATTN_F16_F32 = 2  /* Q,K,V half  -> O float  : launch_attention_kernel_…fp16in_fp32out (…fp32out.cu:962-989) */
+};
+
+/* error codes beyond cudaError_t (chosen above the cudaError_t range) */
+#define LG_ATTN_EINVAL      100001 /* bad argument (null pointer, non-positive size, unknown dtype) */
+#define LG_ATTN_EWORKSPACE  100002 /* workspace missing or smaller than lg_attn_hd64_workspace_bytes() */
+#define LG_ATTN_EDRIVER     100003 /* cuTensorMapEncodeTiled entry point unavailable / failed */
+#define LG_ATTN_EARCH       100004 /* device is not compute capability 10.x */
+
+/* ABI version of this header (bumped on any signature change). */
+int lg_attn_version(void);
+
+/* Per-device one-time setup (shared-memory opt-in, driver entry point lookup). Idempotent and
+ * thread-safe; lg_attn_hd64_launch() calls it lazily, but call it before stream capture.
+ * Replaces the static-initialiser cudaFuncSetAttribute of the reference (…fp16out.cu:242-250). */
+int lg_attn_hd64_init_device(int device);
+
+/* Scratch bytes the launcher needs for this problem: 0 for the half-input modes, the FP16 copy of
+ * Q,K,V for LG_ATTN_F32_F32.  Replaces the fixed 5 MiB of getWorkspaceSize (…plugin.cpp:96-112). */
+size_t lg_attn_hd64_workspace_bytes(int batch, int heads, int n_q, int n_kv, int io_dtype);
+
+/* The hot path: enqueue one fused attention on `stream` (a cudaStream_t passed as void*).
+ * Replaces the pad -> attention -> unpad launch sequence of enqueue (…plugin.cpp:177-267). */
+int lg_attn_hd64_launch(const void* q, const void* k, const void* v, void* o,
+                        int batch, int heads, int n_q, int n_kv, int io_dtype,
+                        void* workspace, size_t workspace_bytes, void* stream);
+
+/* Convenience for non-CUDA hosts (ctypes / cgo): HOST buffers in, HOST buffer out.
+ * Allocates device scratch, copies H2D, launches, copies D2H, synchronises.  Not for the
+ * TensorRT path; used by the end-to-end (`e2e`) measurement and by bindings without a CUDA runtime. */
+int lg_attn_hd64_run_host(const void* q_host, const void* k_host, const void* v_host, void* o_host,
+                          int batch, int heads, int n_q, int n_kv, int io_dtype, int device);
+
+/* Number of kernels lg_attn_hd64_launch() enqueues for a dtype (1, or 2 for LG_ATTN_F32_F32). */
+int lg_attn_hd64_launches_per_call(int io_dtype);
+
+/* Human-readable name of a return code (static storage). */
+const char* lg_attn_error_string(int code);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LG_ATTN_H_ */

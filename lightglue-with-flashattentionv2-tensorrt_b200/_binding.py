@@ -1,0 +1,98 @@
+"""ctypes binding of the C-ABI declared in ``include/lg_attn.h``.
+
+The shared library is built in-tree by ``__graft_entry__.build()`` (or ``csrc/build.py``) as
+``csrc/build/liblightglue_attention_plugin.so`` — the same file name the reference's CMake produces
+(``/root/reference/lightglue_attention_plugin/CMakeLists.txt:76``) — so ``trtexec --plugins=`` /
+``dlopen`` call sites keep working (``/root/reference/demo/lightglue_trt.cpp:15``).
+
+There is no CPU fallback: if the library is missing, loading raises.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from pathlib import Path
+
+_CSRC = Path(__file__).resolve().parent / "csrc"
+LIB_NAME = "liblightglue_attention_plugin.so"
+LIB_PATH = _CSRC / "build" / LIB_NAME
+
+# io_dtype values of include/lg_attn.h
+F16_F16 = 0
+F32_F32 = 1
+F16_F32 = 2
+
+EINVAL = 100001
+EWORKSPACE = 100002
+EDRIVER = 100003
+EARCH = 100004
+
+# every symbol include/lg_attn.h declares (tests check the .so exports exactly these)
+C_ABI_SYMBOLS = (
+    "lg_attn_version",
+    "lg_attn_hd64_init_device",
+    "lg_attn_hd64_workspace_bytes",
+    "lg_attn_hd64_launch",
+    "lg_attn_hd64_run_host",
+    "lg_attn_hd64_launches_per_call",
+    "lg_attn_error_string",
+)
+
+_lib = None
+
+
+class LgAttnError(RuntimeError):
+    def __init__(self, code: int, what: str):
+        super().__init__(f"{what} failed: code {code} ({error_string(code)})")
+        self.code = code
+
+
+def lib_path() -> Path:
+    override = os.environ.get("LG_ATTN_LIB")
+    return Path(override) if override else LIB_PATH
+
+
+def load() -> ctypes.CDLL:
+    """Load the C-ABI library (once). Raises if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = lib_path()
+    if not path.exists():
+        raise FileNotFoundError(
+            f"{path} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(there is no CPU fallback for the attention path)"
+        )
+    lib = ctypes.CDLL(str(path), mode=ctypes.RTLD_GLOBAL)
+    lib.lg_attn_version.restype = ctypes.c_int
+    lib.lg_attn_version.argtypes = []
+    lib.lg_attn_hd64_init_device.restype = ctypes.c_int
+    lib.lg_attn_hd64_init_device.argtypes = [ctypes.c_int]
+    lib.lg_attn_hd64_workspace_bytes.restype = ctypes.c_size_t
+    lib.lg_attn_hd64_workspace_bytes.argtypes = [ctypes.c_int] * 5
+    lib.lg_attn_hd64_launch.restype = ctypes.c_int
+    lib.lg_attn_hd64_launch.argtypes = [
+        ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+        ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+        ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p,
+    ]
+    lib.lg_attn_hd64_run_host.restype = ctypes.c_int
+    lib.lg_attn_hd64_run_host.argtypes = [
+        ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+        ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+    ]
+    lib.lg_attn_hd64_launches_per_call.restype = ctypes.c_int
+    lib.lg_attn_hd64_launches_per_call.argtypes = [ctypes.c_int]
+    lib.lg_attn_error_string.restype = ctypes.c_char_p
+    lib.lg_attn_error_string.argtypes = [ctypes.c_int]
+    _lib = lib
+    return lib
+
+
+def error_string(code: int) -> str:
+    return load().lg_attn_error_string(int(code)).decode()
+
+
+def check(code: int, what: str) -> None:
+    if code != 0:
+        raise LgAttnError(code, what)

@@ -1,0 +1,233 @@
+// C-ABI of the sm_100a attention path (declared in include/lg_attn.h).
+//
+// Host-side glue only: argument checks, per-device one-time setup, TMA tensor-map encoding
+// (cuTensorMapEncodeTiled through cudaGetDriverEntryPoint — a pure host call, legal while a
+// stream is being captured) and the kernel launch.  Mirrors what the reference's
+// LightGlueAttentionPlugin::enqueue does around its launchers
+// (/root/reference/lightglue_attention_plugin/lightglue_attention_plugin.cpp:165-267), minus the
+// pad / unpad passes that the new kernel makes unnecessary.
+
+#include "attn_sm100_kernel.cuh"
+
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <mutex>
+
+#include "../../include/lg_attn.h"
+
+namespace {
+
+using namespace lgattn;
+
+constexpr int kMaxDevices = 64;
+constexpr int kAbiVersion = 1;
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+
+std::mutex g_init_mutex;
+std::atomic<int> g_device_ready[kMaxDevices];  // 0 = not initialised, 1 = ready
+std::atomic<EncodeTiledFn> g_encode{nullptr};
+
+int resolve_encode() {
+    if (g_encode.load(std::memory_order_acquire) != nullptr) return 0;
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+    if (e != cudaSuccess || fn == nullptr || qres != cudaDriverEntryPointSuccess) {
+        (void)cudaGetLastError();
+        return LG_ATTN_EDRIVER;
+    }
+    g_encode.store(reinterpret_cast<EncodeTiledFn>(fn), std::memory_order_release);
+    return 0;
+}
+
+// 3-D map over a contiguous [bh, rows, 64] half tensor: dims (64, rows, bh), box (64, 128, 1),
+// 128-byte swizzle.  Rows past `rows` inside a (batch, head) slice are zero-filled by the TMA unit,
+// which is what makes ragged N / M work without the reference's padded workspace copy.
+int encode_rows_map(CUtensorMap* map, const void* base, int rows, int bh) {
+    const cuuint64_t dims[3] = {static_cast<cuuint64_t>(kHeadDim), static_cast<cuuint64_t>(rows),
+                                static_cast<cuuint64_t>(bh)};
+    const cuuint64_t strides[2] = {static_cast<cuuint64_t>(kHeadDim) * 2,
+                                   static_cast<cuuint64_t>(rows) * kHeadDim * 2};
+    const cuuint32_t box[3] = {static_cast<cuuint32_t>(kHeadDim), static_cast<cuuint32_t>(kBlockN), 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = g_encode.load(std::memory_order_acquire)(
+        map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? 0 : LG_ATTN_EDRIVER;
+}
+
+int init_device_locked(int device) {
+    cudaDeviceProp prop;
+    cudaError_t e = cudaGetDeviceProperties(&prop, device);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    if (prop.major != 10) return LG_ATTN_EARCH;
+    int rc = resolve_encode();
+    if (rc != 0) return rc;
+    int prev = -1;
+    e = cudaGetDevice(&prev);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    if (prev != device) {
+        e = cudaSetDevice(device);
+        if (e != cudaSuccess) return static_cast<int>(e);
+    }
+    // opt in to > 48 KiB dynamic shared memory (per device; the attribute is per context)
+    e = cudaFuncSetAttribute(lg_attn_hd64_fwd<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             static_cast<int>(kSmemBytes));
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(lg_attn_hd64_fwd<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 static_cast<int>(kSmemBytes));
+    if (prev != device && prev >= 0) (void)cudaSetDevice(prev);
+    return static_cast<int>(e);
+}
+
+size_t align256(size_t x) { return (x + 255) & ~static_cast<size_t>(255); }
+
+bool valid_dtype(int d) { return d == LG_ATTN_F16_F16 || d == LG_ATTN_F32_F32 || d == LG_ATTN_F16_F32; }
+
+}  // namespace
+
+extern "C" {
+
+int lg_attn_version(void) { return kAbiVersion; }
+
+int lg_attn_hd64_init_device(int device) {
+    if (device < 0 || device >= kMaxDevices) return LG_ATTN_EINVAL;
+    if (g_device_ready[device].load(std::memory_order_acquire) == 1) return 0;
+    std::lock_guard<std::mutex> lock(g_init_mutex);
+    if (g_device_ready[device].load(std::memory_order_acquire) == 1) return 0;
+    int rc = init_device_locked(device);
+    if (rc == 0) g_device_ready[device].store(1, std::memory_order_release);
+    return rc;
+}
+
+size_t lg_attn_hd64_workspace_bytes(int batch, int heads, int n_q, int n_kv, int io_dtype) {
+    if (batch <= 0 || heads <= 0 || n_q <= 0 || n_kv <= 0 || !valid_dtype(io_dtype)) return 0;
+    if (io_dtype != LG_ATTN_F32_F32) return 0;
+    const size_t bh = static_cast<size_t>(batch) * heads;
+    return align256(bh * n_q * kHeadDim * 2) + 2 * align256(bh * n_kv * kHeadDim * 2);
+}
+
+int lg_attn_hd64_launches_per_call(int io_dtype) {
+    if (!valid_dtype(io_dtype)) return 0;
+    return io_dtype == LG_ATTN_F32_F32 ? 2 : 1;
+}
+
+int lg_attn_hd64_launch(const void* q, const void* k, const void* v, void* o, int batch, int heads,
+                        int n_q, int n_kv, int io_dtype, void* workspace, size_t workspace_bytes,
+                        void* stream_v) {
+    if (q == nullptr || k == nullptr || v == nullptr || o == nullptr) return LG_ATTN_EINVAL;
+    if (batch <= 0 || heads <= 0 || n_q <= 0 || n_kv <= 0 || !valid_dtype(io_dtype)) return LG_ATTN_EINVAL;
+    const long long bh_ll = static_cast<long long>(batch) * heads;
+    const long long tiles_m_ll = (static_cast<long long>(n_q) + kBlockM - 1) / kBlockM;
+    if (bh_ll * tiles_m_ll > 2147483647LL) return LG_ATTN_EINVAL;
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+
+    int device = 0;
+    cudaError_t e = cudaGetDevice(&device);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    int rc = lg_attn_hd64_init_device(device);
+    if (rc != 0) return rc;
+
+    const int bh = static_cast<int>(bh_ll);
+    const int tiles_m = static_cast<int>(tiles_m_ll);
+    const void* qh = q;
+    const void* kh = k;
+    const void* vh = v;
+
+    if (io_dtype == LG_ATTN_F32_F32) {
+        const size_t need = lg_attn_hd64_workspace_bytes(batch, heads, n_q, n_kv, io_dtype);
+        if (workspace == nullptr || workspace_bytes < need) return LG_ATTN_EWORKSPACE;
+        const size_t q_bytes = align256(static_cast<size_t>(bh) * n_q * kHeadDim * 2);
+        const size_t kv_bytes = align256(static_cast<size_t>(bh) * n_kv * kHeadDim * 2);
+        uint8_t* ws = static_cast<uint8_t*>(workspace);
+        uint4* qd = reinterpret_cast<uint4*>(ws);
+        uint4* kd = reinterpret_cast<uint4*>(ws + q_bytes);
+        uint4* vd = reinterpret_cast<uint4*>(ws + q_bytes + kv_bytes);
+        const size_t nq8 = static_cast<size_t>(bh) * n_q * (kHeadDim / 8);
+        const size_t nkv8 = static_cast<size_t>(bh) * n_kv * (kHeadDim / 8);
+        const size_t total = nq8 + 2 * nkv8;
+        size_t blocks = (total + 255) / 256;
+        if (blocks > 148 * 16) blocks = 148 * 16;  // grid-stride; 16 resident-CTA waves over 148 SMs
+        lg_attn_cvt_f32_f16<<<static_cast<unsigned>(blocks), 256, 0, stream>>>(
+            static_cast<const float4*>(q), static_cast<const float4*>(k), static_cast<const float4*>(v), qd,
+            kd, vd, nq8, nkv8);
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return static_cast<int>(e);
+        qh = qd;
+        kh = kd;
+        vh = vd;
+    }
+
+    CUtensorMap tm_q, tm_k, tm_v;
+    if ((rc = encode_rows_map(&tm_q, qh, n_q, bh)) != 0) return rc;
+    if ((rc = encode_rows_map(&tm_k, kh, n_kv, bh)) != 0) return rc;
+    if ((rc = encode_rows_map(&tm_v, vh, n_kv, bh)) != 0) return rc;
+
+    const unsigned grid = static_cast<unsigned>(bh) * static_cast<unsigned>(tiles_m);
+    if (io_dtype == LG_ATTN_F16_F16) {
+        lg_attn_hd64_fwd<false><<<grid, kThreads, kSmemBytes, stream>>>(tm_q, tm_k, tm_v, o, n_q, n_kv, tiles_m);
+    } else {
+        lg_attn_hd64_fwd<true><<<grid, kThreads, kSmemBytes, stream>>>(tm_q, tm_k, tm_v, o, n_q, n_kv, tiles_m);
+    }
+    return static_cast<int>(cudaGetLastError());
+}
+
+int lg_attn_hd64_run_host(const void* q_host, const void* k_host, const void* v_host, void* o_host,
+                          int batch, int heads, int n_q, int n_kv, int io_dtype, int device) {
+    if (q_host == nullptr || k_host == nullptr || v_host == nullptr || o_host == nullptr) return LG_ATTN_EINVAL;
+    if (batch <= 0 || heads <= 0 || n_q <= 0 || n_kv <= 0 || !valid_dtype(io_dtype)) return LG_ATTN_EINVAL;
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    const size_t in_es = (io_dtype == LG_ATTN_F32_F32) ? 4 : 2;
+    const size_t out_es = (io_dtype == LG_ATTN_F16_F16) ? 2 : 4;
+    const size_t bh = static_cast<size_t>(batch) * heads;
+    const size_t q_bytes = bh * n_q * kHeadDim * in_es;
+    const size_t kv_bytes = bh * n_kv * kHeadDim * in_es;
+    const size_t o_bytes = bh * n_q * kHeadDim * out_es;
+    const size_t ws_bytes = lg_attn_hd64_workspace_bytes(batch, heads, n_q, n_kv, io_dtype);
+    uint8_t* dev = nullptr;
+    const size_t total = align256(q_bytes) + 2 * align256(kv_bytes) + align256(o_bytes) + ws_bytes;
+    e = cudaMalloc(&dev, total);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    uint8_t* dq = dev;
+    uint8_t* dk = dq + align256(q_bytes);
+    uint8_t* dv = dk + align256(kv_bytes);
+    uint8_t* dout = dv + align256(kv_bytes);
+    uint8_t* dws = dout + align256(o_bytes);
+    cudaStream_t stream = nullptr;
+    int rc = 0;
+    e = cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dq, q_host, q_bytes, cudaMemcpyHostToDevice, stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dk, k_host, kv_bytes, cudaMemcpyHostToDevice, stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dv, v_host, kv_bytes, cudaMemcpyHostToDevice, stream);
+    if (e == cudaSuccess) {
+        rc = lg_attn_hd64_launch(dq, dk, dv, dout, batch, heads, n_q, n_kv, io_dtype, ws_bytes ? dws : nullptr,
+                                 ws_bytes, stream);
+    }
+    if (e == cudaSuccess && rc == 0) e = cudaMemcpyAsync(o_host, dout, o_bytes, cudaMemcpyDeviceToHost, stream);
+    if (e == cudaSuccess && rc == 0) e = cudaStreamSynchronize(stream);
+    if (stream != nullptr) (void)cudaStreamDestroy(stream);
+    (void)cudaFree(dev);
+    if (rc != 0) return rc;
+    return static_cast<int>(e);
+}
+
+const char* lg_attn_error_string(int code) {
+    switch (code) {
+        case 0: return "success";
+        case LG_ATTN_EINVAL: return "lg_attn: invalid argument";
+        case LG_ATTN_EWORKSPACE: return "lg_attn: workspace missing or too small";
+        case LG_ATTN_EDRIVER: return "lg_attn: cuTensorMapEncodeTiled unavailable or failed";
+        case LG_ATTN_EARCH: return "lg_attn: device is not compute capability 10.x (sm_100a required)";
+        default: return cudaGetErrorString(static_cast<cudaError_t>(code));
+    }
+}
+
+}  // extern "C"

@@ -1,0 +1,90 @@
+"""Torch-tensor front end of the C-ABI launcher (device pointers + current stream only).
+
+PyTorch is plumbing here: it owns device memory and the stream; the arithmetic happens in the
+hand-written sm_100a kernel behind ``lg_attn_hd64_launch``.  There is no eager fallback — a CPU
+tensor, a missing library or a non-sm_100 device raises.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _binding as B
+
+HEAD_DIM = 64
+
+
+def _mode(q: torch.Tensor, out_dtype: torch.dtype) -> int:
+    if q.dtype == torch.float16 and out_dtype == torch.float16:
+        return B.F16_F16
+    if q.dtype == torch.float16 and out_dtype == torch.float32:
+        return B.F16_F32
+    if q.dtype == torch.float32 and out_dtype == torch.float32:
+        return B.F32_F32
+    raise TypeError(f"unsupported dtype combination: in {q.dtype}, out {out_dtype} "
+                    "(supported: f16->f16, f16->f32, f32->f32)")
+
+
+def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, out_dtype: torch.dtype | None = None,
+              out: torch.Tensor | None = None, workspace: torch.Tensor | None = None) -> torch.Tensor:
+    """``softmax(q @ k^T / 8) @ v`` for ``q [B,H,N,64]``, ``k, v [B,H,M,64]`` on a B200.
+
+    Semantics of the reference plugin call (``lightglue_attention_plugin.cpp:114-270``): all three
+    inputs share a dtype (half or float), the output has ``q``'s shape; ``out_dtype`` additionally
+    exposes the reference's internal half-in / float-out kernel (``…fp32out.cu:962-989``).
+    """
+    if not (q.is_cuda and k.is_cuda and v.is_cuda):
+        raise RuntimeError("lg_attn: tensors must live on a CUDA device (no CPU fallback)")
+    if q.dim() != 4 or k.dim() != 4 or v.dim() != 4:
+        raise ValueError("lg_attn: q, k, v must be rank 4 [B,H,rows,64]")
+    if q.shape[-1] != HEAD_DIM or k.shape[-1] != HEAD_DIM or v.shape[-1] != HEAD_DIM:
+        raise ValueError("lg_attn: head_dim must be 64")
+    if k.shape != v.shape or q.shape[:2] != k.shape[:2]:
+        raise ValueError(f"lg_attn: shape mismatch q {tuple(q.shape)} k {tuple(k.shape)} v {tuple(v.shape)}")
+    if not (q.dtype == k.dtype == v.dtype):
+        raise TypeError("lg_attn: q, k, v must share a dtype")
+    out_dtype = out_dtype or q.dtype
+    mode = _mode(q, out_dtype)
+    q, k, v = q.contiguous(), k.contiguous(), v.contiguous()
+    b, h, n, _ = q.shape
+    m = k.shape[2]
+    if out is None:
+        out = torch.empty((b, h, n, HEAD_DIM), dtype=out_dtype, device=q.device)
+    elif out.dtype != out_dtype or tuple(out.shape) != (b, h, n, HEAD_DIM) or not out.is_contiguous():
+        raise ValueError("lg_attn: `out` has the wrong dtype/shape or is not contiguous")
+    lib = B.load()
+    ws_bytes = lib.lg_attn_hd64_workspace_bytes(b, h, n, m, mode)
+    ws_ptr = None
+    if ws_bytes:
+        if workspace is None or workspace.numel() * workspace.element_size() < ws_bytes:
+            workspace = torch.empty(ws_bytes, dtype=torch.uint8, device=q.device)
+        ws_ptr = workspace.data_ptr()
+    with torch.cuda.device(q.device):
+        stream = torch.cuda.current_stream(q.device).cuda_stream
+        rc = lib.lg_attn_hd64_launch(q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(),
+                                     b, h, n, m, mode, ws_ptr, ws_bytes, stream)
+    B.check(rc, "lg_attn_hd64_launch")
+    return out
+
+
+def attention_host(q, k, v, out_dtype=None, device: int = 0):
+    """Host-buffer entry (numpy arrays in, numpy array out) through ``lg_attn_hd64_run_host``."""
+    import numpy as np
+
+    q = np.ascontiguousarray(q)
+    k = np.ascontiguousarray(k)
+    v = np.ascontiguousarray(v)
+    out_dtype = np.dtype(out_dtype or q.dtype)
+    key = (q.dtype.name, out_dtype.name)
+    modes = {("float16", "float16"): B.F16_F16, ("float16", "float32"): B.F16_F32,
+             ("float32", "float32"): B.F32_F32}
+    if key not in modes:
+        raise TypeError(f"unsupported dtype combination {key}")
+    b, h, n, d = q.shape
+    m = k.shape[2]
+    if d != HEAD_DIM or k.shape != v.shape or k.shape[:2] != (b, h) or k.shape[3] != HEAD_DIM:
+        raise ValueError("lg_attn: bad shapes")
+    o = np.empty((b, h, n, HEAD_DIM), dtype=out_dtype)
+    rc = B.load().lg_attn_hd64_run_host(q.ctypes.data, k.ctypes.data, v.ctypes.data, o.ctypes.data,
+                                        b, h, n, m, modes[key], device)
+    B.check(rc, "lg_attn_hd64_run_host")
+    return o
