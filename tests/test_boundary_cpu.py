@@ -1,0 +1,101 @@
+"""CPU: the C-ABI library loads, exports every symbol include/lg_attn.h declares, and the TensorRT
+plugin boundary (driven by the mock host) keeps the reference's contract.  No compute calls."""
+import ctypes
+import json
+import re
+import subprocess
+from pathlib import Path
+
+import pytest
+
+ROOT = Path(__file__).resolve().parent.parent
+
+
+@pytest.fixture(scope="module")
+def lib(pkg):
+    import __graft_entry__ as ge
+
+    ge.build()
+    return pkg.load()
+
+
+def test_header_symbols_are_exported(pkg, lib):
+    header = (ROOT / "include" / "lg_attn.h").read_text()
+    declared = set(re.findall(r"\b(lg_attn_[a-z0-9_]+)\s*\(", header))
+    assert declared == set(pkg.C_ABI_SYMBOLS)
+    out = subprocess.run(["nm", "-D", "--defined-only", str(pkg._binding.lib_path())], capture_output=True, text=True,
+                         check=True).stdout
+    exported = set(re.findall(r" T (\w+)", out))
+    for sym in declared:
+        assert sym in exported, sym
+        assert getattr(lib, sym) is not None
+    assert lib.lg_attn_version() == 1
+
+
+def test_library_is_sm100a_native(pkg):
+    """The shipped kernel is tcgen05/TMA code for sm_100a (SASS mnemonics, B200_PROFILING.md)."""
+    sass = subprocess.run(["cuobjdump", "-sass", str(pkg._binding.lib_path())], capture_output=True, text=True).stdout
+    if not sass:
+        pytest.skip("cuobjdump unavailable")
+    assert "sm_100a" in sass
+    for mnemonic in ("UTCHMMA", "UTMALDG", "LDTM", "STTM"):
+        assert mnemonic in sass, mnemonic
+    assert "HMMA." not in sass.replace("UTCHMMA", "")  # no legacy mma.sync path
+
+
+def test_workspace_and_launch_counts(pkg, lib):
+    assert lib.lg_attn_hd64_workspace_bytes(1, 4, 1024, 1024, pkg.F16_F16) == 0
+    assert lib.lg_attn_hd64_workspace_bytes(1, 4, 1024, 1024, pkg.F16_F32) == 0
+    assert lib.lg_attn_hd64_workspace_bytes(1, 4, 1024, 1000, pkg.F32_F32) == 4 * 64 * 2 * (1024 + 2 * 1000)
+    assert lib.lg_attn_hd64_workspace_bytes(1, 4, 0, 10, pkg.F32_F32) == 0
+    assert lib.lg_attn_hd64_workspace_bytes(1, 4, 10, 10, 7) == 0
+    assert lib.lg_attn_hd64_launches_per_call(pkg.F16_F16) == 1
+    assert lib.lg_attn_hd64_launches_per_call(pkg.F16_F32) == 1
+    assert lib.lg_attn_hd64_launches_per_call(pkg.F32_F32) == 2
+
+
+def test_argument_errors_do_not_abort(pkg, lib):
+    B = pkg._binding
+    one = ctypes.c_void_p(16)
+    assert lib.lg_attn_hd64_launch(None, one, one, one, 1, 4, 8, 8, 0, None, 0, None) == B.EINVAL
+    assert lib.lg_attn_hd64_launch(one, one, one, one, 1, 4, 0, 8, 0, None, 0, None) == B.EINVAL
+    assert lib.lg_attn_hd64_launch(one, one, one, one, 1, 4, 8, 8, 5, None, 0, None) == B.EINVAL
+    assert lib.lg_attn_hd64_run_host(None, one, one, one, 1, 4, 8, 8, 0, 0) == B.EINVAL
+    assert "workspace" in B.error_string(B.EWORKSPACE)
+    assert B.error_string(0) == "success"
+
+
+def test_plugin_contract_via_mock_host(lib):
+    """Registry lookup + the build-time virtuals, vs the reference plugin's answers
+    (lightglue_attention_plugin.cpp:19-20, :45-47, :77-94, :272-310, :363-367)."""
+    lib.lg_mock_trt_describe.argtypes = [ctypes.c_char_p, ctypes.c_size_t]
+    buf = ctypes.create_string_buffer(4096)
+    n = lib.lg_mock_trt_describe(buf, 4096)
+    assert n > 0
+    d = json.loads(buf.value.decode())
+    assert (d["name"], d["version"], d["namespace"]) == ("MHAHeadDim64", "1", "")
+    assert (d["type"], d["plugin_version"]) == ("MHAHeadDim64", "1")
+    assert d["n_creators"] == 1 and d["nb_fields"] == 0
+    assert d["nb_outputs"] == 1
+    assert d["serialization_size"] == 0 and d["serialize_untouched"]
+    # slot 0: (float|half) & linear; slots 1-3: same type as slot 0 (= half here) & linear
+    # order per slot: float/linear float/chw4 half/linear half/chw4 int8/linear int8/chw4
+    assert d["format_table"] == "101000" + "001000" * 3
+    assert d["format_follow_float"] == "10" * 3
+    assert d["out_nb_dims"] == 4 and d["out_dims"] == [1, 4, 777, 64]  # O takes Q's dims
+    assert d["out_type_half"] == 1 and d["out_type_float"] == 0        # DataType::kHALF / kFLOAT
+    assert d["ws_half"] == 0
+    assert d["ws_float"] == 3 * 4 * 2048 * 64 * 2
+    assert d["clone_namespace"] == "ns_probe"
+
+
+def test_python_operator_mirror(pkg):
+    """Same op names as lightglue_pytorch_with_plugin/lightglue.py:16-46,102-115; no CPU fallback."""
+    import torch
+
+    assert pkg.ONNX_OP == "CustomOp::MHAHeadDim64"
+    assert issubclass(pkg.MHAHeadDim64, torch.autograd.Function)
+    assert hasattr(pkg.MHAHeadDim64, "symbolic")
+    q = torch.zeros(1, 4, 8, 64)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        pkg.Attention()(q, q, q)
