@@ -1,0 +1,339 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the MHAHeadDim64 hot path on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Workload (BASELINE.json configs[1]): the standalone attention plugin op, B=1, H=4, N=M=1024, d=64,
+FP16 in / FP16 out.  One STEP = one batch of `CALLS` independent attention problems (synthetic,
+seeded), each issued through the reference-facing entry point `lg_attn_hd64_launch` — exactly what the
+TensorRT plugin's enqueue calls — captured once into a CUDA graph (the reference's deployment mode,
+demo/lightglue_trt.cpp:347-366) as one dependent chain on one stream.  Every problem has its own
+Q/K/V/O buffers; the batch footprint (CALLS x 2 MiB = 256 MiB) exceeds the 126 MB L2, so each
+problem's operands come from HBM ("inputs larger than L2" rule).
+
+Metric: attention TFLOP/s (FLOPs = 4*B*H*N*M*d per problem).  `value` = device-resident throughput,
+`e2e` = same metric through the host-buffer C-ABI session (pinned host buffers, H2D + D2H inside the
+timed region).  N>1: problems are sharded across ranks (independent pairs, no collective in the data
+path; NCCL only for the barrier and the max-over-ranks reduction of the time) -> weak scaling.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+if str(ROOT) not in sys.path:
+    sys.path.insert(0, str(ROOT))
+
+B, H, N, M, D = 1, 4, 1024, 1024, 64
+CALLS = 128                       # problems per step and per rank
+FLOPS_PER_CALL = 4.0 * B * H * N * M * D
+BYTES_PER_CALL = 2 * B * H * D * (N + 2 * M) + 2 * B * H * N * D
+METRIC = "attn TFLOP/s (H4 d64 N1024)"
+UNIT = "TFLOP/s"
+WORKLOAD = "attn_plugin_op_B1_H4_N1024_M1024_d64_f16in_f16out"
+
+
+def load_peaks() -> dict:
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        d = json.loads(p.read_text())
+        return {"bf16_tflops": float(d["bf16_tflops"]), "bf16_tflops_sustained": float(d.get("bf16_tflops_sustained", 0)),
+                "hbm_gbs": float(d["hbm_gbs"]), "source": "measured (MEASURED_PEAKS.json)"}
+    return {"bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "hbm_gbs": 6650.0,
+            "source": "fallback (B200_PROFILING.md)"}
+
+
+class ClockSampler:
+    """nvidia-smi clock / throttle-reason samples during the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.samples, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            parts = [x.strip() for x in line.split(",")]
+            if len(parts) >= 7:
+                self.samples.append(parts)
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm = sorted(float(s[0]) for s in self.samples if s[0].replace(".", "").isdigit())
+        mx = [float(s[1]) for s in self.samples if s[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for s in self.samples for i in range(4) if s[3 + i].lower().startswith("active")})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(self.samples)}
+
+
+def cpu_baseline_sample(reps: int) -> dict:
+    """The reference's CPU path (lightglue_pytorch_no_plugin Attention.forward, lightglue.py:82-85) restated by
+    the oracle's torch-CPU port, timed on this host with all cores on a bounded sample of the workload."""
+    import torch
+    from oracle import attention_oracle as orc
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    g = torch.Generator().manual_seed(20260411)
+    q = torch.randn(B, H, N, D, generator=g).half().float()
+    k = torch.randn(B, H, M, D, generator=g).half().float()
+    v = torch.randn(B, H, M, D, generator=g).half().float()
+    orc.attention_torch_cpu(q, k, v)
+    orc.attention_torch_cpu(q, k, v)
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        orc.attention_torch_cpu(q, k, v)
+    dt = (time.perf_counter() - t0) / reps
+    return {"value": FLOPS_PER_CALL / dt / 1e12, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"{reps} problems of the workload shape (B1 H4 N=M=1024 d64), FP32 torch CPU, {dt*1e3:.2f} ms each"}
+
+
+def run_reference(args) -> None:
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    steps, warmup = args.steps, args.warmup
+    per_step = 8     # bounded sample: 8 problems per step
+    for _ in range(max(1, warmup)):
+        cpu_baseline_sample(per_step)
+    t0 = time.perf_counter()
+    vals = [cpu_baseline_sample(per_step) for _ in range(steps)]
+    wall = time.perf_counter() - t0
+    tf = sum(v["value"] for v in vals) / len(vals)
+    cb = dict(vals[-1])
+    cb["value"] = tf
+    cb["sample"] = f"{per_step} problems/step of the workload shape, FP32 torch CPU (oracle port of lightglue.py:82-85)"
+    line = {"impl": "reference", "metric": METRIC, "value": tf, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+            "warmup": warmup, "ms_per_step": wall / steps * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "problems_per_step": per_step, "note": "CPU reference arm, rank 0 only"},
+            "cpu_baseline": cb,
+            "e2e": {"value": tf, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args) -> None:
+    import torch
+    import torch.distributed as dist
+
+    from lgattn_pkg import pkg
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the product path has no CPU fallback)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    lib = pkg.load()
+    pkg._binding.check(lib.lg_attn_hd64_init_device(local), "init_device")
+    peaks = load_peaks()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- synthetic inputs, resident in HBM: CALLS independent problems (seed differs per rank)
+    g = torch.Generator(device=dev).manual_seed(20260411 + rank)
+    q = torch.randn(CALLS, B, H, N, D, device=dev, generator=g).half()
+    k = torch.randn(CALLS, B, H, M, D, device=dev, generator=g).half()
+    v = torch.randn(CALLS, B, H, M, D, device=dev, generator=g).half()
+    o = torch.empty(CALLS, B, H, N, D, device=dev, dtype=torch.float16)
+
+    def launch_all(stream_ptr):
+        for i in range(CALLS):
+            rc = lib.lg_attn_hd64_launch(q[i].data_ptr(), k[i].data_ptr(), v[i].data_ptr(), o[i].data_ptr(), B, H, N, M,
+                                         pkg.F16_F16, None, 0, stream_ptr)
+            if rc != 0:
+                raise RuntimeError(pkg._binding.error_string(rc))
+
+    stream = torch.cuda.Stream(device=dev)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(stream):
+        launch_all(stream.cuda_stream)          # eager warm-up (module load) before capture
+        stream.synchronize()
+        with torch.cuda.graph(graph, stream=stream):
+            launch_all(torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+
+    # ---- correctness spot check against the oracle (rank 0, one problem) — outside the timed region
+    if rank == 0:
+        from oracle import attention_oracle as orc
+        graph.replay()
+        torch.cuda.synchronize()
+        i = CALLS - 1
+        ref = orc.attention_np(q[i].cpu().numpy(), k[i].cpu().numpy(), v[i].cpu().numpy())
+        err = orc.max_abs_err(o[i].float().cpu().numpy(), ref)
+        if err > orc.TOL_F16_MAX_ABS:
+            raise SystemExit(f"bench.py: parity check failed before timing (max_abs {err})")
+
+    # ---- device-resident timing
+    for _ in range(args.warmup):
+        graph.replay()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        graph.replay()
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop() if rank == 0 else None
+    t = torch.tensor([ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    launches = CALLS * args.steps
+    value = world * launches * FLOPS_PER_CALL / (ms * 1e-3) / 1e12
+    launch_us = ms * 1e3 / launches
+    achieved = FLOPS_PER_CALL / (launch_us * 1e-6) / 1e12
+
+    # ---- end-to-end: host buffers through the C-ABI session (H2D + launch + D2H per problem)
+    e2e_steps = max(1, min(args.steps, 10))
+    qh = torch.empty(CALLS, B, H, N, D, dtype=torch.float16).pin_memory()
+    kh = torch.empty(CALLS, B, H, M, D, dtype=torch.float16).pin_memory()
+    vh = torch.empty(CALLS, B, H, M, D, dtype=torch.float16).pin_memory()
+    oh = torch.empty(CALLS, B, H, N, D, dtype=torch.float16).pin_memory()
+    qh.copy_(q)
+    kh.copy_(k)
+    vh.copy_(v)
+    sess = pkg.HostSession(B, H, N, M, pkg.F16_F16, n_slots=4, device=local)
+    qs, ks, vs, os_ = q[0].numel() * 2, k[0].numel() * 2, v[0].numel() * 2, o[0].numel() * 2
+
+    def e2e_step():
+        for i in range(CALLS):
+            sess.submit(qh.data_ptr() + i * qs, kh.data_ptr() + i * ks, vh.data_ptr() + i * vs, oh.data_ptr() + i * os_, B, N, M)
+        sess.sync()
+
+    for _ in range(3):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    e2e_s = time.perf_counter() - t0
+    barrier()
+    te = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_value = world * CALLS * e2e_steps * FLOPS_PER_CALL / float(te.item()) / 1e12
+    if rank == 0 and not torch.equal(oh[CALLS - 1].to(dev), o[CALLS - 1]):
+        raise SystemExit("bench.py: e2e output differs from the device-resident output")
+    sess.close()
+
+    # ---- supporting numbers (not the headline): batched shapes against the tensor roofline
+    extra = {}
+    if rank == 0 and not args.no_extra:
+        extra = extra_shapes(pkg, torch, dev, peaks)
+
+    cpu = None
+    if rank == 0 and world == 1:
+        probe = cpu_baseline_sample(3)
+        per = FLOPS_PER_CALL / (probe["value"] * 1e12)
+        cpu = cpu_baseline_sample(max(10, min(4000, int(12.0 / per))))
+
+    if rank == 0:
+        peak = peaks["bf16_tflops"]
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f16 operands, f32 accumulate", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "problems_per_step_per_gpu": CALLS, "issue": "lg_attn_hd64_launch per problem, one CUDA-graph chain",
+                       "l2": f"inputs larger than L2 ({CALLS * BYTES_PER_CALL / 2**20:.0f} MiB per step per GPU)",
+                       "sharding": "independent problems per rank, no data-path collective"},
+            "gpu_launches": launches,
+            "us_per_launch": launch_us,
+            "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+                         "traffic": args.traffic, "peak_source": peaks["source"] + ", burst bf16 GEMM",
+                         "kernel": "lg_attn_hd64_fwd<false>", "flops_per_launch": FLOPS_PER_CALL,
+                         "hbm_floor_us": BYTES_PER_CALL / (peaks["hbm_gbs"] * 1e9) * 1e6,
+                         "note": "latency-bound shape: 32 CTAs on 148 SMs; duration = timed region / launches (includes launch gaps)"},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": CALLS * (qs + ks + vs), "d2h_bytes_per_step": CALLS * os_,
+                    "steps": e2e_steps, "timing": "host wall clock around submit+sync, pinned host buffers, 4 streams"},
+            "clocks": clocks,
+            "extra": extra,
+        }
+        if cpu is not None:
+            line["cpu_baseline"] = cpu
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def extra_shapes(pkg, torch, dev, peaks) -> dict:
+    """Batched shapes (BASELINE configs[4] attention shapes) — TFLOP/s against the measured tensor peak."""
+    out = {}
+    for (b, n, out_dt, tag) in [(64, 2048, torch.float16, "B64_N2048_f16out"), (64, 2048, torch.float32, "B64_N2048_f32out"),
+                                (16, 4096, torch.float16, "B16_N4096_f16out")]:
+        q = torch.randn(b, H, n, D, device=dev).half()
+        k = torch.randn(b, H, n, D, device=dev).half()
+        v = torch.randn(b, H, n, D, device=dev).half()
+        o = torch.empty(b, H, n, D, device=dev, dtype=out_dt)
+        for _ in range(3):
+            pkg.attention(q, k, v, out_dtype=out_dt, out=o)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        iters = 20
+        e0.record()
+        for _ in range(iters):
+            pkg.attention(q, k, v, out_dtype=out_dt, out=o)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / iters
+        tf = 4.0 * b * H * n * n * D / (ms * 1e-3) / 1e12
+        out[tag] = {"ms": ms, "tflops": tf, "frac_of_measured_burst": tf / peaks["bf16_tflops"],
+                    "frac_of_measured_sustained": tf / peaks["bf16_tflops_sustained"] if peaks["bf16_tflops_sustained"] else None,
+                    "frac_of_nominal_2250": tf / 2250.0}
+        del q, k, v, o
+    return out
+
+
+def main() -> None:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-extra", action="store_true")
+    ap.add_argument("--traffic", type=float, default=None, help="dram bytes per launch from an ncu capture (profiles/)")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    if args.impl == "reference":
+        run_reference(args)
+        return
+    if args.gpus > 1 and "WORLD_SIZE" not in os.environ:
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}", "--master-addr",
+               "127.0.0.1", "--master-port", "29533", __file__] + sys.argv[1:]
+        raise SystemExit(subprocess.call(cmd))
+    run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

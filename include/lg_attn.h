@@ -66,6 +66,20 @@ int lg_attn_hd64_launch(const void* q, const void* k, const void* v, void* o,
 int lg_attn_hd64_run_host(const void* q_host, const void* k_host, const void* v_host, void* o_host,
                           int batch, int heads, int n_q, int n_kv, int io_dtype, int device);
 
+/* Host-buffer session: persistent device buffers + streams for callers that hold HOST tensors
+ * (bindings without a CUDA runtime, the bench's end-to-end leg).  `n_slots` independent
+ * (device buffers, stream) sets are used round-robin, so copies of one call overlap the kernel of
+ * another when the host buffers are pinned.  submit() is asynchronous: it enqueues
+ * H2D(q,k,v) -> launch -> D2H(o) on the slot's stream and returns; o_host is valid after sync().
+ * Shapes up to the create-time maxima; any n_q, n_kv >= 1 below them. */
+typedef struct lg_attn_session lg_attn_session;
+int lg_attn_session_create(lg_attn_session** out, int device, int max_batch, int heads, int max_n_q, int max_n_kv,
+                           int io_dtype, int n_slots);
+int lg_attn_session_submit(lg_attn_session* s, const void* q_host, const void* k_host, const void* v_host,
+                           void* o_host, int batch, int n_q, int n_kv);
+int lg_attn_session_sync(lg_attn_session* s);
+void lg_attn_session_destroy(lg_attn_session* s);
+
 /* Number of kernels lg_attn_hd64_launch() enqueues for a dtype (1, or 2 for LG_ATTN_F32_F32). */
 int lg_attn_hd64_launches_per_call(int io_dtype);
 

@@ -36,6 +36,10 @@ C_ABI_SYMBOLS = (
     "lg_attn_hd64_run_host",
     "lg_attn_hd64_launches_per_call",
     "lg_attn_error_string",
+    "lg_attn_session_create",
+    "lg_attn_session_submit",
+    "lg_attn_session_sync",
+    "lg_attn_session_destroy",
 )
 
 _lib = None
@@ -85,6 +89,14 @@ def load() -> ctypes.CDLL:
     lib.lg_attn_hd64_launches_per_call.argtypes = [ctypes.c_int]
     lib.lg_attn_error_string.restype = ctypes.c_char_p
     lib.lg_attn_error_string.argtypes = [ctypes.c_int]
+    lib.lg_attn_session_create.restype = ctypes.c_int
+    lib.lg_attn_session_create.argtypes = [ctypes.POINTER(ctypes.c_void_p)] + [ctypes.c_int] * 7
+    lib.lg_attn_session_submit.restype = ctypes.c_int
+    lib.lg_attn_session_submit.argtypes = [ctypes.c_void_p] * 5 + [ctypes.c_int] * 3
+    lib.lg_attn_session_sync.restype = ctypes.c_int
+    lib.lg_attn_session_sync.argtypes = [ctypes.c_void_p]
+    lib.lg_attn_session_destroy.restype = None
+    lib.lg_attn_session_destroy.argtypes = [ctypes.c_void_p]
     _lib = lib
     return lib
 

@@ -219,6 +219,97 @@ int lg_attn_hd64_run_host(const void* q_host, const void* k_host, const void* v_
     return static_cast<int>(e);
 }
 
+struct lg_attn_session {
+    int device = 0, max_batch = 0, heads = 0, max_n_q = 0, max_n_kv = 0, io_dtype = 0, n_slots = 0;
+    size_t q_bytes = 0, kv_bytes = 0, o_bytes = 0, ws_bytes = 0;
+    uint8_t* pool = nullptr;
+    cudaStream_t* streams = nullptr;
+    unsigned long long next = 0;
+};
+
+int lg_attn_session_create(lg_attn_session** out, int device, int max_batch, int heads, int max_n_q, int max_n_kv,
+                           int io_dtype, int n_slots) {
+    if (out == nullptr || max_batch <= 0 || heads <= 0 || max_n_q <= 0 || max_n_kv <= 0 || n_slots <= 0 ||
+        n_slots > 64 || !valid_dtype(io_dtype))
+        return LG_ATTN_EINVAL;
+    *out = nullptr;
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    int rc = lg_attn_hd64_init_device(device);
+    if (rc != 0) return rc;
+    auto* s = new lg_attn_session();
+    s->device = device; s->max_batch = max_batch; s->heads = heads; s->max_n_q = max_n_q; s->max_n_kv = max_n_kv;
+    s->io_dtype = io_dtype; s->n_slots = n_slots;
+    const size_t in_es = (io_dtype == LG_ATTN_F32_F32) ? 4 : 2;
+    const size_t out_es = (io_dtype == LG_ATTN_F16_F16) ? 2 : 4;
+    const size_t bh = static_cast<size_t>(max_batch) * heads;
+    s->q_bytes = align256(bh * max_n_q * kHeadDim * in_es);
+    s->kv_bytes = align256(bh * max_n_kv * kHeadDim * in_es);
+    s->o_bytes = align256(bh * max_n_q * kHeadDim * out_es);
+    s->ws_bytes = align256(lg_attn_hd64_workspace_bytes(max_batch, heads, max_n_q, max_n_kv, io_dtype));
+    const size_t slot = s->q_bytes + 2 * s->kv_bytes + s->o_bytes + s->ws_bytes;
+    e = cudaMalloc(&s->pool, slot * n_slots);
+    if (e != cudaSuccess) { delete s; return static_cast<int>(e); }
+    s->streams = new cudaStream_t[n_slots]();
+    for (int i = 0; i < n_slots; ++i) {
+        e = cudaStreamCreateWithFlags(&s->streams[i], cudaStreamNonBlocking);
+        if (e != cudaSuccess) { lg_attn_session_destroy(s); return static_cast<int>(e); }
+    }
+    *out = s;
+    return 0;
+}
+
+int lg_attn_session_submit(lg_attn_session* s, const void* q_host, const void* k_host, const void* v_host,
+                           void* o_host, int batch, int n_q, int n_kv) {
+    if (s == nullptr || q_host == nullptr || k_host == nullptr || v_host == nullptr || o_host == nullptr)
+        return LG_ATTN_EINVAL;
+    if (batch <= 0 || batch > s->max_batch || n_q <= 0 || n_q > s->max_n_q || n_kv <= 0 || n_kv > s->max_n_kv)
+        return LG_ATTN_EINVAL;
+    cudaError_t e = cudaSetDevice(s->device);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    const int i = static_cast<int>(s->next++ % static_cast<unsigned long long>(s->n_slots));
+    const size_t slot = s->q_bytes + 2 * s->kv_bytes + s->o_bytes + s->ws_bytes;
+    uint8_t* dq = s->pool + slot * i;
+    uint8_t* dk = dq + s->q_bytes;
+    uint8_t* dv = dk + s->kv_bytes;
+    uint8_t* dout = dv + s->kv_bytes;
+    uint8_t* dws = dout + s->o_bytes;
+    const size_t in_es = (s->io_dtype == LG_ATTN_F32_F32) ? 4 : 2;
+    const size_t out_es = (s->io_dtype == LG_ATTN_F16_F16) ? 2 : 4;
+    const size_t bh = static_cast<size_t>(batch) * s->heads;
+    cudaStream_t st = s->streams[i];
+    e = cudaMemcpyAsync(dq, q_host, bh * n_q * kHeadDim * in_es, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dk, k_host, bh * n_kv * kHeadDim * in_es, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dv, v_host, bh * n_kv * kHeadDim * in_es, cudaMemcpyHostToDevice, st);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    int rc = lg_attn_hd64_launch(dq, dk, dv, dout, batch, s->heads, n_q, n_kv, s->io_dtype,
+                                 s->ws_bytes ? dws : nullptr, s->ws_bytes, st);
+    if (rc != 0) return rc;
+    e = cudaMemcpyAsync(o_host, dout, bh * n_q * kHeadDim * out_es, cudaMemcpyDeviceToHost, st);
+    return static_cast<int>(e);
+}
+
+int lg_attn_session_sync(lg_attn_session* s) {
+    if (s == nullptr) return LG_ATTN_EINVAL;
+    for (int i = 0; i < s->n_slots; ++i) {
+        cudaError_t e = cudaStreamSynchronize(s->streams[i]);
+        if (e != cudaSuccess) return static_cast<int>(e);
+    }
+    return 0;
+}
+
+void lg_attn_session_destroy(lg_attn_session* s) {
+    if (s == nullptr) return;
+    (void)cudaSetDevice(s->device);
+    if (s->streams != nullptr) {
+        for (int i = 0; i < s->n_slots; ++i)
+            if (s->streams[i] != nullptr) (void)cudaStreamDestroy(s->streams[i]);
+        delete[] s->streams;
+    }
+    if (s->pool != nullptr) (void)cudaFree(s->pool);
+    delete s;
+}
+
 const char* lg_attn_error_string(int code) {
     switch (code) {
         case 0: return "success";

@@ -88,3 +88,39 @@ def attention_host(q, k, v, out_dtype=None, device: int = 0):
                                         b, h, n, m, modes[key], device)
     B.check(rc, "lg_attn_hd64_run_host")
     return o
+
+
+class HostSession:
+    """Host-buffer front end (``lg_attn_session_*``): persistent device buffers, round-robin streams.
+
+    ``submit`` takes host arrays / pinned CPU tensors (anything with a stable address) and is
+    asynchronous; results are valid after ``sync``.
+    """
+
+    def __init__(self, max_batch: int, heads: int, max_n_q: int, max_n_kv: int, mode: int = B.F16_F16,
+                 n_slots: int = 4, device: int = 0):
+        import ctypes
+
+        self._lib = B.load()
+        self._h = ctypes.c_void_p()
+        self.heads = heads
+        B.check(self._lib.lg_attn_session_create(ctypes.byref(self._h), device, max_batch, heads, max_n_q, max_n_kv,
+                                                 mode, n_slots), "lg_attn_session_create")
+
+    def submit(self, q_ptr: int, k_ptr: int, v_ptr: int, o_ptr: int, batch: int, n_q: int, n_kv: int) -> None:
+        B.check(self._lib.lg_attn_session_submit(self._h, q_ptr, k_ptr, v_ptr, o_ptr, batch, n_q, n_kv),
+                "lg_attn_session_submit")
+
+    def sync(self) -> None:
+        B.check(self._lib.lg_attn_session_sync(self._h), "lg_attn_session_sync")
+
+    def close(self) -> None:
+        if self._h:
+            self._lib.lg_attn_session_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
