@@ -9,13 +9,27 @@
 // with ONE kernel: ragged N, M are handled by TMA out-of-bounds zero fill (loads), an in-kernel
 // -inf mask on the last KV tile, and row-predicated 128-bit stores — no pad / unpad passes.
 //
-// Structure (one CTA = one 128-row Q tile of one (batch, head); 2 CTAs co-reside per SM):
-//   warps 0-3  softmax warpgroup: one S row per thread (tcgen05.ld 32x32b), FP32 online softmax,
-//              P written back to TMEM as packed FP16, lazy O rescale, epilogue
-//   warp  4    TMA producer (one elected lane): Q once, K/V tiles through a 2-stage mbarrier ring
-//   warp  5    tcgen05.mma issuer (one elected lane): S = Q K^T (SS), O += P V (TS, P from TMEM)
-//   warp  6    TMEM allocator;  warp 7 idle (register donor)
+// Structure (one CTA = one 128-row Q tile of one (batch, head) x one KV range; 2 CTAs per SM):
+//   warps 0-7  softmax: warp w owns TMEM lanes 32*(w%4).. (one S row per thread, tcgen05.ld
+//              32x32b) and the 64-column half (w/4) of every 128-wide S tile; the two halves of a
+//              row exchange their partial row max through shared memory (one 64-thread named
+//              barrier per tile).  FP32 online softmax, exp2 split between MUFU.EX2 and an
+//              FMA-pipe polynomial, P written back to TMEM as packed FP16, lazy O rescale, epilogue.
+//   warp  8    TMA producer (one elected lane): Q once, K/V tiles through a 2-stage mbarrier ring;
+//              the first loads are issued before the CTA-wide setup barrier
+//   warp  9    tcgen05.mma issuer (one elected lane): S = Q K^T (SS), O += P V (TS, P from TMEM)
+//   warp  10   TMEM allocator;  warp 11 idle (register donor)
 // TMEM columns: S [0,128) fp32 | O [128,192) fp32 | P [192,256) packed fp16 pairs.
+//
+// Split-KV (latency shapes, e.g. B=1 N=M=1024: 32 Q tiles for 148 SMs): `num_splits` CTAs of one
+// thread-block cluster share a Q tile and take consecutive KV ranges.  Each CTA stages its
+// unnormalised partial (O, m, l) in its own shared memory and bulk-copies (cp.async.bulk through
+// DSMEM, mbarrier complete_tx) the rows owned by each peer into that peer's receive area; every CTA
+// then rescales / sums / normalises / stores the 128/num_splits rows it owns.  One launch, no
+// workspace, no second kernel.
+//
+// Programmatic dependent launch: the prologue (barrier init, TMEM alloc, descriptor prefetch) runs
+// before griddepcontrol.wait, so in a back-to-back chain it overlaps the previous kernel's tail.
 //
 // No CUTLASS; see ptx_sm100.cuh for the hand-written encodings.
 
@@ -29,6 +43,7 @@
 #include <stdint.h>
 
 #include "attn_sm100.h"
+#include "softmax_math.cuh"
 
 namespace lgattn {
 
@@ -39,10 +54,10 @@ using namespace ptx;
 // ------------------------------------------------------------------------------------------------
 constexpr uint32_t kTileBytes = kBlockN * kHeadDim * 2;  // 16 KiB: 128 rows x 128 B
 constexpr uint32_t kSmemQ = 0;
-constexpr uint32_t kSmemK = kSmemQ + kTileBytes;               // kStages tiles
-constexpr uint32_t kSmemV = kSmemK + kStages * kTileBytes;     // kStages tiles
-constexpr uint32_t kSmemBar = kSmemV + kStages * kTileBytes;   // mbarriers + tmem slot
-constexpr uint32_t kSmemStage = kSmemK;                        // epilogue staging aliases K/V ring
+constexpr uint32_t kSmemRing = kSmemQ + kTileBytes;            // stage s: K at +s*32K, V at +s*32K+16K
+constexpr uint32_t kStageBytes = 2 * kTileBytes;
+constexpr uint32_t kSmemBar = kSmemRing + kStages * kStageBytes;  // mbarriers, tmem slot, row stats
+constexpr uint32_t kSmemStage = kSmemRing;                     // epilogue staging aliases the ring
 // barrier indices (8 bytes each)
 enum : uint32_t {
     kBarQFull = 0,
@@ -54,11 +69,25 @@ enum : uint32_t {
     kBarSEmpty,
     kBarPFull,
     kBarPVDone,
+    kBarComb,                         // split-KV: bytes pushed into this CTA's receive area
     kNumBars
 };
 constexpr uint32_t kSmemTmemSlot = kSmemBar + 8 * kNumBars;
-constexpr uint32_t kSmemUsed = kSmemTmemSlot + 16;
+// row-max / row-sum exchange between the two column halves: [parity][half][row] floats
+constexpr uint32_t kSmemExch = (kSmemTmemSlot + 16 + 15u) & ~15u;
+// split-KV: this CTA's own per-row (m, l), source of the bulk copies to the peers
+constexpr uint32_t kSmemStat = kSmemExch + 2 * 2 * kBlockM * 4;
+// split-KV receive area, (m, l) part: [source split][owned row] float2  (1 KiB for any split count)
+constexpr uint32_t kSmemCombStat = kSmemStat + kBlockM * 8;
+constexpr uint32_t kSmemUsed = kSmemCombStat + kBlockM * 8;
 static_assert(kSmemUsed + 1024 <= kSmemBytes, "shared memory budget");
+// split-KV receive area, partial-O part: [source split][owned row][64] fp32 = 32 KiB, carried only by
+// split launches (kSmemSplitExtra more dynamic shared memory; never aliased with live tiles because a
+// peer may finish first).  Cluster launches of a TMEM kernel run one CTA per SM anyway.
+constexpr uint32_t kSmemCombO = (kSmemUsed + 127u) & ~127u;
+constexpr uint32_t kSmemSplitExtra = kBlockM * kHeadDim * 4 + 128;
+constexpr uint32_t kCombBytes = kBlockM * kHeadDim * 4 + kBlockM * 8;  // what each CTA receives in total
+constexpr int kMaxSplits = 8;  // portable cluster size
 
 // TMEM column map
 constexpr uint32_t kTmemCols = 256;
@@ -66,31 +95,63 @@ constexpr uint32_t kColS = 0;
 constexpr uint32_t kColO = 128;
 constexpr uint32_t kColP = 192;
 
-// softmax(x/8): exp(0.125*(s-m)) = exp2((s-m) * 0.125 * log2(e))
-constexpr float kScaleLog2 = 0.125f * 1.4426950408889634f;
-// lazy rescale: keep the stale row max while the new one is < 2^kTau larger (P stays < 2^8 in fp16)
-constexpr float kTau = 8.0f;
+constexpr int kHalfN = kBlockN / 2;  // S columns per softmax warp
 
-constexpr int kRegsSoftmax = 216;
-constexpr int kRegsOther = 40;
+// register budget: 384 threads launch at 80; the 4 service warps drop to 32, the 8 softmax warps take 104
+constexpr int kRegsSoftmax = 104;
+constexpr int kRegsOther = 32;
 
-template <bool kOutF32>
+// launch flags
+constexpr int kFlagEarlyTrigger = 2; // single-wave grid: release the dependent launch right after setup
+
+// Optional timeline tracing (tuning builds only, -DLG_ATTN_TRACE): %globaltimer stamps of the first
+// CTAs of each launch, read back through lg_attn_debug_read_trace().
+#ifdef LG_ATTN_TRACE
+constexpr int kTraceLaunches = 64, kTraceCtas = 4, kTraceEvents = 14;
+__device__ unsigned long long g_trace[kTraceLaunches][kTraceCtas][kTraceEvents];
+__device__ __forceinline__ void trace_event(int seq, int ev) {
+    if (blockIdx.x < kTraceCtas) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        g_trace[seq % kTraceLaunches][blockIdx.x][ev] = t;
+    }
+}
+#define LG_TRACE(ev) trace_event(trace_seq, ev)
+#define LG_TRACE_ARG , int trace_seq
+#else
+#define LG_TRACE(ev)
+#define LG_TRACE_ARG
+#endif
+
+// kBigSmem only distinguishes the instantiation launched with the extra split-KV receive area, so that
+// its larger MaxDynamicSharedMemorySize attribute does not cap the occupancy of the regular launches.
+template <bool kOutF32, bool kBigSmem = false>
 __global__ void __launch_bounds__(kThreads, 2)
 lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
                  const __grid_constant__ CUtensorMap tm_v, void* __restrict__ out, int n_q, int n_kv,
-                 int tiles_m) {
+                 int tiles_m, int num_splits, int flags LG_TRACE_ARG) {
+    if (threadIdx.x == 0) LG_TRACE(0);
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t bars = smem + kSmemBar;
     auto bar = [&](uint32_t i) { return bars + 8u * i; };
+    auto smem_k = [&](int s) { return smem + kSmemRing + static_cast<uint32_t>(s) * kStageBytes; };
+    auto smem_v = [&](int s) { return smem + kSmemRing + static_cast<uint32_t>(s) * kStageBytes + kTileBytes; };
 
     const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
     const int lane = threadIdx.x & 31;
-    const int tile_m = blockIdx.x % tiles_m;
-    const int bh = blockIdx.x / tiles_m;
-    const int num_kv_tiles = (n_kv + kBlockN - 1) / kBlockN;
+    // Split-KV: the num_splits CTAs of a cluster share one Q tile and take consecutive KV ranges.
+    const int split = num_splits > 1 ? static_cast<int>(cluster_ctarank()) : 0;
+    const int work = blockIdx.x / num_splits;
+    const int tile_m = work % tiles_m;
+    const int bh = work / tiles_m;
+    const int total_kv_tiles = (n_kv + kBlockN - 1) / kBlockN;
+    const int kv_base = total_kv_tiles / num_splits, kv_rem = total_kv_tiles % num_splits;
+    const int num_kv_tiles = kv_base + (split < kv_rem ? 1 : 0);            // >= 1 (host: splits <= tiles)
+    const int kv_tile0 = split * kv_base + (split < kv_rem ? split : kv_rem);
+    const int prologue_tiles = num_kv_tiles < kStages ? num_kv_tiles : kStages;
 
-    if (warp == 4 && lane == 0) {
+    if (warp == kSoftmaxWarps && lane == 0) {
         prefetch_tmap(&tm_q);
         prefetch_tmap(&tm_k);
         prefetch_tmap(&tm_v);
@@ -102,12 +163,27 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
             mbar_init(bar(kBarVEmpty + s), 1);
         }
         mbar_init(bar(kBarSFull), 1);
-        mbar_init(bar(kBarSEmpty), 4);  // one arrival per softmax warp
-        mbar_init(bar(kBarPFull), 4);
+        mbar_init(bar(kBarSEmpty), kSoftmaxWarps);  // one arrival per softmax warp
+        mbar_init(bar(kBarPFull), kSoftmaxWarps);
         mbar_init(bar(kBarPVDone), 1);
+        mbar_init(bar(kBarComb), 1);
         fence_mbar_init();
+        if (num_splits > 1) mbar_arrive_expect_tx(bar(kBarComb), kCombBytes);
+        // Everything above is independent of earlier kernels in the stream; the loads are not.
+        pdl_wait_prior_grids();
+        LG_TRACE(12);
+        // First loads go out before the CTA-wide setup barrier (they only need this thread's inits).
+        mbar_arrive_expect_tx(bar(kBarQFull), kTileBytes);
+        tma_load_3d(smem + kSmemQ, &tm_q, bar(kBarQFull), 0, tile_m * kBlockM, bh);
+        for (int j = 0; j < prologue_tiles; ++j) {
+            mbar_arrive_expect_tx(bar(kBarKFull + j), kTileBytes);
+            tma_load_3d(smem_k(j), &tm_k, bar(kBarKFull + j), 0, (kv_tile0 + j) * kBlockN, bh);
+            mbar_arrive_expect_tx(bar(kBarVFull + j), kTileBytes);
+            tma_load_3d(smem_v(j), &tm_v, bar(kBarVFull + j), 0, (kv_tile0 + j) * kBlockN, bh);
+        }
+        LG_TRACE(13);
     }
-    if (warp == 6) {
+    if (warp == kSoftmaxWarps + 2) {
         tmem_alloc<kTmemCols>(smem + kSmemTmemSlot);
         tmem_relinquish();
     }
@@ -116,26 +192,31 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
     tc_fence_after();
     uint32_t tmem_base;
     asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(smem + kSmemTmemSlot));
+    if (threadIdx.x == 0) {
+        // Small (single-wave) grids let the next kernel in the stream start its prologue right away;
+        // large grids trigger at their epilogue so the dependents do not take slots from their own tail.
+        if (flags & kFlagEarlyTrigger) pdl_launch_dependents();
+        LG_TRACE(1);
+    }
+    // split-KV cluster barrier #1 ("my kBarComb is armed"): arrive now, wait only right before the
+    // first push into a peer, by which time every peer has long arrived.
+    if (num_splits > 1) cluster_arrive();
 
-    if (warp >= 4) {
+    if (warp >= kSoftmaxWarps) {
         setmaxnreg_dec<kRegsOther>();
-        if (warp == 4 && lane == 0) {
+        if (warp == kSoftmaxWarps && lane == 0) {
             // ===================================================================== TMA producer
-            mbar_arrive_expect_tx(bar(kBarQFull), kTileBytes);
-            tma_load_3d(smem + kSmemQ, &tm_q, bar(kBarQFull), 0, tile_m * kBlockM, bh);
-            for (int j = 0; j < num_kv_tiles; ++j) {
+            for (int j = prologue_tiles; j < num_kv_tiles; ++j) {
                 const int s = j % kStages;
                 const uint32_t par = ((j / kStages) - 1) & 1;
-                if (j >= kStages) mbar_wait(bar(kBarKEmpty + s), par);
+                mbar_wait(bar(kBarKEmpty + s), par);
                 mbar_arrive_expect_tx(bar(kBarKFull + s), kTileBytes);
-                tma_load_3d(smem + kSmemK + s * kTileBytes, &tm_k, bar(kBarKFull + s), 0,
-                            j * kBlockN, bh);
-                if (j >= kStages) mbar_wait(bar(kBarVEmpty + s), par);
+                tma_load_3d(smem_k(s), &tm_k, bar(kBarKFull + s), 0, (kv_tile0 + j) * kBlockN, bh);
+                mbar_wait(bar(kBarVEmpty + s), par);
                 mbar_arrive_expect_tx(bar(kBarVFull + s), kTileBytes);
-                tma_load_3d(smem + kSmemV + s * kTileBytes, &tm_v, bar(kBarVFull + s), 0,
-                            j * kBlockN, bh);
+                tma_load_3d(smem_v(s), &tm_v, bar(kBarVFull + s), 0, (kv_tile0 + j) * kBlockN, bh);
             }
-        } else if (warp == 5 && lane == 0) {
+        } else if (warp == kSoftmaxWarps + 1 && lane == 0) {
             // ===================================================================== MMA issuer
             constexpr uint32_t idesc_qk = make_idesc_f16_f32acc(kBlockM, kBlockN, false);
             constexpr uint32_t idesc_pv = make_idesc_f16_f32acc(kBlockM, kHeadDim, true);
@@ -148,7 +229,7 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
                 const int s = j % kStages;
                 mbar_wait(bar(kBarKFull + s), (j / kStages) & 1);
                 tc_fence_after();
-                const uint64_t desc_k = make_smem_desc_sw128(smem + kSmemK + s * kTileBytes, 16, 1024);
+                const uint64_t desc_k = make_smem_desc_sw128(smem_k(s), 16, 1024);
 #pragma unroll
                 for (int kk = 0; kk < kHeadDim / 16; ++kk) {
                     // K-major: advancing 16 halves along K = +32 B inside the 128-B swizzle row
@@ -159,6 +240,7 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
             };
 
             mbar_wait(bar(kBarQFull), 0);
+            LG_TRACE(2);
             issue_qk(0);
             for (int j = 0; j < num_kv_tiles; ++j) {
                 if (j + 1 < num_kv_tiles) {
@@ -169,8 +251,7 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
                 mbar_wait(bar(kBarVFull + s), (j / kStages) & 1);
                 mbar_wait(bar(kBarPFull), j & 1);
                 tc_fence_after();
-                const uint64_t desc_v =
-                    make_smem_desc_sw128(smem + kSmemV + s * kTileBytes, kTileBytes, 1024);
+                const uint64_t desc_v = make_smem_desc_sw128(smem_v(s), kTileBytes, 1024);
 #pragma unroll
                 for (int kk = 0; kk < kBlockN / 16; ++kk) {
                     // A = P from TMEM: 16 halves = 8 columns per k-step.
@@ -182,48 +263,67 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
                 mma_commit(bar(kBarPVDone));
             }
         }
+        if (num_splits > 1) {  // service warps just take part in the two cluster barriers
+            cluster_wait();
+            cluster_arrive();
+            cluster_wait();
+        }
     } else {
-        // ========================================================================= softmax warpgroup
+        // ========================================================================= softmax warps
         setmaxnreg_inc<kRegsSoftmax>();
-        const uint32_t lane_sel = static_cast<uint32_t>(warp * 32) << 16;
-        const uint32_t t_s = tmem_base + lane_sel + kColS;
-        const uint32_t t_o = tmem_base + lane_sel + kColO;
-        const uint32_t t_p = tmem_base + lane_sel + kColP;
+        const int quarter = warp & 3;          // TMEM lane quarter: rows 32*quarter + lane
+        const int half = warp >> 2;            // S columns [64*half, 64*half + 64)
+        const int row = quarter * 32 + lane;   // row inside the Q tile
+        const uint32_t lane_sel = static_cast<uint32_t>(quarter * 32) << 16;
+        const uint32_t t_s = tmem_base + lane_sel + kColS + static_cast<uint32_t>(half * kHalfN);
+        const uint32_t t_o = tmem_base + lane_sel + kColO + static_cast<uint32_t>(half * 32);
+        const uint32_t t_p = tmem_base + lane_sel + kColP + static_cast<uint32_t>(half * 32);
+        const uint32_t exch = smem + kSmemExch;  // [parity][half][row] floats
+        // named barrier shared with the other column half of the same rows: ids 1..4 (immediates, so
+        // the CTA reserves 6 of the SM's 16 hardware barriers and two CTAs still fit on one SM)
+        auto pair_sync = [&]() {
+            switch (quarter) {
+                case 0: asm volatile("bar.sync 1, 64;" ::: "memory"); break;
+                case 1: asm volatile("bar.sync 2, 64;" ::: "memory"); break;
+                case 2: asm volatile("bar.sync 3, 64;" ::: "memory"); break;
+                default: asm volatile("bar.sync 4, 64;" ::: "memory"); break;
+            }
+        };
+        auto exch_addr = [&](int parity, int h) {
+            return exch + static_cast<uint32_t>(((parity * 2 + h) * kBlockM + row) * 4);
+        };
 
         float m_used = -INFINITY;  // row max the exponent is referenced to (raw score units)
-        float l_sum = 0.f;
+        float l_sum = 0.f;         // this half's share of the row sum
 
         for (int j = 0; j < num_kv_tiles; ++j) {
             mbar_wait(bar(kBarSFull), j & 1);
+            if (j == 0 && threadIdx.x == 0) LG_TRACE(3);
             tc_fence_after();
-            uint32_t sr[kBlockN];
-#pragma unroll
-            for (int c = 0; c < kBlockN / 32; ++c) tmem_ld_x32(t_s + 32u * c, sr + 32 * c);
+            uint32_t sr[kHalfN];
+            tmem_ld_x32(t_s, sr);
+            tmem_ld_x32(t_s + 32u, sr + 32);
             tmem_wait_ld();
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(bar(kBarSEmpty));
 
             // ragged KV tail: columns past n_kv get -inf (TMA zero-filled K rows gave S = 0 there)
-            const int valid = n_kv - j * kBlockN;
-            if (valid < kBlockN) {
+            const int valid = n_kv - (kv_tile0 + j) * kBlockN - half * kHalfN;
+            if (valid < kHalfN) {
 #pragma unroll
-                for (int c = 0; c < kBlockN; ++c)
+                for (int c = 0; c < kHalfN; ++c)
                     if (c >= valid) sr[c] = 0xff800000u;
             }
 
-            float mx0 = __uint_as_float(sr[0]), mx1 = __uint_as_float(sr[1]);
-            float mx2 = __uint_as_float(sr[2]), mx3 = __uint_as_float(sr[3]);
-#pragma unroll
-            for (int c = 4; c < kBlockN; c += 4) {
-                mx0 = fmaxf(mx0, __uint_as_float(sr[c + 0]));
-                mx1 = fmaxf(mx1, __uint_as_float(sr[c + 1]));
-                mx2 = fmaxf(mx2, __uint_as_float(sr[c + 2]));
-                mx3 = fmaxf(mx3, __uint_as_float(sr[c + 3]));
-            }
-            const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
+            float mx = row_max<kHalfN>(sr);
+            // combine with the other column half of the same rows
+            st_shared_f32(exch_addr(j & 1, half), mx);
+            pair_sync();
+            mx = fmaxf(mx, ld_shared_f32(exch_addr(j & 1, half ^ 1)));
 
-            // lazy rescale decision (warp-uniform so the tcgen05.ld/st below stay aligned)
+            // lazy rescale decision (warp-uniform so the tcgen05.ld/st below stay aligned; both
+            // halves see identical row maxima, so they take the same branch)
             float alpha = 1.f;
             bool rescale = false;
             if (j == 0) {
@@ -239,38 +339,25 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
             }
             const float neg_m = -m_used * kScaleLog2;
 
-            // P = exp2(s*c - m*c); row sum in FP32; pack to FP16 pairs (element 2c in the low half)
-            uint32_t pk[kBlockN / 2];
-            float sum0 = 0.f, sum1 = 0.f;
-#pragma unroll
-            for (int c = 0; c < kBlockN; c += 2) {
-                const float p0 = ex2_approx(fmaf(__uint_as_float(sr[c]), kScaleLog2, neg_m));
-                const float p1 = ex2_approx(fmaf(__uint_as_float(sr[c + 1]), kScaleLog2, neg_m));
-                sum0 += p0;
-                sum1 += p1;
-                pk[c / 2] = pack_half2(p0, p1);
-            }
+            // P = exp2(s*c - m*c) as packed FP16 pairs + this half's FP32 row sum (softmax_math.cuh)
+            uint32_t pk[kHalfN / 2];
+            const float tile_sum = softmax_exp_pass<kHalfN>(sr, pk, neg_m);
 
             if (j > 0) {
                 mbar_wait(bar(kBarPVDone), (j - 1) & 1);  // P buffer free, O(j-1) final
                 tc_fence_after();
             }
             tmem_st_x32(t_p, pk);
-            tmem_st_x32(t_p + 32u, pk + 32);
             if (rescale) {
+                uint32_t orow[32];
+                tmem_ld_x32(t_o, orow);
+                tmem_wait_ld();
 #pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    uint32_t orow[32];
-                    tmem_ld_x32(t_o + 32u * h, orow);
-                    tmem_wait_ld();
-#pragma unroll
-                    for (int c = 0; c < 32; ++c)
-                        orow[c] = __float_as_uint(__uint_as_float(orow[c]) * alpha);
-                    tmem_st_x32(t_o + 32u * h, orow);
-                }
+                for (int c = 0; c < 32; ++c) orow[c] = __float_as_uint(__uint_as_float(orow[c]) * alpha);
+                tmem_st_x32(t_o, orow);
                 l_sum *= alpha;
             }
-            l_sum += sum0 + sum1;
+            l_sum += tile_sum;
             tmem_wait_st();
             tc_fence_before();
             __syncwarp();
@@ -278,65 +365,163 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
         }
 
         // ------------------------------------------------------------------------------- epilogue
+        if (threadIdx.x == 0) {
+            if (!(flags & kFlagEarlyTrigger)) pdl_launch_dependents();
+            LG_TRACE(4);
+        }
         mbar_wait(bar(kBarPVDone), (num_kv_tiles - 1) & 1);
         tc_fence_after();
-        uint32_t orow[kHeadDim];
+        if (threadIdx.x == 0) LG_TRACE(5);
+        // full row sum = this half's + the other half's (the parity slot last used by tile n-2 is free)
+        st_shared_f32(exch_addr(num_kv_tiles & 1, half), l_sum);
+        pair_sync();
+        const float l_row = l_sum + ld_shared_f32(exch_addr(num_kv_tiles & 1, half ^ 1));
+        uint32_t orow[32];  // this warp's 32 of the 64 output columns
         tmem_ld_x32(t_o, orow);
-        tmem_ld_x32(t_o + 32u, orow + 32);
         tmem_wait_ld();
-        const float inv_l = 1.0f / l_sum;
-        const int row0 = tile_m * kBlockM + warp * 32;  // first row of this warp's 32-row slab
+        const int row0 = tile_m * kBlockM + quarter * 32;  // first row of this warp's 32-row slab
+        // All MMAs and TMA loads of this CTA are complete (PVDone of the last tile), so its K/V ring is
+        // dead: stage through it (16-B chunks XOR-swizzled by row).
 
-        if constexpr (!kOutF32) {
-            // stage 32 rows x 128 B per warp (16-B chunks XOR-swizzled by row), then 512-B coalesced stores
-            const uint32_t stage = smem + kSmemStage + warp * (32 * 128);
+        if (num_splits > 1) {
+            // ================================================================= split-KV combine
+            // 1. stage the UNNORMALISED partial O row (fp32, [128][64]) and its (m, l) locally
+            if (half == 0) st_shared_v2f(smem + kSmemStat + row * 8, m_used, l_row);
 #pragma unroll
-            for (int c = 0; c < 8; ++c) {
+            for (int c = 0; c < 8; ++c)
+                st_shared_v4(smem + kSmemStage + row * 256 + (((half * 8 + c) ^ (row & 15)) << 4), orow[4 * c + 0],
+                             orow[4 * c + 1], orow[4 * c + 2], orow[4 * c + 3]);
+            fence_proxy_async_smem();                      // generic-proxy writes -> bulk-copy engine
+            if (threadIdx.x == 0) LG_TRACE(10);
+            cluster_wait();                                // barrier #1: every peer's kBarComb is armed
+            asm volatile("bar.sync 5, 256;" ::: "memory");  // all softmax threads have staged
+            if (threadIdx.x == 0) LG_TRACE(11);
+            // 2. one thread bulk-copies, to every cluster CTA, the block of rows that CTA owns
+            const int rows_per = kBlockM / num_splits;
+            const uint32_t recv_o = smem + kSmemCombO;
+            if (threadIdx.x == 0) {
+                for (int owner = 0; owner < num_splits; ++owner) {
+                    const uint32_t peer_bar = dsmem_addr(bar(kBarComb), owner);
+                    bulk_copy_smem_to_cluster(dsmem_addr(recv_o + split * rows_per * 256, owner),
+                                              smem + kSmemStage + owner * rows_per * 256, rows_per * 256, peer_bar);
+                    bulk_copy_smem_to_cluster(dsmem_addr(smem + kSmemCombStat + split * rows_per * 8, owner),
+                                              smem + kSmemStat + owner * rows_per * 8, rows_per * 8, peer_bar);
+                }
+                LG_TRACE(6);
+            }
+            // 3. wait until every split's block for the rows this CTA owns has landed, then combine
+            mbar_wait(bar(kBarComb), 0);
+            // cluster barrier #2 (exit): nobody may leave while a peer's bulk copy could still be reading
+            // its shared memory; once every CTA has seen its own receive barrier complete, all copies
+            // are done.  Arrive here, wait after the stores.
+            cluster_arrive();
+            if (threadIdx.x == 0) LG_TRACE(7);
+            for (int task = threadIdx.x; task < rows_per * 8; task += kSoftmaxWarps * 32) {
+                const int lr = task >> 3;  // owned row
+                const int cp = task & 7;   // 8-column group of the 64 output columns
+                const int grow = tile_m * kBlockM + split * rows_per + lr;
+                if (grow >= n_q) continue;
+                float ms[kMaxSplits], ls[kMaxSplits];
+                float4 v0[kMaxSplits], v1[kMaxSplits];
+                float m_glob = -INFINITY;
+#pragma unroll
+                for (int sp = 0; sp < kMaxSplits; ++sp) {
+                    if (sp < num_splits) {
+                        const int slot = sp * rows_per + lr;
+                        const float2 st = ld_shared_v2f(smem + kSmemCombStat + slot * 8);
+                        ms[sp] = st.x;
+                        ls[sp] = st.y;
+                        m_glob = fmaxf(m_glob, st.x);
+                        const uint32_t src = recv_o + slot * 256;
+                        v0[sp] = ld_shared_v4f(src + (((2 * cp) ^ (lr & 15)) << 4));
+                        v1[sp] = ld_shared_v4f(src + (((2 * cp + 1) ^ (lr & 15)) << 4));
+                    }
+                }
+                float l_tot = 0.f;
+                float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                for (int sp = 0; sp < kMaxSplits; ++sp) {
+                    if (sp < num_splits) {
+                        const float a = ex2_approx((ms[sp] - m_glob) * kScaleLog2);
+                        l_tot = fmaf(ls[sp], a, l_tot);
+                        acc[0] = fmaf(v0[sp].x, a, acc[0]); acc[1] = fmaf(v0[sp].y, a, acc[1]);
+                        acc[2] = fmaf(v0[sp].z, a, acc[2]); acc[3] = fmaf(v0[sp].w, a, acc[3]);
+                        acc[4] = fmaf(v1[sp].x, a, acc[4]); acc[5] = fmaf(v1[sp].y, a, acc[5]);
+                        acc[6] = fmaf(v1[sp].z, a, acc[6]); acc[7] = fmaf(v1[sp].w, a, acc[7]);
+                    }
+                }
+                const float inv = 1.0f / l_tot;
+                const size_t off = (static_cast<size_t>(bh) * n_q + grow) * kHeadDim + cp * 8;
+                if constexpr (!kOutF32) {
+                    uint4 v;
+                    v.x = pack_half2(acc[0] * inv, acc[1] * inv);
+                    v.y = pack_half2(acc[2] * inv, acc[3] * inv);
+                    v.z = pack_half2(acc[4] * inv, acc[5] * inv);
+                    v.w = pack_half2(acc[6] * inv, acc[7] * inv);
+                    st_global_v4(reinterpret_cast<__half*>(out) + off, v);
+                } else {
+                    uint4 w0, w1;
+                    w0.x = __float_as_uint(acc[0] * inv); w0.y = __float_as_uint(acc[1] * inv);
+                    w0.z = __float_as_uint(acc[2] * inv); w0.w = __float_as_uint(acc[3] * inv);
+                    w1.x = __float_as_uint(acc[4] * inv); w1.y = __float_as_uint(acc[5] * inv);
+                    w1.z = __float_as_uint(acc[6] * inv); w1.w = __float_as_uint(acc[7] * inv);
+                    st_global_v4(reinterpret_cast<float*>(out) + off, w0);
+                    st_global_v4(reinterpret_cast<float*>(out) + off + 4, w1);
+                }
+            }
+            cluster_wait();
+        } else if constexpr (!kOutF32) {
+            const float inv_l = 1.0f / l_row;
+            const uint32_t stage = smem + kSmemStage + warp * (32 * 64);  // 32 rows x 64 B per warp
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
                 uint32_t w[4];
 #pragma unroll
                 for (int e = 0; e < 4; ++e)
                     w[e] = pack_half2(__uint_as_float(orow[8 * c + 2 * e]) * inv_l,
                                       __uint_as_float(orow[8 * c + 2 * e + 1]) * inv_l);
-                st_shared_v4(stage + lane * 128 + ((c ^ (lane & 7)) << 4), w[0], w[1], w[2], w[3]);
+                st_shared_v4(stage + lane * 64 + ((c ^ ((lane >> 1) & 3)) << 4), w[0], w[1], w[2], w[3]);
             }
             __syncwarp();
-            __half* o = reinterpret_cast<__half*>(out) + static_cast<size_t>(bh) * n_q * kHeadDim;
+            __half* o = reinterpret_cast<__half*>(out) + static_cast<size_t>(bh) * n_q * kHeadDim + half * 32;
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const int r = i * 4 + (lane >> 3);
-                const int c = lane & 7;
-                const uint4 v = ld_shared_v4(stage + r * 128 + ((c ^ (r & 7)) << 4));
+            for (int i = 0; i < 4; ++i) {
+                const int r = i * 8 + (lane >> 2);
+                const int c = lane & 3;
+                const uint4 v = ld_shared_v4(stage + r * 64 + ((c ^ ((r >> 1) & 3)) << 4));
                 if (row0 + r < n_q) st_global_v4(o + static_cast<size_t>(row0 + r) * kHeadDim + c * 8, v);
             }
         } else {
-            // 32 rows x 256 B per warp
-            const uint32_t stage = smem + kSmemStage + warp * (32 * 256);
+            const float inv_l = 1.0f / l_row;
+            const uint32_t stage = smem + kSmemStage + warp * (32 * 128);  // 32 rows x 128 B per warp
 #pragma unroll
-            for (int c = 0; c < 16; ++c) {
-                st_shared_v4(stage + lane * 256 + ((c ^ (lane & 15)) << 4),
+            for (int c = 0; c < 8; ++c) {
+                st_shared_v4(stage + lane * 128 + ((c ^ (lane & 7)) << 4),
                              __float_as_uint(__uint_as_float(orow[4 * c + 0]) * inv_l),
                              __float_as_uint(__uint_as_float(orow[4 * c + 1]) * inv_l),
                              __float_as_uint(__uint_as_float(orow[4 * c + 2]) * inv_l),
                              __float_as_uint(__uint_as_float(orow[4 * c + 3]) * inv_l));
             }
             __syncwarp();
-            float* o = reinterpret_cast<float*>(out) + static_cast<size_t>(bh) * n_q * kHeadDim;
+            float* o = reinterpret_cast<float*>(out) + static_cast<size_t>(bh) * n_q * kHeadDim + half * 32;
 #pragma unroll
-            for (int i = 0; i < 16; ++i) {
-                const int r = i * 2 + (lane >> 4);
-                const int c = lane & 15;
-                const uint4 v = ld_shared_v4(stage + r * 256 + ((c ^ (r & 15)) << 4));
+            for (int i = 0; i < 8; ++i) {
+                const int r = i * 4 + (lane >> 3);
+                const int c = lane & 7;
+                const uint4 v = ld_shared_v4(stage + r * 128 + ((c ^ (r & 7)) << 4));
                 if (row0 + r < n_q) st_global_v4(o + static_cast<size_t>(row0 + r) * kHeadDim + c * 4, v);
             }
         }
     }
 
+    if (threadIdx.x == 0) LG_TRACE(8);
     tc_fence_before();
     __syncthreads();
-    if (warp == 6) {
+    if (warp == kSoftmaxWarps + 2) {
         tc_fence_after();
         tmem_dealloc<kTmemCols>(tmem_base);
     }
+    if (threadIdx.x == 0) LG_TRACE(9);
 }
 
 // FP32 -> FP16 (round-to-nearest-even) of Q, K, V in one launch; the kFLOAT plugin branch.

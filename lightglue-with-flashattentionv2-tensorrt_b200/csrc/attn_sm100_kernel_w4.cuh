@@ -1,0 +1,352 @@
+// B200-native (sm_100a) fused multi-head attention for LightGlue, head_dim 64.
+//
+//   O = softmax(Q K^T / 8) V      per (batch, head); Q [B,H,N,64], K/V [B,H,M,64], O [B,H,N,64]
+//
+// Replaces the reference hot path (all under /root/reference/lightglue_attention_plugin/):
+//   attention_headdim_64_fp16in_fp16out.cu:253-733   FA2-style kernel, FP16 out
+//   attention_headdim_64_fp16in_fp32out.cu:253-703   FA2-style kernel, FP32 out
+//   …fp16out.cu:736-857 / …fp32out.cu:706-830         pad / convert / unpad copy kernels
+// with ONE kernel: ragged N, M are handled by TMA out-of-bounds zero fill (loads), an in-kernel
+// -inf mask on the last KV tile, and row-predicated 128-bit stores — no pad / unpad passes.
+//
+// Structure (one CTA = one 128-row Q tile of one (batch, head); 2 CTAs co-reside per SM):
+//   warps 0-3  softmax warpgroup: one S row per thread (tcgen05.ld 32x32b), FP32 online softmax,
+//              P written back to TMEM as packed FP16, lazy O rescale, epilogue
+//   warp  4    TMA producer (one elected lane): Q once, K/V tiles through a 2-stage mbarrier ring
+//   warp  5    tcgen05.mma issuer (one elected lane): S = Q K^T (SS), O += P V (TS, P from TMEM)
+//   warp  6    TMEM allocator;  warp 7 idle (register donor)
+// TMEM columns: S [0,128) fp32 | O [128,192) fp32 | P [192,256) packed fp16 pairs.
+//
+// No CUTLASS; see ptx_sm100.cuh for the hand-written encodings.
+
+#pragma once
+#include "ptx_sm100.cuh"
+
+#include <cuda.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdint.h>
+
+#include "attn_sm100.h"
+#include "softmax_math.cuh"
+
+namespace lgattn {
+
+using namespace ptx;
+
+// ------------------------------------------------------------------------------------------------
+// shared-memory map (offsets from a 1024-byte aligned base; SWIZZLE_128B tiles need that alignment)
+// ------------------------------------------------------------------------------------------------
+constexpr uint32_t kTileBytes = kBlockN * kHeadDim * 2;  // 16 KiB: 128 rows x 128 B
+constexpr uint32_t kSmemQ = 0;
+constexpr uint32_t kSmemK = kSmemQ + kTileBytes;               // kStages tiles
+constexpr uint32_t kSmemV = kSmemK + kStages * kTileBytes;     // kStages tiles
+constexpr uint32_t kSmemBar = kSmemV + kStages * kTileBytes;   // mbarriers + tmem slot
+constexpr uint32_t kSmemStage = kSmemK;                        // epilogue staging aliases K/V ring
+// barrier indices (8 bytes each)
+enum : uint32_t {
+    kBarQFull = 0,
+    kBarKFull = 1,                    // [kStages]
+    kBarKEmpty = kBarKFull + kStages, // [kStages]
+    kBarVFull = kBarKEmpty + kStages,
+    kBarVEmpty = kBarVFull + kStages,
+    kBarSFull = kBarVEmpty + kStages,
+    kBarSEmpty,
+    kBarPFull,
+    kBarPVDone,
+    kNumBars
+};
+constexpr uint32_t kSmemTmemSlot = kSmemBar + 8 * kNumBars;
+constexpr uint32_t kSmemUsed = kSmemTmemSlot + 16;
+static_assert(kSmemUsed + 1024 <= kSmemBytes, "shared memory budget");
+
+// TMEM column map
+constexpr uint32_t kTmemCols = 256;
+constexpr uint32_t kColS = 0;
+constexpr uint32_t kColO = 128;
+constexpr uint32_t kColP = 192;
+
+constexpr int kRegsSoftmax = 216;
+constexpr int kRegsOther = 40;
+
+template <bool kOutF32>
+__global__ void __launch_bounds__(kThreads, 2)
+lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
+                 const __grid_constant__ CUtensorMap tm_v, void* __restrict__ out, int n_q, int n_kv,
+                 int tiles_m) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t bars = smem + kSmemBar;
+    auto bar = [&](uint32_t i) { return bars + 8u * i; };
+
+    const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
+    const int lane = threadIdx.x & 31;
+    const int tile_m = blockIdx.x % tiles_m;
+    const int bh = blockIdx.x / tiles_m;
+    const int num_kv_tiles = (n_kv + kBlockN - 1) / kBlockN;
+
+    if (warp == 4 && lane == 0) {
+        prefetch_tmap(&tm_q);
+        prefetch_tmap(&tm_k);
+        prefetch_tmap(&tm_v);
+        mbar_init(bar(kBarQFull), 1);
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(bar(kBarKFull + s), 1);
+            mbar_init(bar(kBarKEmpty + s), 1);
+            mbar_init(bar(kBarVFull + s), 1);
+            mbar_init(bar(kBarVEmpty + s), 1);
+        }
+        mbar_init(bar(kBarSFull), 1);
+        mbar_init(bar(kBarSEmpty), 4);  // one arrival per softmax warp
+        mbar_init(bar(kBarPFull), 4);
+        mbar_init(bar(kBarPVDone), 1);
+        fence_mbar_init();
+    }
+    if (warp == 6) {
+        tmem_alloc<kTmemCols>(smem + kSmemTmemSlot);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    uint32_t tmem_base;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(smem + kSmemTmemSlot));
+
+    if (warp >= 4) {
+        setmaxnreg_dec<kRegsOther>();
+        if (warp == 4 && lane == 0) {
+            // ===================================================================== TMA producer
+            mbar_arrive_expect_tx(bar(kBarQFull), kTileBytes);
+            tma_load_3d(smem + kSmemQ, &tm_q, bar(kBarQFull), 0, tile_m * kBlockM, bh);
+            for (int j = 0; j < num_kv_tiles; ++j) {
+                const int s = j % kStages;
+                const uint32_t par = ((j / kStages) - 1) & 1;
+                if (j >= kStages) mbar_wait(bar(kBarKEmpty + s), par);
+                mbar_arrive_expect_tx(bar(kBarKFull + s), kTileBytes);
+                tma_load_3d(smem + kSmemK + s * kTileBytes, &tm_k, bar(kBarKFull + s), 0,
+                            j * kBlockN, bh);
+                if (j >= kStages) mbar_wait(bar(kBarVEmpty + s), par);
+                mbar_arrive_expect_tx(bar(kBarVFull + s), kTileBytes);
+                tma_load_3d(smem + kSmemV + s * kTileBytes, &tm_v, bar(kBarVFull + s), 0,
+                            j * kBlockN, bh);
+            }
+        } else if (warp == 5 && lane == 0) {
+            // ===================================================================== MMA issuer
+            constexpr uint32_t idesc_qk = make_idesc_f16_f32acc(kBlockM, kBlockN, false);
+            constexpr uint32_t idesc_pv = make_idesc_f16_f32acc(kBlockM, kHeadDim, true);
+            const uint32_t t_s = tmem_base + kColS;
+            const uint32_t t_o = tmem_base + kColO;
+            const uint32_t t_p = tmem_base + kColP;
+            const uint64_t desc_q = make_smem_desc_sw128(smem + kSmemQ, 16, 1024);
+
+            auto issue_qk = [&](int j) {
+                const int s = j % kStages;
+                mbar_wait(bar(kBarKFull + s), (j / kStages) & 1);
+                tc_fence_after();
+                const uint64_t desc_k = make_smem_desc_sw128(smem + kSmemK + s * kTileBytes, 16, 1024);
+#pragma unroll
+                for (int kk = 0; kk < kHeadDim / 16; ++kk) {
+                    // K-major: advancing 16 halves along K = +32 B inside the 128-B swizzle row
+                    mma_f16_ss(t_s, desc_q + 2u * kk, desc_k + 2u * kk, idesc_qk, kk > 0 ? 1u : 0u);
+                }
+                mma_commit(bar(kBarKEmpty + s));
+                mma_commit(bar(kBarSFull));
+            };
+
+            mbar_wait(bar(kBarQFull), 0);
+            issue_qk(0);
+            for (int j = 0; j < num_kv_tiles; ++j) {
+                if (j + 1 < num_kv_tiles) {
+                    mbar_wait(bar(kBarSEmpty), j & 1);  // S(j) now lives in softmax registers
+                    issue_qk(j + 1);
+                }
+                const int s = j % kStages;
+                mbar_wait(bar(kBarVFull + s), (j / kStages) & 1);
+                mbar_wait(bar(kBarPFull), j & 1);
+                tc_fence_after();
+                const uint64_t desc_v =
+                    make_smem_desc_sw128(smem + kSmemV + s * kTileBytes, kTileBytes, 1024);
+#pragma unroll
+                for (int kk = 0; kk < kBlockN / 16; ++kk) {
+                    // A = P from TMEM: 16 halves = 8 columns per k-step.
+                    // B = V, MN-major: 16 kv rows = 2048 B per k-step.
+                    mma_f16_ts(t_o, t_p + 8u * kk, desc_v + 128u * kk, idesc_pv,
+                               (j > 0 || kk > 0) ? 1u : 0u);
+                }
+                mma_commit(bar(kBarVEmpty + s));
+                mma_commit(bar(kBarPVDone));
+            }
+        }
+    } else {
+        // ========================================================================= softmax warpgroup
+        setmaxnreg_inc<kRegsSoftmax>();
+        const uint32_t lane_sel = static_cast<uint32_t>(warp * 32) << 16;
+        const uint32_t t_s = tmem_base + lane_sel + kColS;
+        const uint32_t t_o = tmem_base + lane_sel + kColO;
+        const uint32_t t_p = tmem_base + lane_sel + kColP;
+
+        float m_used = -INFINITY;  // row max the exponent is referenced to (raw score units)
+        float l_sum = 0.f;
+
+        for (int j = 0; j < num_kv_tiles; ++j) {
+            mbar_wait(bar(kBarSFull), j & 1);
+            tc_fence_after();
+            uint32_t sr[kBlockN];
+#pragma unroll
+            for (int c = 0; c < kBlockN / 32; ++c) tmem_ld_x32(t_s + 32u * c, sr + 32 * c);
+            tmem_wait_ld();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar(kBarSEmpty));
+
+            // ragged KV tail: columns past n_kv get -inf (TMA zero-filled K rows gave S = 0 there)
+            const int valid = n_kv - j * kBlockN;
+            if (valid < kBlockN) {
+#pragma unroll
+                for (int c = 0; c < kBlockN; ++c)
+                    if (c >= valid) sr[c] = 0xff800000u;
+            }
+
+            const float mx = row_max<kBlockN>(sr);
+
+            // lazy rescale decision (warp-uniform so the tcgen05.ld/st below stay aligned)
+            float alpha = 1.f;
+            bool rescale = false;
+            if (j == 0) {
+                m_used = mx;
+            } else {
+                const bool need = (mx - m_used) * kScaleLog2 > kTau;
+                rescale = __any_sync(0xffffffffu, need);
+                if (rescale) {
+                    const float m_new = fmaxf(m_used, mx);
+                    alpha = ex2_approx((m_used - m_new) * kScaleLog2);
+                    m_used = m_new;
+                }
+            }
+            const float neg_m = -m_used * kScaleLog2;
+
+            // P = exp2(s*c - m*c) as packed FP16 pairs + the FP32 row sum (softmax_math.cuh)
+            uint32_t pk[kBlockN / 2];
+            const float tile_sum = softmax_exp_pass<kBlockN>(sr, pk, neg_m);
+
+            if (j > 0) {
+                mbar_wait(bar(kBarPVDone), (j - 1) & 1);  // P buffer free, O(j-1) final
+                tc_fence_after();
+            }
+            tmem_st_x32(t_p, pk);
+            tmem_st_x32(t_p + 32u, pk + 32);
+            if (rescale) {
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    uint32_t orow[32];
+                    tmem_ld_x32(t_o + 32u * h, orow);
+                    tmem_wait_ld();
+#pragma unroll
+                    for (int c = 0; c < 32; ++c)
+                        orow[c] = __float_as_uint(__uint_as_float(orow[c]) * alpha);
+                    tmem_st_x32(t_o + 32u * h, orow);
+                }
+                l_sum *= alpha;
+            }
+            l_sum += tile_sum;
+            tmem_wait_st();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar(kBarPFull));
+        }
+
+        // ------------------------------------------------------------------------------- epilogue
+        mbar_wait(bar(kBarPVDone), (num_kv_tiles - 1) & 1);
+        tc_fence_after();
+        uint32_t orow[kHeadDim];
+        tmem_ld_x32(t_o, orow);
+        tmem_ld_x32(t_o + 32u, orow + 32);
+        tmem_wait_ld();
+        const float inv_l = 1.0f / l_sum;
+        const int row0 = tile_m * kBlockM + warp * 32;  // first row of this warp's 32-row slab
+
+        if constexpr (!kOutF32) {
+            // stage 32 rows x 128 B per warp (16-B chunks XOR-swizzled by row), then 512-B coalesced stores
+            const uint32_t stage = smem + kSmemStage + warp * (32 * 128);
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                uint32_t w[4];
+#pragma unroll
+                for (int e = 0; e < 4; ++e)
+                    w[e] = pack_half2(__uint_as_float(orow[8 * c + 2 * e]) * inv_l,
+                                      __uint_as_float(orow[8 * c + 2 * e + 1]) * inv_l);
+                st_shared_v4(stage + lane * 128 + ((c ^ (lane & 7)) << 4), w[0], w[1], w[2], w[3]);
+            }
+            __syncwarp();
+            __half* o = reinterpret_cast<__half*>(out) + static_cast<size_t>(bh) * n_q * kHeadDim;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int r = i * 4 + (lane >> 3);
+                const int c = lane & 7;
+                const uint4 v = ld_shared_v4(stage + r * 128 + ((c ^ (r & 7)) << 4));
+                if (row0 + r < n_q) st_global_v4(o + static_cast<size_t>(row0 + r) * kHeadDim + c * 8, v);
+            }
+        } else {
+            // 32 rows x 256 B per warp
+            const uint32_t stage = smem + kSmemStage + warp * (32 * 256);
+#pragma unroll
+            for (int c = 0; c < 16; ++c) {
+                st_shared_v4(stage + lane * 256 + ((c ^ (lane & 15)) << 4),
+                             __float_as_uint(__uint_as_float(orow[4 * c + 0]) * inv_l),
+                             __float_as_uint(__uint_as_float(orow[4 * c + 1]) * inv_l),
+                             __float_as_uint(__uint_as_float(orow[4 * c + 2]) * inv_l),
+                             __float_as_uint(__uint_as_float(orow[4 * c + 3]) * inv_l));
+            }
+            __syncwarp();
+            float* o = reinterpret_cast<float*>(out) + static_cast<size_t>(bh) * n_q * kHeadDim;
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                const int r = i * 2 + (lane >> 4);
+                const int c = lane & 15;
+                const uint4 v = ld_shared_v4(stage + r * 256 + ((c ^ (r & 15)) << 4));
+                if (row0 + r < n_q) st_global_v4(o + static_cast<size_t>(row0 + r) * kHeadDim + c * 4, v);
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 6) {
+        tc_fence_after();
+        tmem_dealloc<kTmemCols>(tmem_base);
+    }
+}
+
+// FP32 -> FP16 (round-to-nearest-even) of Q, K, V in one launch; the kFLOAT plugin branch.
+// Replaces QKV_convert_from_fp32_to_fp16 (…fp32out.cu:706-768) minus its padding (not needed).
+__global__ void __launch_bounds__(256)
+lg_attn_cvt_f32_f16(const float4* __restrict__ q, const float4* __restrict__ k,
+                    const float4* __restrict__ v, uint4* __restrict__ qh, uint4* __restrict__ kh,
+                    uint4* __restrict__ vh, size_t nq8, size_t nkv8) {
+    // one thread = 8 elements: two float4 loads, one 16-byte store
+    const size_t total = nq8 + 2 * nkv8;
+    for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
+         i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+        const float4* src;
+        uint4* dst;
+        size_t off;
+        if (i < nq8) {
+            src = q; dst = qh; off = i;
+        } else if (i < nq8 + nkv8) {
+            src = k; dst = kh; off = i - nq8;
+        } else {
+            src = v; dst = vh; off = i - nq8 - nkv8;
+        }
+        const float4 a = __ldg(src + 2 * off);
+        const float4 b = __ldg(src + 2 * off + 1);
+        uint4 r;
+        r.x = pack_half2(a.x, a.y);
+        r.y = pack_half2(a.z, a.w);
+        r.z = pack_half2(b.x, b.y);
+        r.w = pack_half2(b.z, b.w);
+        dst[off] = r;
+    }
+}
+
+}  // namespace lgattn

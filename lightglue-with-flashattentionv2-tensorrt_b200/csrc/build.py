@@ -21,7 +21,8 @@ LIB = BUILD / "liblightglue_attention_plugin.so"
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 SOURCES = [CSRC / "lg_attn_api.cu", CSRC / "plugin" / "lightglue_attention_plugin.cpp",
            CSRC / "plugin" / "mock_trt_host.cpp"]
-HEADERS = [CSRC / "attn_sm100_kernel.cuh", CSRC / "attn_sm100.h", CSRC / "ptx_sm100.cuh",
+HEADERS = [CSRC / "attn_sm100_kernel.cuh", CSRC / "attn_sm100_kernel_w4.cuh", CSRC / "softmax_math.cuh",
+           CSRC / "attn_sm100.h", CSRC / "ptx_sm100.cuh",
            CSRC / "plugin" / "lightglue_attention_plugin.h", CSRC / "plugin" / "mock_nvinfer" / "NvInfer.h",
            CSRC.parent.parent / "include" / "lg_attn.h"]
 
@@ -52,15 +53,18 @@ def up_to_date() -> bool:
     return all(p.stat().st_mtime <= t for p in SOURCES + HEADERS + [Path(__file__)])
 
 
-def build(force: bool = False, verbose: bool = False) -> Path:
-    if not force and up_to_date():
+def build(force: bool = False, verbose: bool = False, defs: list[str] | None = None, out: Path | None = None) -> Path:
+    """Default: the product library.  `defs` / `out` build a tuning variant (extra -D flags) elsewhere."""
+    if out is None and not force and up_to_date():
         return LIB
     BUILD.mkdir(exist_ok=True)
+    lib = out or LIB
+    lib.parent.mkdir(parents=True, exist_ok=True)
     trt_inc = find_tensorrt_include()
     inc = ["-I", str(trt_inc)] if trt_inc else ["-I", str(CSRC / "plugin" / "mock_nvinfer")]
     libs = ["-lnvinfer"] if trt_inc else []
     cmd = [nvcc(), *ARCH, "-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-fvisibility=default",
-           "-shared", "-cudart", "shared", *inc, "-o", str(LIB), *map(str, SOURCES), *libs]
+           "-shared", "-cudart", "shared", *inc, *(defs or []), "-o", str(lib), *map(str, SOURCES), *libs]
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
     r = subprocess.run(cmd, capture_output=True, text=True)
@@ -69,7 +73,7 @@ def build(force: bool = False, verbose: bool = False) -> Path:
         raise RuntimeError("nvcc failed: " + " ".join(cmd))
     if verbose:
         sys.stderr.write(r.stderr)
-    return LIB
+    return lib
 
 
 if __name__ == "__main__":

@@ -7,12 +7,19 @@
 // (/root/reference/lightglue_attention_plugin/lightglue_attention_plugin.cpp:165-267), minus the
 // pad / unpad passes that the new kernel makes unnecessary.
 
+#include "attn_sm100.h"
+#if LG_ATTN_SOFTMAX_WARPS == 4
+#include "attn_sm100_kernel_w4.cuh"
+#else
 #include "attn_sm100_kernel.cuh"
+#endif
 
 #include <cuda.h>
 #include <cuda_runtime.h>
 
 #include <atomic>
+#include <cstdio>
+#include <cstdlib>
 #include <mutex>
 
 #include "../../include/lg_attn.h"
@@ -20,6 +27,12 @@
 namespace {
 
 using namespace lgattn;
+
+#if LG_ATTN_SOFTMAX_WARPS != 4
+#define LG_SPLIT_EXTRA kSmemSplitExtra
+#else
+#define LG_SPLIT_EXTRA 0
+#endif
 
 constexpr int kMaxDevices = 64;
 constexpr int kAbiVersion = 1;
@@ -32,6 +45,10 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
 std::mutex g_init_mutex;
 std::atomic<int> g_device_ready[kMaxDevices];  // 0 = not initialised, 1 = ready
 std::atomic<EncodeTiledFn> g_encode{nullptr};
+int g_sm_count[kMaxDevices];              // written once per device under g_init_mutex, before g_device_ready
+int g_max_clusters[kMaxDevices][4];       // co-resident clusters of 1 << i CTAs (same publication rule)
+std::atomic<int> g_forced_splits{0};      // tuning override (LG_ATTN_SPLITS), 0 = automatic
+std::atomic<int> g_use_pdl{1};            // LG_ATTN_PDL=0 disables programmatic dependent launch
 
 int resolve_encode() {
     if (g_encode.load(std::memory_order_acquire) != nullptr) return 0;
@@ -68,6 +85,12 @@ int init_device_locked(int device) {
     cudaError_t e = cudaGetDeviceProperties(&prop, device);
     if (e != cudaSuccess) return static_cast<int>(e);
     if (prop.major != 10) return LG_ATTN_EARCH;
+    g_sm_count[device] = prop.multiProcessorCount;
+    if (const char* env = getenv("LG_ATTN_SPLITS")) {
+        const int v = atoi(env);
+        if (v == 1 || v == 2 || v == 4 || v == 8) g_forced_splits.store(v, std::memory_order_relaxed);
+    }
+    if (const char* env = getenv("LG_ATTN_PDL")) g_use_pdl.store(atoi(env) != 0 ? 1 : 0, std::memory_order_relaxed);
     int rc = resolve_encode();
     if (rc != 0) return rc;
     int prev = -1;
@@ -83,6 +106,35 @@ int init_device_locked(int device) {
     if (e == cudaSuccess)
         e = cudaFuncSetAttribute(lg_attn_hd64_fwd<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  static_cast<int>(kSmemBytes));
+#if LG_ATTN_SOFTMAX_WARPS != 4
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(lg_attn_hd64_fwd<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 static_cast<int>(kSmemBytes + kSmemSplitExtra));
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(lg_attn_hd64_fwd<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 static_cast<int>(kSmemBytes + kSmemSplitExtra));
+#endif
+#if LG_ATTN_SOFTMAX_WARPS != 4
+    for (int lg = 1; lg <= 3 && e == cudaSuccess; ++lg) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(64u << lg);
+        cfg.blockDim = dim3(kThreads);
+        cfg.dynamicSmemBytes = kSmemBytes + kSmemSplitExtra;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 1u << lg;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        int n = 0;
+        if (cudaOccupancyMaxActiveClusters(&n, lg_attn_hd64_fwd<false, true>, &cfg) != cudaSuccess) {
+            (void)cudaGetLastError();
+            n = 0;  // no split launches on this device
+        }
+        g_max_clusters[device][lg] = n;
+    }
+#endif
     if (prev != device && prev >= 0) (void)cudaSetDevice(prev);
     return static_cast<int>(e);
 }
@@ -92,6 +144,58 @@ size_t align256(size_t x) { return (x + 255) & ~static_cast<size_t>(255); }
 bool valid_dtype(int d) { return d == LG_ATTN_F16_F16 || d == LG_ATTN_F32_F32 || d == LG_ATTN_F16_F32; }
 
 }  // namespace
+
+#ifdef LG_ATTN_TRACE
+static std::atomic<int> g_trace_seq{0};
+#define LG_TRACE_SEQ , g_trace_seq.fetch_add(1)
+extern "C" int lg_attn_debug_blocks_per_sm(int extra_smem) {
+    int nb = -1;
+    cudaFuncAttributes fa;
+    cudaFuncGetAttributes(&fa, lgattn::lg_attn_hd64_fwd<false>);
+    printf("func attrs: regs=%d static smem=%zu maxDyn=%d maxThreads=%d carveout=%d clusterReq=%d nonPortable=%d\n", fa.numRegs,
+           fa.sharedSizeBytes, fa.maxDynamicSharedSizeBytes, fa.maxThreadsPerBlock, fa.preferredShmemCarveout,
+           fa.clusterDimMustBeSet, fa.nonPortableClusterSizeAllowed);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, lgattn::lg_attn_hd64_fwd<false>, lgattn::kThreads,
+                                                  lgattn::kSmemBytes + (extra_smem ? lgattn::kSmemSplitExtra : 0));
+    return nb;
+}
+extern "C" int lg_attn_debug_max_clusters(int splits, int extra_smem) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(static_cast<unsigned>(splits) * 64);
+    cfg.blockDim = dim3(lgattn::kThreads);
+    cfg.dynamicSmemBytes = lgattn::kSmemBytes + (extra_smem ? lgattn::kSmemSplitExtra : 0);
+    if (extra_smem) {
+        int n2 = -1;
+        cudaLaunchAttribute a2[1];
+        a2[0].id = cudaLaunchAttributeClusterDimension;
+        a2[0].val.clusterDim.x = static_cast<unsigned>(splits);
+        a2[0].val.clusterDim.y = 1;
+        a2[0].val.clusterDim.z = 1;
+        cfg.gridDim = dim3(static_cast<unsigned>(splits) * 64);
+        cfg.blockDim = dim3(lgattn::kThreads);
+        cfg.attrs = a2;
+        cfg.numAttrs = 1;
+        cudaError_t e2 = cudaOccupancyMaxActiveClusters(&n2, lgattn::lg_attn_hd64_fwd<false, true>, &cfg);
+        return e2 == cudaSuccess ? n2 : -static_cast<int>(e2);
+    }
+    cudaLaunchAttribute a[1];
+    a[0].id = cudaLaunchAttributeClusterDimension;
+    a[0].val.clusterDim.x = static_cast<unsigned>(splits);
+    a[0].val.clusterDim.y = 1;
+    a[0].val.clusterDim.z = 1;
+    cfg.attrs = a;
+    cfg.numAttrs = 1;
+    int n = -1;
+    cudaError_t e = cudaOccupancyMaxActiveClusters(&n, lgattn::lg_attn_hd64_fwd<false>, &cfg);
+    return e == cudaSuccess ? n : -static_cast<int>(e);
+}
+extern "C" int lg_attn_debug_read_trace(unsigned long long* dst, int reset_seq) {
+    if (reset_seq) g_trace_seq.store(0);
+    return static_cast<int>(cudaMemcpyFromSymbol(dst, lgattn::g_trace, sizeof(lgattn::g_trace)));
+}
+#else
+#define LG_TRACE_SEQ
+#endif
 
 extern "C" {
 
@@ -170,12 +274,71 @@ int lg_attn_hd64_launch(const void* q, const void* k, const void* v, void* o, in
     if ((rc = encode_rows_map(&tm_k, kh, n_kv, bh)) != 0) return rc;
     if ((rc = encode_rows_map(&tm_v, vh, n_kv, bh)) != 0) return rc;
 
-    const unsigned grid = static_cast<unsigned>(bh) * static_cast<unsigned>(tiles_m);
-    if (io_dtype == LG_ATTN_F16_F16) {
-        lg_attn_hd64_fwd<false><<<grid, kThreads, kSmemBytes, stream>>>(tm_q, tm_k, tm_v, o, n_q, n_kv, tiles_m);
-    } else {
-        lg_attn_hd64_fwd<true><<<grid, kThreads, kSmemBytes, stream>>>(tm_q, tm_k, tm_v, o, n_q, n_kv, tiles_m);
+    // Split-KV for latency shapes: when the Q tiles alone cannot fill the GPU, a cluster of `splits`
+    // CTAs shares each Q tile (consecutive KV ranges, DSMEM combine).  Power of two, <= 8, <= KV tiles;
+    // the largest count whose clusters are all co-resident (one wave), as reported by
+    // cudaOccupancyMaxActiveClusters at device init (B200: 74 / 33 / 15 clusters of 2 / 4 / 8).
+    const int kv_tiles = (n_kv + kBlockN - 1) / kBlockN;
+    int splits = 1;
+    int flags = 0;
+#if LG_ATTN_SOFTMAX_WARPS != 4
+    {
+        const long long base = bh_ll * tiles_m_ll;
+        const int forced = g_forced_splits.load(std::memory_order_relaxed);
+        if (forced > 0) {
+            splits = forced;
+            while (splits > 1 && splits > kv_tiles) splits /= 2;
+        } else if (base < g_sm_count[device]) {
+            for (int lg = 1; lg <= 3; ++lg) {
+                const int s = 1 << lg;
+                if (s <= kv_tiles && base <= g_max_clusters[device][lg]) splits = s;
+            }
+        }
     }
+#endif
+    if (bh_ll * tiles_m_ll * splits > 2147483647LL) return LG_ATTN_EINVAL;
+    if (bh_ll * tiles_m_ll * splits <= 2LL * g_sm_count[device]) flags |= kFlagEarlyTrigger;
+
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(static_cast<unsigned>(bh) * static_cast<unsigned>(tiles_m) * static_cast<unsigned>(splits));
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = kSmemBytes + (splits > 1 ? LG_SPLIT_EXTRA : 0);
+    cfg.stream = stream;
+    cudaLaunchAttribute attrs[2];
+    unsigned n_attrs = 0;
+    if (splits > 1) {
+        attrs[n_attrs].id = cudaLaunchAttributeClusterDimension;
+        attrs[n_attrs].val.clusterDim.x = static_cast<unsigned>(splits);
+        attrs[n_attrs].val.clusterDim.y = 1;
+        attrs[n_attrs].val.clusterDim.z = 1;
+        ++n_attrs;
+    }
+    if (g_use_pdl.load(std::memory_order_relaxed)) {
+        // programmatic dependent launch: this kernel's prologue may overlap the previous kernel's tail
+        // (it still waits, at griddepcontrol.wait, for that kernel to complete before touching memory)
+        attrs[n_attrs].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attrs[n_attrs].val.programmaticStreamSerializationAllowed = 1;
+        ++n_attrs;
+    }
+    cfg.attrs = attrs;
+    cfg.numAttrs = n_attrs;
+#if LG_ATTN_SOFTMAX_WARPS != 4
+    const bool big = cfg.dynamicSmemBytes > kSmemBytes;
+    if (io_dtype == LG_ATTN_F16_F16) {
+        e = cudaLaunchKernelEx(&cfg, big ? lg_attn_hd64_fwd<false, true> : lg_attn_hd64_fwd<false, false>, tm_q, tm_k, tm_v, o,
+                               n_q, n_kv, tiles_m, splits, flags LG_TRACE_SEQ);
+    } else {
+        e = cudaLaunchKernelEx(&cfg, big ? lg_attn_hd64_fwd<true, true> : lg_attn_hd64_fwd<true, false>, tm_q, tm_k, tm_v, o,
+                               n_q, n_kv, tiles_m, splits, flags LG_TRACE_SEQ);
+    }
+#else
+    if (io_dtype == LG_ATTN_F16_F16) {
+        e = cudaLaunchKernelEx(&cfg, lg_attn_hd64_fwd<false>, tm_q, tm_k, tm_v, o, n_q, n_kv, tiles_m);
+    } else {
+        e = cudaLaunchKernelEx(&cfg, lg_attn_hd64_fwd<true>, tm_q, tm_k, tm_v, o, n_q, n_kv, tiles_m);
+    }
+#endif
+    if (e != cudaSuccess) return static_cast<int>(e);
     return static_cast<int>(cudaGetLastError());
 }
 

@@ -58,6 +58,29 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     }
 }
 
+// Same wait for the single-thread producer / MMA-issuer warps: the suspend-time hint lets the
+// hardware park the thread until the phase flips instead of re-issuing TRYWAIT every few cycles
+// (those spin instructions otherwise take issue slots from the softmax warps of the same SMSP).
+__device__ __forceinline__ void mbar_wait_parked(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{\n\t"
+            ".reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t"
+            "}\n"
+            : "=r"(ok)
+            : "r"(bar), "r"(parity), "r"(1000000u)
+            : "memory");
+    } while (ok == 0);
+}
+
+// named barrier among `count` threads (ids 1..15; id 0 is __syncthreads)
+__device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t count) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
+}
+
 // ----------------------------------------------------------------------------- TMA
 __device__ __forceinline__ void prefetch_tmap(const void* tmap) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tmap)) : "memory");
@@ -187,6 +210,74 @@ __device__ __forceinline__ void tmem_st_x16(uint32_t taddr, const uint32_t* r) {
         : "memory");
 }
 
+// ----------------------------------------------------------------------------- clusters / DSMEM
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+
+// Cluster-wide barrier over every thread of every CTA in the cluster, split into its two halves so
+// the latency can be hidden: arrive early (release: earlier shared / global writes become visible to
+// the peers), wait late (acquire).  Call with the warp converged (.aligned).
+__device__ __forceinline__ void cluster_arrive() {
+    __syncwarp();
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void cluster_wait() {
+    __syncwarp();
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+// address of the same shared-memory offset in CTA `rank` of this cluster
+__device__ __forceinline__ uint32_t dsmem_addr(uint32_t local_smem_addr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_smem_addr), "r"(rank));
+    return r;
+}
+
+__device__ __forceinline__ float4 ld_dsmem_v4(uint32_t cluster_addr) {
+    float4 v;
+    asm volatile("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                 : "r"(cluster_addr)
+                 : "memory");
+    return v;
+}
+
+__device__ __forceinline__ float2 ld_dsmem_v2(uint32_t cluster_addr) {
+    float2 v;
+    asm volatile("ld.shared::cluster.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(cluster_addr) : "memory");
+    return v;
+}
+
+__device__ __forceinline__ void st_dsmem_v4(uint32_t cluster_addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.shared::cluster.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(cluster_addr), "r"(a), "r"(b), "r"(c), "r"(d)
+                 : "memory");
+}
+
+__device__ __forceinline__ void st_dsmem_v2(uint32_t cluster_addr, float a, float b) {
+    asm volatile("st.shared::cluster.v2.f32 [%0], {%1, %2};" ::"r"(cluster_addr), "f"(a), "f"(b) : "memory");
+}
+
+// shared::cta -> (possibly remote) shared::cluster bulk copy by the TMA engine; the byte count is
+// signalled on an mbarrier of the DESTINATION CTA (complete_tx).  size: multiple of 16 bytes.
+__device__ __forceinline__ void bulk_copy_smem_to_cluster(uint32_t dst_cluster_addr, uint32_t src_smem, uint32_t bytes,
+                                                          uint32_t dst_cluster_bar) {
+    asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     dst_cluster_addr),
+                 "r"(src_smem), "r"(bytes), "r"(dst_cluster_bar)
+                 : "memory");
+}
+
+// order this thread's generic-proxy shared-memory writes before subsequent async-proxy (TMA) reads
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// programmatic dependent launch: wait for the grids this launch depends on (no-op without the
+// launch attribute) / allow the dependent grid to start its prologue
+__device__ __forceinline__ void pdl_wait_prior_grids() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // ----------------------------------------------------------------------------- registers
 template <int kRegs>
 __device__ __forceinline__ void setmaxnreg_inc() {
@@ -200,8 +291,59 @@ __device__ __forceinline__ void setmaxnreg_dec() {
 // ----------------------------------------------------------------------------- misc math / memory
 __device__ __forceinline__ float ex2_approx(float x) {
     float y;
-    asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
+}
+
+// ----------------------------------------------------------------------------- packed f32x2 math
+// sm_100 has two-wide FP32 FMA/ADD (SASS FFMA2 / FADD2): one issue slot for two elements.
+__device__ __forceinline__ uint64_t pack_f32x2(float lo, float hi) {
+    uint64_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack_f32x2(uint64_t v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t fma_f32x2(uint64_t a, uint64_t b, uint64_t c) {
+    uint64_t d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ uint64_t add_f32x2(uint64_t a, uint64_t b) {
+    uint64_t d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ uint64_t sub_f32x2(uint64_t a, uint64_t b) {
+    uint64_t d;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+
+// 2^x for a pair, on the FMA/ALU pipes instead of the MUFU (16/clk/SM) pipe: Cody-Waite split
+// x = n + f, n = round(x) via the 1.5*2^23 magic add, 2^f by a degree-3 minimax polynomial on
+// [-0.5, 0.5] (relative error 7.5e-5, below the FP16 rounding of P), exponent patched in with one
+// shift-add (LEA).  x is clamped to >= -125 so the patched exponent stays positive (masked -inf
+// columns come out as 2^-125, i.e. 0 in FP16 and negligible in the FP32 row sum).
+__device__ __forceinline__ void ex2_poly_x2(uint64_t x, float& p0, float& p1) {
+    float x0, x1;
+    unpack_f32x2(x, x0, x1);
+    x0 = fmaxf(x0, -125.f);
+    x1 = fmaxf(x1, -125.f);
+    const uint64_t xc = pack_f32x2(x0, x1);
+    const uint64_t magic = pack_f32x2(12582912.f, 12582912.f);
+    const uint64_t t = add_f32x2(xc, magic);
+    const uint64_t n = sub_f32x2(t, magic);
+    const uint64_t f = sub_f32x2(xc, n);
+    uint64_t p = fma_f32x2(f, pack_f32x2(0.0551716648f, 0.0551716648f), pack_f32x2(0.2426111251f, 0.2426111251f));
+    p = fma_f32x2(p, f, pack_f32x2(0.6932609677f, 0.6932609677f));
+    p = fma_f32x2(p, f, pack_f32x2(0.9999280572f, 0.9999280572f));
+    float q0, q1, t0, t1;
+    unpack_f32x2(p, q0, q1);
+    unpack_f32x2(t, t0, t1);
+    p0 = __int_as_float(__float_as_int(q0) + (__float_as_int(t0) << 23));
+    p1 = __int_as_float(__float_as_int(q1) + (__float_as_int(t1) << 23));
 }
 
 __device__ __forceinline__ uint32_t pack_half2(float lo, float hi) {
@@ -217,12 +359,39 @@ __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t
                  : "memory");
 }
 
+__device__ __forceinline__ void st_shared_f32(uint32_t addr, float v) {
+    asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+
+__device__ __forceinline__ float ld_shared_f32(uint32_t addr) {
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory");
+    return v;
+}
+
+__device__ __forceinline__ void st_shared_v2f(uint32_t addr, float a, float b) {
+    asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(addr), "f"(a), "f"(b) : "memory");
+}
+
 __device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
     uint4 v;
     asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
                  : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
                  : "r"(addr)
                  : "memory");
+    return v;
+}
+
+// plain (non-volatile) shared loads: the compiler may batch them ahead of the arithmetic
+__device__ __forceinline__ float4 ld_shared_v4f(uint32_t addr) {
+    float4 v;
+    asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
+}
+
+__device__ __forceinline__ float2 ld_shared_v2f(uint32_t addr) {
+    float2 v;
+    asm("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(addr));
     return v;
 }
 

@@ -1,0 +1,136 @@
+// Per-thread softmax arithmetic of the attention kernel: one S row slice in registers ->
+// P = exp2(s*c - m*c) packed to FP16 pairs + the FP32 row sum.
+//
+// d = 64 attention does one exponential per 256 tensor FLOPs, so this file — not the MMAs — sets
+// the kernel's speed.  Measured issue costs on B200 per SM sub-partition (tools/microbench/pipe_rates.cu):
+//   MUFU.EX2 8 cycles | FFMA/FADD ~1-1.4 (heavy + lite pipes) | FFMA2/FADD2 ~3.5 (heavy pipe only)
+//   FMNMX / FMNMX3 / LEA / IMAD 2 (16-lane pipes)
+// so a fraction of the exponentials is moved from the MUFU pipe to the FMA pipes (Cody-Waite +
+// degree-3 polynomial), and packed f32x2 forms are used only where they save issue slots without
+// overloading the heavy pipe.  Compile-time knobs (defaults = best measured):
+//   LG_ATTN_POLY_OF_8    how many of every 8 columns take the polynomial path
+//   LG_ATTN_PACKED_SCALE 1: the s*c - m*c FFMA runs two columns per FFMA2 on the MUFU-path columns
+//   LG_ATTN_PACKED_SUM   1: row sums accumulate with FADD2
+#pragma once
+#include "ptx_sm100.cuh"
+
+#ifndef LG_ATTN_POLY_OF_8
+#define LG_ATTN_POLY_OF_8 3
+#endif
+#ifndef LG_ATTN_PACKED_SCALE
+#define LG_ATTN_PACKED_SCALE 0
+#endif
+#ifndef LG_ATTN_PACKED_SUM
+#define LG_ATTN_PACKED_SUM 0
+#endif
+
+namespace lgattn {
+
+using namespace ptx;
+
+// softmax(x/8): exp(0.125*(s-m)) = exp2((s-m) * 0.125 * log2(e))
+constexpr float kScaleLog2 = 0.125f * 1.4426950408889634f;
+// lazy rescale: keep the stale row max while the new one is < 2^kTau larger (P stays < 2^8 in fp16)
+constexpr float kTau = 8.0f;
+
+// ---- polynomial exp2 on the FMA pipes -----------------------------------------------------------
+// x = s*c - m*c lies in (-inf, kTau].  y = sat((x + 120) / 128) in [0, 1] comes out of ONE saturating
+// FFMA (the clamp is free), x' = 128*y = x + 120 in [0, 128]; n = round(x') via the 1.5*2^23 magic
+// add, f = x' - n in [-0.5, 0.5]; 2^f by a degree-3 minimax polynomial (relative error 7.5e-5, below
+// the FP16 rounding of P) whose coefficients carry the 2^-120 bias; the integer part is added to
+// the exponent field with one shift-add.  Columns masked to -inf give 2^-120 (0 in FP16).
+constexpr float kPolyBias = 120.f;
+constexpr float kPolyInvSpan = 1.f / 128.f;
+constexpr float kMagic = 12582912.f;  // 1.5 * 2^23
+constexpr float kTwoM120 = 7.52316384526264e-37f;  // 2^-120
+constexpr float kC0 = 0.9999280572f * kTwoM120;
+constexpr float kC1 = 0.6932609677f * kTwoM120;
+constexpr float kC2 = 0.2426111251f * kTwoM120;
+constexpr float kC3 = 0.0551716648f * kTwoM120;
+
+struct PolyConsts {
+    float scale;  // c / 128
+    float bias;   // (120 - m*c) / 128
+};
+
+__device__ __forceinline__ PolyConsts make_poly_consts(float neg_m_scaled) {
+    return {kScaleLog2 * kPolyInvSpan, (neg_m_scaled + kPolyBias) * kPolyInvSpan};
+}
+
+__device__ __forceinline__ float ex2_poly(float s, const PolyConsts& pc) {
+    float y;
+    asm("fma.rn.sat.f32 %0, %1, %2, %3;" : "=f"(y) : "f"(s), "f"(pc.scale), "f"(pc.bias));
+    const float t = fmaf(y, 128.f, kMagic);      // integer part of x' in the low mantissa bits
+    const float nn = kMagic - t;                 // -round(x')
+    const float f = fmaf(y, 128.f, nn);          // x' - round(x') in [-0.5, 0.5]
+    float p = fmaf(f, kC3, kC2);
+    p = fmaf(p, f, kC1);
+    p = fmaf(p, f, kC0);
+    return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
+}
+
+// ---- one row slice ------------------------------------------------------------------------------
+// sr[kCols]: raw scores (bit patterns); pk[kCols/2]: FP16 pairs (column 2i in the low half).
+// Returns the FP32 sum of the (unrounded) probabilities.
+template <int kCols>
+__device__ __forceinline__ float softmax_exp_pass(const uint32_t (&sr)[kCols], uint32_t (&pk)[kCols / 2],
+                                                  float neg_m_scaled) {
+    const PolyConsts pc = make_poly_consts(neg_m_scaled);
+    float p[kCols];
+#pragma unroll
+    for (int c = 0; c < kCols; c += 2) {
+        const bool poly0 = ((c % 8) < LG_ATTN_POLY_OF_8);
+        const bool poly1 = (((c + 1) % 8) < LG_ATTN_POLY_OF_8);
+        if (!poly0 && !poly1 && LG_ATTN_PACKED_SCALE) {
+            float x0, x1;
+            unpack_f32x2(fma_f32x2(pack_f32x2(__uint_as_float(sr[c]), __uint_as_float(sr[c + 1])),
+                                   pack_f32x2(kScaleLog2, kScaleLog2), pack_f32x2(neg_m_scaled, neg_m_scaled)),
+                         x0, x1);
+            p[c] = ex2_approx(x0);
+            p[c + 1] = ex2_approx(x1);
+        } else {
+            p[c] = poly0 ? ex2_poly(__uint_as_float(sr[c]), pc)
+                         : ex2_approx(fmaf(__uint_as_float(sr[c]), kScaleLog2, neg_m_scaled));
+            p[c + 1] = poly1 ? ex2_poly(__uint_as_float(sr[c + 1]), pc)
+                             : ex2_approx(fmaf(__uint_as_float(sr[c + 1]), kScaleLog2, neg_m_scaled));
+        }
+        pk[c / 2] = pack_half2(p[c], p[c + 1]);
+    }
+    float sum;
+    if (LG_ATTN_PACKED_SUM) {
+        uint64_t acc[4] = {0ull, 0ull, 0ull, 0ull};
+#pragma unroll
+        for (int c = 0; c < kCols; c += 2) acc[(c / 2) % 4] = add_f32x2(acc[(c / 2) % 4], pack_f32x2(p[c], p[c + 1]));
+        float s0, s1;
+        unpack_f32x2(add_f32x2(add_f32x2(acc[0], acc[1]), add_f32x2(acc[2], acc[3])), s0, s1);
+        sum = s0 + s1;
+    } else {
+        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+        for (int c = 0; c < kCols; c += 4) {
+            a0 += p[c];
+            a1 += p[c + 1];
+            a2 += p[c + 2];
+            a3 += p[c + 3];
+        }
+        sum = (a0 + a1) + (a2 + a3);
+    }
+    return sum;
+}
+
+// row max of a slice with 3-input FMNMX chains
+template <int kCols>
+__device__ __forceinline__ float row_max(const uint32_t (&sr)[kCols]) {
+    float mx0 = __uint_as_float(sr[0]), mx1 = __uint_as_float(sr[1]);
+    float mx2 = __uint_as_float(sr[2]), mx3 = __uint_as_float(sr[3]);
+#pragma unroll
+    for (int c = 4; c < kCols; c += 4) {
+        mx0 = fmaxf(mx0, __uint_as_float(sr[c + 0]));
+        mx1 = fmaxf(mx1, __uint_as_float(sr[c + 1]));
+        mx2 = fmaxf(mx2, __uint_as_float(sr[c + 2]));
+        mx3 = fmaxf(mx3, __uint_as_float(sr[c + 3]));
+    }
+    return fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
+}
+
+}  // namespace lgattn
