@@ -45,9 +45,20 @@
 #include "attn_sm100.h"
 #include "softmax_math.cuh"
 
+// poll interval of the single-thread service warps (TMA producer, MMA issuer)
+#ifndef LG_ATTN_SPIN_NS
+#define LG_ATTN_SPIN_NS 64
+#endif
+
 namespace lgattn {
+namespace w8 {  // the 8-softmax-warp kernel: latency shapes, split-KV clusters
 
 using namespace ptx;
+
+constexpr int kSoftmaxWarps = 8;                     // two column-half warpgroups over the same 128 rows
+constexpr int kThreads = 32 * (kSoftmaxWarps + 4);   // + TMA, MMA, TMEM-alloc, spare
+// Q tile + 2 x (K, V) tiles (16 KiB each) + barriers / row statistics, + 1 KiB slack for 1024-B alignment
+constexpr uint32_t kSmemBytes = (1 + 2 * kStages) * 16384 + 5120 + 1024;
 
 // ------------------------------------------------------------------------------------------------
 // shared-memory map (offsets from a 1024-byte aligned base; SWIZZLE_128B tiles need that alignment)
@@ -209,10 +220,10 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
             for (int j = prologue_tiles; j < num_kv_tiles; ++j) {
                 const int s = j % kStages;
                 const uint32_t par = ((j / kStages) - 1) & 1;
-                mbar_wait(bar(kBarKEmpty + s), par);
+                mbar_wait_backoff(bar(kBarKEmpty + s), par, LG_ATTN_SPIN_NS);
                 mbar_arrive_expect_tx(bar(kBarKFull + s), kTileBytes);
                 tma_load_3d(smem_k(s), &tm_k, bar(kBarKFull + s), 0, (kv_tile0 + j) * kBlockN, bh);
-                mbar_wait(bar(kBarVEmpty + s), par);
+                mbar_wait_backoff(bar(kBarVEmpty + s), par, LG_ATTN_SPIN_NS);
                 mbar_arrive_expect_tx(bar(kBarVFull + s), kTileBytes);
                 tma_load_3d(smem_v(s), &tm_v, bar(kBarVFull + s), 0, (kv_tile0 + j) * kBlockN, bh);
             }
@@ -227,7 +238,7 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
 
             auto issue_qk = [&](int j) {
                 const int s = j % kStages;
-                mbar_wait(bar(kBarKFull + s), (j / kStages) & 1);
+                mbar_wait_backoff(bar(kBarKFull + s), (j / kStages) & 1, LG_ATTN_SPIN_NS);
                 tc_fence_after();
                 const uint64_t desc_k = make_smem_desc_sw128(smem_k(s), 16, 1024);
 #pragma unroll
@@ -244,12 +255,12 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
             issue_qk(0);
             for (int j = 0; j < num_kv_tiles; ++j) {
                 if (j + 1 < num_kv_tiles) {
-                    mbar_wait(bar(kBarSEmpty), j & 1);  // S(j) now lives in softmax registers
+                    mbar_wait_backoff(bar(kBarSEmpty), j & 1, LG_ATTN_SPIN_NS);  // S(j) now lives in softmax registers
                     issue_qk(j + 1);
                 }
                 const int s = j % kStages;
-                mbar_wait(bar(kBarVFull + s), (j / kStages) & 1);
-                mbar_wait(bar(kBarPFull), j & 1);
+                mbar_wait_backoff(bar(kBarVFull + s), (j / kStages) & 1, LG_ATTN_SPIN_NS);
+                mbar_wait_backoff(bar(kBarPFull), j & 1, LG_ATTN_SPIN_NS);
                 tc_fence_after();
                 const uint64_t desc_v = make_smem_desc_sw128(smem_v(s), kTileBytes, 1024);
 #pragma unroll
@@ -524,35 +535,5 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
     if (threadIdx.x == 0) LG_TRACE(9);
 }
 
-// FP32 -> FP16 (round-to-nearest-even) of Q, K, V in one launch; the kFLOAT plugin branch.
-// Replaces QKV_convert_from_fp32_to_fp16 (…fp32out.cu:706-768) minus its padding (not needed).
-__global__ void __launch_bounds__(256)
-lg_attn_cvt_f32_f16(const float4* __restrict__ q, const float4* __restrict__ k,
-                    const float4* __restrict__ v, uint4* __restrict__ qh, uint4* __restrict__ kh,
-                    uint4* __restrict__ vh, size_t nq8, size_t nkv8) {
-    // one thread = 8 elements: two float4 loads, one 16-byte store
-    const size_t total = nq8 + 2 * nkv8;
-    for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
-         i += static_cast<size_t>(gridDim.x) * blockDim.x) {
-        const float4* src;
-        uint4* dst;
-        size_t off;
-        if (i < nq8) {
-            src = q; dst = qh; off = i;
-        } else if (i < nq8 + nkv8) {
-            src = k; dst = kh; off = i - nq8;
-        } else {
-            src = v; dst = vh; off = i - nq8 - nkv8;
-        }
-        const float4 a = __ldg(src + 2 * off);
-        const float4 b = __ldg(src + 2 * off + 1);
-        uint4 r;
-        r.x = pack_half2(a.x, a.y);
-        r.y = pack_half2(a.z, a.w);
-        r.z = pack_half2(b.x, b.y);
-        r.w = pack_half2(b.z, b.w);
-        dst[off] = r;
-    }
-}
-
+}  // namespace w8
 }  // namespace lgattn

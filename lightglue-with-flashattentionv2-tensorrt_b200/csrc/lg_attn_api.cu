@@ -8,11 +8,9 @@
 // pad / unpad passes that the new kernel makes unnecessary.
 
 #include "attn_sm100.h"
-#if LG_ATTN_SOFTMAX_WARPS == 4
-#include "attn_sm100_kernel_w4.cuh"
-#else
-#include "attn_sm100_kernel.cuh"
-#endif
+#include "attn_sm100_kernel.cuh"     // lgattn::w8 — latency shapes, split-KV clusters, PDL
+#include "attn_sm100_kernel_w4.cuh"  // lgattn::w4 — full grids (throughput)
+#include "cvt_f32_f16.cuh"
 
 #include <cuda.h>
 #include <cuda_runtime.h>
@@ -27,12 +25,6 @@
 namespace {
 
 using namespace lgattn;
-
-#if LG_ATTN_SOFTMAX_WARPS != 4
-#define LG_SPLIT_EXTRA kSmemSplitExtra
-#else
-#define LG_SPLIT_EXTRA 0
-#endif
 
 constexpr int kMaxDevices = 64;
 constexpr int kAbiVersion = 1;
@@ -101,25 +93,22 @@ int init_device_locked(int device) {
         if (e != cudaSuccess) return static_cast<int>(e);
     }
     // opt in to > 48 KiB dynamic shared memory (per device; the attribute is per context)
-    e = cudaFuncSetAttribute(lg_attn_hd64_fwd<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             static_cast<int>(kSmemBytes));
-    if (e == cudaSuccess)
-        e = cudaFuncSetAttribute(lg_attn_hd64_fwd<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 static_cast<int>(kSmemBytes));
-#if LG_ATTN_SOFTMAX_WARPS != 4
-    if (e == cudaSuccess)
-        e = cudaFuncSetAttribute(lg_attn_hd64_fwd<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 static_cast<int>(kSmemBytes + kSmemSplitExtra));
-    if (e == cudaSuccess)
-        e = cudaFuncSetAttribute(lg_attn_hd64_fwd<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 static_cast<int>(kSmemBytes + kSmemSplitExtra));
-#endif
-#if LG_ATTN_SOFTMAX_WARPS != 4
+    auto opt_in = [&](const void* fn, uint32_t bytes) {
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(bytes));
+    };
+    e = cudaSuccess;
+    opt_in(reinterpret_cast<const void*>(w4::lg_attn_hd64_fwd<false>), w4::kSmemBytes);
+    opt_in(reinterpret_cast<const void*>(w4::lg_attn_hd64_fwd<true>), w4::kSmemBytes);
+    opt_in(reinterpret_cast<const void*>(w8::lg_attn_hd64_fwd<false, false>), w8::kSmemBytes);
+    opt_in(reinterpret_cast<const void*>(w8::lg_attn_hd64_fwd<true, false>), w8::kSmemBytes);
+    opt_in(reinterpret_cast<const void*>(w8::lg_attn_hd64_fwd<false, true>), w8::kSmemBytes + w8::kSmemSplitExtra);
+    opt_in(reinterpret_cast<const void*>(w8::lg_attn_hd64_fwd<true, true>), w8::kSmemBytes + w8::kSmemSplitExtra);
+    // how many clusters of 2 / 4 / 8 split-KV CTAs are co-resident on this device
     for (int lg = 1; lg <= 3 && e == cudaSuccess; ++lg) {
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3(64u << lg);
-        cfg.blockDim = dim3(kThreads);
-        cfg.dynamicSmemBytes = kSmemBytes + kSmemSplitExtra;
+        cfg.blockDim = dim3(w8::kThreads);
+        cfg.dynamicSmemBytes = w8::kSmemBytes + w8::kSmemSplitExtra;
         cudaLaunchAttribute attr[1];
         attr[0].id = cudaLaunchAttributeClusterDimension;
         attr[0].val.clusterDim.x = 1u << lg;
@@ -128,13 +117,12 @@ int init_device_locked(int device) {
         cfg.attrs = attr;
         cfg.numAttrs = 1;
         int n = 0;
-        if (cudaOccupancyMaxActiveClusters(&n, lg_attn_hd64_fwd<false, true>, &cfg) != cudaSuccess) {
+        if (cudaOccupancyMaxActiveClusters(&n, w8::lg_attn_hd64_fwd<false, true>, &cfg) != cudaSuccess) {
             (void)cudaGetLastError();
             n = 0;  // no split launches on this device
         }
         g_max_clusters[device][lg] = n;
     }
-#endif
     if (prev != device && prev >= 0) (void)cudaSetDevice(prev);
     return static_cast<int>(e);
 }
@@ -148,50 +136,12 @@ bool valid_dtype(int d) { return d == LG_ATTN_F16_F16 || d == LG_ATTN_F32_F32 ||
 #ifdef LG_ATTN_TRACE
 static std::atomic<int> g_trace_seq{0};
 #define LG_TRACE_SEQ , g_trace_seq.fetch_add(1)
-extern "C" int lg_attn_debug_blocks_per_sm(int extra_smem) {
-    int nb = -1;
-    cudaFuncAttributes fa;
-    cudaFuncGetAttributes(&fa, lgattn::lg_attn_hd64_fwd<false>);
-    printf("func attrs: regs=%d static smem=%zu maxDyn=%d maxThreads=%d carveout=%d clusterReq=%d nonPortable=%d\n", fa.numRegs,
-           fa.sharedSizeBytes, fa.maxDynamicSharedSizeBytes, fa.maxThreadsPerBlock, fa.preferredShmemCarveout,
-           fa.clusterDimMustBeSet, fa.nonPortableClusterSizeAllowed);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, lgattn::lg_attn_hd64_fwd<false>, lgattn::kThreads,
-                                                  lgattn::kSmemBytes + (extra_smem ? lgattn::kSmemSplitExtra : 0));
-    return nb;
-}
-extern "C" int lg_attn_debug_max_clusters(int splits, int extra_smem) {
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(static_cast<unsigned>(splits) * 64);
-    cfg.blockDim = dim3(lgattn::kThreads);
-    cfg.dynamicSmemBytes = lgattn::kSmemBytes + (extra_smem ? lgattn::kSmemSplitExtra : 0);
-    if (extra_smem) {
-        int n2 = -1;
-        cudaLaunchAttribute a2[1];
-        a2[0].id = cudaLaunchAttributeClusterDimension;
-        a2[0].val.clusterDim.x = static_cast<unsigned>(splits);
-        a2[0].val.clusterDim.y = 1;
-        a2[0].val.clusterDim.z = 1;
-        cfg.gridDim = dim3(static_cast<unsigned>(splits) * 64);
-        cfg.blockDim = dim3(lgattn::kThreads);
-        cfg.attrs = a2;
-        cfg.numAttrs = 1;
-        cudaError_t e2 = cudaOccupancyMaxActiveClusters(&n2, lgattn::lg_attn_hd64_fwd<false, true>, &cfg);
-        return e2 == cudaSuccess ? n2 : -static_cast<int>(e2);
-    }
-    cudaLaunchAttribute a[1];
-    a[0].id = cudaLaunchAttributeClusterDimension;
-    a[0].val.clusterDim.x = static_cast<unsigned>(splits);
-    a[0].val.clusterDim.y = 1;
-    a[0].val.clusterDim.z = 1;
-    cfg.attrs = a;
-    cfg.numAttrs = 1;
-    int n = -1;
-    cudaError_t e = cudaOccupancyMaxActiveClusters(&n, lgattn::lg_attn_hd64_fwd<false>, &cfg);
-    return e == cudaSuccess ? n : -static_cast<int>(e);
+extern "C" int lg_attn_debug_max_clusters(int device, int log2_splits) {
+    return (device >= 0 && device < kMaxDevices && log2_splits >= 1 && log2_splits <= 3) ? g_max_clusters[device][log2_splits] : -1;
 }
 extern "C" int lg_attn_debug_read_trace(unsigned long long* dst, int reset_seq) {
     if (reset_seq) g_trace_seq.store(0);
-    return static_cast<int>(cudaMemcpyFromSymbol(dst, lgattn::g_trace, sizeof(lgattn::g_trace)));
+    return static_cast<int>(cudaMemcpyFromSymbol(dst, lgattn::w8::g_trace, sizeof(lgattn::w8::g_trace)));
 }
 #else
 #define LG_TRACE_SEQ
@@ -274,70 +224,69 @@ int lg_attn_hd64_launch(const void* q, const void* k, const void* v, void* o, in
     if ((rc = encode_rows_map(&tm_k, kh, n_kv, bh)) != 0) return rc;
     if ((rc = encode_rows_map(&tm_v, vh, n_kv, bh)) != 0) return rc;
 
-    // Split-KV for latency shapes: when the Q tiles alone cannot fill the GPU, a cluster of `splits`
-    // CTAs shares each Q tile (consecutive KV ranges, DSMEM combine).  Power of two, <= 8, <= KV tiles;
-    // the largest count whose clusters are all co-resident (one wave), as reported by
+    // Two kernels (see their headers): full grids take the 4-softmax-warp kernel (best sustained
+    // throughput); grids that cannot fill the GPU take the 8-softmax-warp kernel, which splits each
+    // Q tile's KV range over a cluster of `splits` CTAs (DSMEM combine) and uses programmatic
+    // dependent launch so its prologue overlaps the previous kernel's tail.  splits = the largest
+    // power of two <= min(8, KV tiles) whose clusters are all co-resident (one wave), from
     // cudaOccupancyMaxActiveClusters at device init (B200: 74 / 33 / 15 clusters of 2 / 4 / 8).
     const int kv_tiles = (n_kv + kBlockN - 1) / kBlockN;
-    int splits = 1;
-    int flags = 0;
-#if LG_ATTN_SOFTMAX_WARPS != 4
-    {
-        const long long base = bh_ll * tiles_m_ll;
-        const int forced = g_forced_splits.load(std::memory_order_relaxed);
-        if (forced > 0) {
-            splits = forced;
-            while (splits > 1 && splits > kv_tiles) splits /= 2;
-        } else if (base < g_sm_count[device]) {
-            for (int lg = 1; lg <= 3; ++lg) {
-                const int s = 1 << lg;
-                if (s <= kv_tiles && base <= g_max_clusters[device][lg]) splits = s;
-            }
-        }
-    }
-#endif
-    if (bh_ll * tiles_m_ll * splits > 2147483647LL) return LG_ATTN_EINVAL;
-    if (bh_ll * tiles_m_ll * splits <= 2LL * g_sm_count[device]) flags |= kFlagEarlyTrigger;
+    const long long base = bh_ll * tiles_m_ll;
+    const int forced = g_forced_splits.load(std::memory_order_relaxed);
+    const bool full_grid = base >= 2LL * g_sm_count[device] && forced == 0;
 
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(static_cast<unsigned>(bh) * static_cast<unsigned>(tiles_m) * static_cast<unsigned>(splits));
-    cfg.blockDim = dim3(kThreads);
-    cfg.dynamicSmemBytes = kSmemBytes + (splits > 1 ? LG_SPLIT_EXTRA : 0);
     cfg.stream = stream;
     cudaLaunchAttribute attrs[2];
     unsigned n_attrs = 0;
-    if (splits > 1) {
-        attrs[n_attrs].id = cudaLaunchAttributeClusterDimension;
-        attrs[n_attrs].val.clusterDim.x = static_cast<unsigned>(splits);
-        attrs[n_attrs].val.clusterDim.y = 1;
-        attrs[n_attrs].val.clusterDim.z = 1;
-        ++n_attrs;
-    }
-    if (g_use_pdl.load(std::memory_order_relaxed)) {
-        // programmatic dependent launch: this kernel's prologue may overlap the previous kernel's tail
-        // (it still waits, at griddepcontrol.wait, for that kernel to complete before touching memory)
-        attrs[n_attrs].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-        attrs[n_attrs].val.programmaticStreamSerializationAllowed = 1;
-        ++n_attrs;
-    }
-    cfg.attrs = attrs;
-    cfg.numAttrs = n_attrs;
-#if LG_ATTN_SOFTMAX_WARPS != 4
-    const bool big = cfg.dynamicSmemBytes > kSmemBytes;
-    if (io_dtype == LG_ATTN_F16_F16) {
-        e = cudaLaunchKernelEx(&cfg, big ? lg_attn_hd64_fwd<false, true> : lg_attn_hd64_fwd<false, false>, tm_q, tm_k, tm_v, o,
-                               n_q, n_kv, tiles_m, splits, flags LG_TRACE_SEQ);
+    if (full_grid) {
+        cfg.gridDim = dim3(static_cast<unsigned>(base));
+        cfg.blockDim = dim3(w4::kThreads);
+        cfg.dynamicSmemBytes = w4::kSmemBytes;
+        cfg.attrs = attrs;
+        cfg.numAttrs = 0;
+        e = cudaLaunchKernelEx(&cfg, io_dtype == LG_ATTN_F16_F16 ? w4::lg_attn_hd64_fwd<false> : w4::lg_attn_hd64_fwd<true>, tm_q,
+                               tm_k, tm_v, o, n_q, n_kv, tiles_m);
     } else {
-        e = cudaLaunchKernelEx(&cfg, big ? lg_attn_hd64_fwd<true, true> : lg_attn_hd64_fwd<true, false>, tm_q, tm_k, tm_v, o,
-                               n_q, n_kv, tiles_m, splits, flags LG_TRACE_SEQ);
+        int splits = 1;
+        if (forced > 0) {
+            splits = forced;
+        } else if (base < g_sm_count[device]) {
+            for (int lg = 1; lg <= 3; ++lg)
+                if ((1 << lg) <= kv_tiles && base <= g_max_clusters[device][lg]) splits = 1 << lg;
+        }
+        while (splits > 1 && splits > kv_tiles) splits /= 2;
+        if (base * splits > 2147483647LL) return LG_ATTN_EINVAL;
+        int flags = 0;
+        if (base * splits <= 2LL * g_sm_count[device]) flags |= w8::kFlagEarlyTrigger;
+        cfg.gridDim = dim3(static_cast<unsigned>(base) * static_cast<unsigned>(splits));
+        cfg.blockDim = dim3(w8::kThreads);
+        cfg.dynamicSmemBytes = w8::kSmemBytes + (splits > 1 ? w8::kSmemSplitExtra : 0);
+        if (splits > 1) {
+            attrs[n_attrs].id = cudaLaunchAttributeClusterDimension;
+            attrs[n_attrs].val.clusterDim.x = static_cast<unsigned>(splits);
+            attrs[n_attrs].val.clusterDim.y = 1;
+            attrs[n_attrs].val.clusterDim.z = 1;
+            ++n_attrs;
+        }
+        if (g_use_pdl.load(std::memory_order_relaxed)) {
+            // this kernel's prologue may overlap the previous kernel's tail (it still waits, at
+            // griddepcontrol.wait, for that kernel to complete before touching memory)
+            attrs[n_attrs].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            attrs[n_attrs].val.programmaticStreamSerializationAllowed = 1;
+            ++n_attrs;
+        }
+        cfg.attrs = attrs;
+        cfg.numAttrs = n_attrs;
+        const bool f32 = io_dtype != LG_ATTN_F16_F16;
+        if (splits > 1) {
+            e = cudaLaunchKernelEx(&cfg, f32 ? w8::lg_attn_hd64_fwd<true, true> : w8::lg_attn_hd64_fwd<false, true>, tm_q, tm_k,
+                                   tm_v, o, n_q, n_kv, tiles_m, splits, flags LG_TRACE_SEQ);
+        } else {
+            e = cudaLaunchKernelEx(&cfg, f32 ? w8::lg_attn_hd64_fwd<true, false> : w8::lg_attn_hd64_fwd<false, false>, tm_q, tm_k,
+                                   tm_v, o, n_q, n_kv, tiles_m, splits, flags LG_TRACE_SEQ);
+        }
     }
-#else
-    if (io_dtype == LG_ATTN_F16_F16) {
-        e = cudaLaunchKernelEx(&cfg, lg_attn_hd64_fwd<false>, tm_q, tm_k, tm_v, o, n_q, n_kv, tiles_m);
-    } else {
-        e = cudaLaunchKernelEx(&cfg, lg_attn_hd64_fwd<true>, tm_q, tm_k, tm_v, o, n_q, n_kv, tiles_m);
-    }
-#endif
     if (e != cudaSuccess) return static_cast<int>(e);
     return static_cast<int>(cudaGetLastError());
 }

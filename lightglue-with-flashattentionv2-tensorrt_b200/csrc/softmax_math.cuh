@@ -15,13 +15,13 @@
 #include "ptx_sm100.cuh"
 
 #ifndef LG_ATTN_POLY_OF_8
-#define LG_ATTN_POLY_OF_8 3
+#define LG_ATTN_POLY_OF_8 2
 #endif
 #ifndef LG_ATTN_PACKED_SCALE
-#define LG_ATTN_PACKED_SCALE 0
+#define LG_ATTN_PACKED_SCALE 1
 #endif
 #ifndef LG_ATTN_PACKED_SUM
-#define LG_ATTN_PACKED_SUM 0
+#define LG_ATTN_PACKED_SUM 1
 #endif
 
 namespace lgattn {

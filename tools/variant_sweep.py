@@ -16,19 +16,13 @@ CSRC = ROOT / "lightglue-with-flashattentionv2-tensorrt_b200" / "csrc"
 VDIR = CSRC / "build" / "variants"
 
 VARIANTS = {
-    # tag: defs
-    "w8_p3": ["-DLG_ATTN_SOFTMAX_WARPS=8", "-DLG_ATTN_POLY_OF_8=3"],
-    "w8_p0": ["-DLG_ATTN_SOFTMAX_WARPS=8", "-DLG_ATTN_POLY_OF_8=0"],
-    "w8_p2": ["-DLG_ATTN_SOFTMAX_WARPS=8", "-DLG_ATTN_POLY_OF_8=2"],
-    "w8_p4": ["-DLG_ATTN_SOFTMAX_WARPS=8", "-DLG_ATTN_POLY_OF_8=4"],
-    "w8_p3_ps": ["-DLG_ATTN_SOFTMAX_WARPS=8", "-DLG_ATTN_POLY_OF_8=3", "-DLG_ATTN_PACKED_SCALE=1"],
-    "w8_p3_psum": ["-DLG_ATTN_SOFTMAX_WARPS=8", "-DLG_ATTN_POLY_OF_8=3", "-DLG_ATTN_PACKED_SUM=1"],
-    "w4_p0": ["-DLG_ATTN_SOFTMAX_WARPS=4", "-DLG_ATTN_POLY_OF_8=0"],
-    "w4_p2": ["-DLG_ATTN_SOFTMAX_WARPS=4", "-DLG_ATTN_POLY_OF_8=2"],
-    "w4_p3": ["-DLG_ATTN_SOFTMAX_WARPS=4", "-DLG_ATTN_POLY_OF_8=3"],
-    "w4_p4": ["-DLG_ATTN_SOFTMAX_WARPS=4", "-DLG_ATTN_POLY_OF_8=4"],
-    "w4_p3_ps": ["-DLG_ATTN_SOFTMAX_WARPS=4", "-DLG_ATTN_POLY_OF_8=3", "-DLG_ATTN_PACKED_SCALE=1"],
-    "w4_p3_psum": ["-DLG_ATTN_SOFTMAX_WARPS=4", "-DLG_ATTN_POLY_OF_8=3", "-DLG_ATTN_PACKED_SUM=1"],
+    # tag: defs (both kernels of the library share the softmax arithmetic knobs)
+    "default": [],
+    "p0": ["-DLG_ATTN_POLY_OF_8=0"],
+    "p1": ["-DLG_ATTN_POLY_OF_8=1"],
+    "p3": ["-DLG_ATTN_POLY_OF_8=3"],
+    "p2_scalar_scale": ["-DLG_ATTN_PACKED_SCALE=0"],
+    "p2_scalar_sum": ["-DLG_ATTN_PACKED_SUM=0"],
 }
 
 
@@ -99,6 +93,8 @@ def run_all(tags):
         lib = VDIR / tag / "liblightglue_attention_plugin.so"
         if not lib.exists():
             continue
+        import time
+        time.sleep(3.0)  # let power / clocks recover: every variant is timed as a burst from idle
         env = dict(os.environ, LG_ATTN_LIB=str(lib))
         r = subprocess.run([sys.executable, "-c", CHILD % str(ROOT)], env=env, capture_output=True, text=True, timeout=300)
         line = [l for l in r.stdout.splitlines() if l.startswith("RESULT ")]
