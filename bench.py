@@ -41,6 +41,22 @@ UNIT = "TFLOP/s"
 WORKLOAD = "attn_plugin_op_B1_H4_N1024_M1024_d64_f16in_f16out"
 
 
+def load_traffic() -> float | None:
+    """DRAM bytes per launch of the headline kernel, from the committed `ncu --set full` summary
+    (profiles/r1_ncu_full_summary.csv, row 0 = B1 H4 N=M=1024 f16)."""
+    import csv
+
+    p = ROOT / "profiles" / "r1_ncu_full_summary.csv"
+    try:
+        rows = [r for r in csv.reader(l for l in p.read_text().splitlines() if not l.startswith("#"))]
+        hdr, first = rows[0], rows[2]
+        rd = float(first[hdr.index("dram__bytes_read.sum")]) * 1e6      # Mbyte
+        wr = float(first[hdr.index("dram__bytes_write.sum")]) * 1e6
+        return rd + wr
+    except Exception:  # noqa: BLE001
+        return None
+
+
 def load_peaks() -> dict:
     p = ROOT / "MEASURED_PEAKS.json"
     if p.exists():
@@ -271,10 +287,10 @@ def run_ours(args) -> None:
             "gpu_launches": launches,
             "us_per_launch": launch_us,
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-                         "traffic": args.traffic, "peak_source": peaks["source"] + ", burst bf16 GEMM",
-                         "kernel": "lg_attn_hd64_fwd<false>", "flops_per_launch": FLOPS_PER_CALL,
+                         "traffic": args.traffic if args.traffic is not None else load_traffic(), "peak_source": peaks["source"] + ", burst bf16 GEMM",
+                         "kernel": "lgattn::w8::lg_attn_hd64_fwd<false, true> (4-CTA split-KV clusters)", "flops_per_launch": FLOPS_PER_CALL,
                          "hbm_floor_us": BYTES_PER_CALL / (peaks["hbm_gbs"] * 1e9) * 1e6,
-                         "note": "latency-bound shape: 32 CTAs on 148 SMs; duration = timed region / launches (includes launch gaps)"},
+                         "note": "latency-bound shape: 32 Q tiles x 4 KV splits = 128 CTAs on 148 SMs; duration = timed region / launches (includes launch gaps)"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": CALLS * (qs + ks + vs), "d2h_bytes_per_step": CALLS * os_,
                     "steps": e2e_steps, "timing": "host wall clock around submit+sync, pinned host buffers, 4 streams"},
             "clocks": clocks,

@@ -15,6 +15,11 @@ __global__ void __launch_bounds__(256)
 lg_attn_cvt_f32_f16(const float4* __restrict__ q, const float4* __restrict__ k,
                     const float4* __restrict__ v, uint4* __restrict__ qh, uint4* __restrict__ kh,
                     uint4* __restrict__ vh, size_t nq8, size_t nkv8) {
+    // Programmatic dependent launch on both sides: the attention kernel that follows may run its
+    // prologue now (it waits for this grid to complete before loading), and this grid waits for
+    // whatever precedes it in the stream before touching memory.
+    pdl_launch_dependents();
+    pdl_wait_prior_grids();
     // one thread = 8 elements: two float4 loads, one 16-byte store
     const size_t total = nq8 + 2 * nkv8;
     for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;

@@ -209,9 +209,18 @@ int lg_attn_hd64_launch(const void* q, const void* k, const void* v, void* o, in
         const size_t total = nq8 + 2 * nkv8;
         size_t blocks = (total + 255) / 256;
         if (blocks > 148 * 16) blocks = 148 * 16;  // grid-stride; 16 resident-CTA waves over 148 SMs
-        lg_attn_cvt_f32_f16<<<static_cast<unsigned>(blocks), 256, 0, stream>>>(
-            static_cast<const float4*>(q), static_cast<const float4*>(k), static_cast<const float4*>(v), qd,
-            kd, vd, nq8, nkv8);
+        cudaLaunchConfig_t ccfg = {};
+        ccfg.gridDim = dim3(static_cast<unsigned>(blocks));
+        ccfg.blockDim = dim3(256);
+        ccfg.stream = stream;
+        cudaLaunchAttribute cattr[1];
+        cattr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        cattr[0].val.programmaticStreamSerializationAllowed = 1;
+        ccfg.attrs = cattr;
+        ccfg.numAttrs = g_use_pdl.load(std::memory_order_relaxed) ? 1 : 0;
+        e = cudaLaunchKernelEx(&ccfg, lg_attn_cvt_f32_f16, static_cast<const float4*>(q), static_cast<const float4*>(k),
+                               static_cast<const float4*>(v), qd, kd, vd, nq8, nkv8);
+        if (e != cudaSuccess) return static_cast<int>(e);
         e = cudaGetLastError();
         if (e != cudaSuccess) return static_cast<int>(e);
         qh = qd;
