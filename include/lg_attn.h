@@ -60,6 +60,20 @@ int lg_attn_hd64_launch(const void* q, const void* k, const void* v, void* o,
                         int batch, int heads, int n_q, int n_kv, int io_dtype,
                         void* workspace, size_t workspace_bytes, void* stream);
 
+/* Strided variant of the hot path for callers that hold Q/K/V inside packed projection buffers
+ * (the reshape / transpose / .contiguous() glue around every plugin call in the reference:
+ * lightglue_pytorch_with_plugin/lightglue.py:139-147, 154-156, 190-199).  Q, K, V are FP16; element
+ * (b, h, r, c) of a tensor lives at base + b*batch + h*head + r*row + c (strides in ELEMENTS, the 64
+ * head-dim elements contiguous).  Strides must be multiples of 16 bytes, pointers 16-byte aligned.
+ * out_f32: 0 -> FP16 output, 1 -> FP32 output.  No workspace.  Same guarantees as lg_attn_hd64_launch. */
+typedef struct lg_attn_strides {
+    long long batch, head, row;
+} lg_attn_strides;
+int lg_attn_hd64_launch_strided(const void* q, const void* k, const void* v, void* o,
+                                int batch, int heads, int n_q, int n_kv, int out_f32,
+                                const lg_attn_strides* sq, const lg_attn_strides* sk,
+                                const lg_attn_strides* sv, const lg_attn_strides* so, void* stream);
+
 /* Convenience for non-CUDA hosts (ctypes / cgo): HOST buffers in, HOST buffer out.
  * Allocates device scratch, copies H2D, launches, copies D2H, synchronises.  Not for the
  * TensorRT path; used by the end-to-end (`e2e`) measurement and by bindings without a CUDA runtime. */

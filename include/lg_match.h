@@ -1,0 +1,64 @@
+/* lg_match.h — C-ABI of the memory-bound glue either side of the attention hot path
+ * (widened only after rows a–e were parity-green and measured).
+ *
+ * The reference runs these as many small eager / TensorRT-fused elementwise launches around each
+ * plugin call.  Here each is ONE hand-written sm_100a kernel over packed FP16 activation buffers, so
+ * that the strided attention entry (lg_attn_hd64_launch_strided) never needs a layout copy:
+ *
+ *   lg_match_posenc          LearnableFourierPositionalEncoding.forward
+ *                            (lightglue_pytorch_with_plugin/lightglue.py:77-86)
+ *   lg_match_rotary          SelfBlock.rotate_half / apply_cached_rotary_emb on q and k
+ *                            (lightglue.py:143-144, 154-165), in place inside the packed projection
+ *   lg_match_layernorm_gelu  the LayerNorm(512) + GELU in the middle of both ffn stacks
+ *                            (lightglue.py:131-136, 181-186)
+ *   lg_match_assign          sigmoid_log_double_softmax + filter_matches
+ *                            (lightglue.py:216-224, 253-276; demo/lightglue_trt.cpp:291-345)
+ *
+ * All pointers are DEVICE pointers; every function only enqueues on `stream` (a cudaStream_t as
+ * void*): no allocation, no synchronisation, legal under stream capture.  Returns 0 or a
+ * cudaError_t / LG_ATTN_E* code (see lg_attn.h).
+ */
+#ifndef LG_MATCH_H_
+#define LG_MATCH_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* cs[r][i] = (cos, sin)(kpts[r] . wr[i]) for i < 32: kpts [rows,2] float (normalised keypoints),
+ * wr [32,2] float (posenc.Wr.weight), cs [rows,32,2] float. */
+int lg_match_posenc(const float* kpts, const float* wr, float* cs, long long rows, void* stream);
+
+/* In-place rotary on `n_blocks` consecutive 256-column blocks (4 heads x 64) at the start of every
+ * row of a packed FP16 buffer with leading dimension `ld` (elements): for each pair (2i, 2i+1) of a
+ * head, (a, b) -> (a cos_i - b sin_i, b cos_i + a sin_i), the same 32 angles for every head. */
+int lg_match_rotary(void* packed_half, long long rows, int ld, int n_blocks, const float* cs, void* stream);
+
+/* In place on h [rows, 512] FP16 (row stride `ld` elements): y = GELU(LayerNorm(h) * gamma + beta),
+ * erf-form GELU, statistics in FP32.  gamma, beta: float[512]. */
+int lg_match_layernorm_gelu(void* h_half, long long rows, int ld, const float* gamma, const float* beta,
+                            float eps, void* stream);
+
+/* Assignment + mutual-nearest-neighbour filter for `batch` pairs.
+ *   sim  [batch, n0, n1] float  : mdesc0 . mdesc1^T (already divided by dim^0.25 on both sides)
+ *   z0   matchability logits of image 0, FP16, element (b, i) at z0[(b*n0 + i) * z_stride]; z1 likewise
+ *   matches0 [batch, n0] int32  : index into image 1, or -1         (LightGlue `matches0`)
+ *   mscores0 [batch, n0] float  : exp(score) where mutual, else 0   (LightGlue `mscores0`)
+ *   scores   [batch, n0, n1] float or NULL: the full log-assignment matrix (`lightglue_scores`,
+ *            export_onnx_with_plugin.py:197) — only materialised when asked for.
+ * workspace: lg_match_assign_workspace_bytes() bytes. */
+size_t lg_match_assign_workspace_bytes(int batch, int n0, int n1);
+int lg_match_assign(const float* sim, const void* z0_half, const void* z1_half, long long z_stride,
+                    int batch, int n0, int n1, float threshold, int* matches0, float* mscores0,
+                    float* scores, void* workspace, size_t workspace_bytes, void* stream);
+
+/* Number of kernels each entry enqueues (for the bench's gpu_launches accounting). */
+int lg_match_assign_launches(int with_scores);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LG_MATCH_H_ */

@@ -6,12 +6,12 @@ host-side mirror of the reference's operator interface.  See DESIGN.md / INTEGRA
 """
 from . import _binding
 from ._binding import C_ABI_SYMBOLS, F16_F16, F16_F32, F32_F32, LIB_NAME, LgAttnError, load
-from .ops import HEAD_DIM, HostSession, attention, attention_host
+from .ops import HEAD_DIM, HostSession, attention, attention_host, attention_strided
 from .plugin_op import (ONNX_OP, PLUGIN_NAME, PLUGIN_NAMESPACE, PLUGIN_VERSION, Attention,
                         MHAHeadDim64, bind_reference_model)
 
 __all__ = [
-    "attention", "attention_host", "HostSession", "Attention", "MHAHeadDim64", "bind_reference_model", "load",
+    "attention", "attention_host", "attention_strided", "HostSession", "Attention", "MHAHeadDim64", "bind_reference_model", "load",
     "LgAttnError", "HEAD_DIM", "F16_F16", "F16_F32", "F32_F32", "C_ABI_SYMBOLS", "LIB_NAME",
     "PLUGIN_NAME", "PLUGIN_VERSION", "PLUGIN_NAMESPACE", "ONNX_OP",
 ]

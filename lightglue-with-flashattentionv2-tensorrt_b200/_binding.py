@@ -33,6 +33,7 @@ C_ABI_SYMBOLS = (
     "lg_attn_hd64_init_device",
     "lg_attn_hd64_workspace_bytes",
     "lg_attn_hd64_launch",
+    "lg_attn_hd64_launch_strided",
     "lg_attn_hd64_run_host",
     "lg_attn_hd64_launches_per_call",
     "lg_attn_error_string",
@@ -43,6 +44,11 @@ C_ABI_SYMBOLS = (
 )
 
 _lib = None
+
+
+class Strides(ctypes.Structure):
+    """``lg_attn_strides``: element strides of the batch / head / row dimensions."""
+    _fields_ = [("batch", ctypes.c_longlong), ("head", ctypes.c_longlong), ("row", ctypes.c_longlong)]
 
 
 class LgAttnError(RuntimeError):
@@ -79,6 +85,13 @@ def load() -> ctypes.CDLL:
         ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
         ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
         ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p,
+    ]
+    lib.lg_attn_hd64_launch_strided.restype = ctypes.c_int
+    lib.lg_attn_hd64_launch_strided.argtypes = [
+        ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+        ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+        ctypes.POINTER(Strides), ctypes.POINTER(Strides), ctypes.POINTER(Strides), ctypes.POINTER(Strides),
+        ctypes.c_void_p,
     ]
     lib.lg_attn_hd64_run_host.restype = ctypes.c_int
     lib.lg_attn_hd64_run_host.argtypes = [

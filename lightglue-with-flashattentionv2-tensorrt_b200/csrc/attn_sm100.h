@@ -9,4 +9,11 @@ constexpr int kBlockM = 128;    // Q rows per CTA  (= tcgen05.mma M, one TMEM la
 constexpr int kBlockN = 128;    // KV rows per pipeline step (= tcgen05.mma N of S = Q K^T)
 constexpr int kStages = 2;      // K/V shared-memory ring depth
 
+// Where a (batch, head) slice of O starts and how far apart its rows are, in ELEMENTS of the output
+// type.  Contiguous [B,H,N,64] (the plugin layout): sb = H*N*64, sh = N*64, sr = 64.
+struct OutLayout {
+    long long sb, sh, sr;
+    int heads;
+};
+
 }  // namespace lgattn

@@ -140,7 +140,7 @@ template <bool kOutF32, bool kBigSmem = false>
 __global__ void __launch_bounds__(kThreads, 2)
 lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
                  const __grid_constant__ CUtensorMap tm_v, void* __restrict__ out, int n_q, int n_kv,
-                 int tiles_m, int num_splits, int flags LG_TRACE_ARG) {
+                 int tiles_m, int num_splits, int flags, const OutLayout ol LG_TRACE_ARG) {
     if (threadIdx.x == 0) LG_TRACE(0);
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -156,6 +156,7 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
     const int work = blockIdx.x / num_splits;
     const int tile_m = work % tiles_m;
     const int bh = work / tiles_m;
+    const int hi = bh % ol.heads, bi = bh / ol.heads;
     const int total_kv_tiles = (n_kv + kBlockN - 1) / kBlockN;
     const int kv_base = total_kv_tiles / num_splits, kv_rem = total_kv_tiles % num_splits;
     const int num_kv_tiles = kv_base + (split < kv_rem ? 1 : 0);            // >= 1 (host: splits <= tiles)
@@ -185,12 +186,12 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
         LG_TRACE(12);
         // First loads go out before the CTA-wide setup barrier (they only need this thread's inits).
         mbar_arrive_expect_tx(bar(kBarQFull), kTileBytes);
-        tma_load_3d(smem + kSmemQ, &tm_q, bar(kBarQFull), 0, tile_m * kBlockM, bh);
+        tma_load_4d(smem + kSmemQ, &tm_q, bar(kBarQFull), 0, tile_m * kBlockM, hi, bi);
         for (int j = 0; j < prologue_tiles; ++j) {
             mbar_arrive_expect_tx(bar(kBarKFull + j), kTileBytes);
-            tma_load_3d(smem_k(j), &tm_k, bar(kBarKFull + j), 0, (kv_tile0 + j) * kBlockN, bh);
+            tma_load_4d(smem_k(j), &tm_k, bar(kBarKFull + j), 0, (kv_tile0 + j) * kBlockN, hi, bi);
             mbar_arrive_expect_tx(bar(kBarVFull + j), kTileBytes);
-            tma_load_3d(smem_v(j), &tm_v, bar(kBarVFull + j), 0, (kv_tile0 + j) * kBlockN, bh);
+            tma_load_4d(smem_v(j), &tm_v, bar(kBarVFull + j), 0, (kv_tile0 + j) * kBlockN, hi, bi);
         }
         LG_TRACE(13);
     }
@@ -222,10 +223,10 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
                 const uint32_t par = ((j / kStages) - 1) & 1;
                 mbar_wait_backoff(bar(kBarKEmpty + s), par, LG_ATTN_SPIN_NS);
                 mbar_arrive_expect_tx(bar(kBarKFull + s), kTileBytes);
-                tma_load_3d(smem_k(s), &tm_k, bar(kBarKFull + s), 0, (kv_tile0 + j) * kBlockN, bh);
+                tma_load_4d(smem_k(s), &tm_k, bar(kBarKFull + s), 0, (kv_tile0 + j) * kBlockN, hi, bi);
                 mbar_wait_backoff(bar(kBarVEmpty + s), par, LG_ATTN_SPIN_NS);
                 mbar_arrive_expect_tx(bar(kBarVFull + s), kTileBytes);
-                tma_load_3d(smem_v(s), &tm_v, bar(kBarVFull + s), 0, (kv_tile0 + j) * kBlockN, bh);
+                tma_load_4d(smem_v(s), &tm_v, bar(kBarVFull + s), 0, (kv_tile0 + j) * kBlockN, hi, bi);
             }
         } else if (warp == kSoftmaxWarps + 1 && lane == 0) {
             // ===================================================================== MMA issuer
@@ -462,7 +463,7 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
                     }
                 }
                 const float inv = 1.0f / l_tot;
-                const size_t off = (static_cast<size_t>(bh) * n_q + grow) * kHeadDim + cp * 8;
+                const long long off = bi * ol.sb + hi * ol.sh + grow * ol.sr + cp * 8;
                 if constexpr (!kOutF32) {
                     uint4 v;
                     v.x = pack_half2(acc[0] * inv, acc[1] * inv);
@@ -494,13 +495,13 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
                 st_shared_v4(stage + lane * 64 + ((c ^ ((lane >> 1) & 3)) << 4), w[0], w[1], w[2], w[3]);
             }
             __syncwarp();
-            __half* o = reinterpret_cast<__half*>(out) + static_cast<size_t>(bh) * n_q * kHeadDim + half * 32;
+            __half* o = reinterpret_cast<__half*>(out) + (bi * ol.sb + hi * ol.sh) + half * 32;
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 const int r = i * 8 + (lane >> 2);
                 const int c = lane & 3;
                 const uint4 v = ld_shared_v4(stage + r * 64 + ((c ^ ((r >> 1) & 3)) << 4));
-                if (row0 + r < n_q) st_global_v4(o + static_cast<size_t>(row0 + r) * kHeadDim + c * 8, v);
+                if (row0 + r < n_q) st_global_v4(o + (row0 + r) * ol.sr + c * 8, v);
             }
         } else {
             const float inv_l = 1.0f / l_row;
@@ -514,13 +515,13 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
                              __float_as_uint(__uint_as_float(orow[4 * c + 3]) * inv_l));
             }
             __syncwarp();
-            float* o = reinterpret_cast<float*>(out) + static_cast<size_t>(bh) * n_q * kHeadDim + half * 32;
+            float* o = reinterpret_cast<float*>(out) + (bi * ol.sb + hi * ol.sh) + half * 32;
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
                 const int r = i * 4 + (lane >> 3);
                 const int c = lane & 7;
                 const uint4 v = ld_shared_v4(stage + r * 128 + ((c ^ (r & 7)) << 4));
-                if (row0 + r < n_q) st_global_v4(o + static_cast<size_t>(row0 + r) * kHeadDim + c * 4, v);
+                if (row0 + r < n_q) st_global_v4(o + (row0 + r) * ol.sr + c * 4, v);
             }
         }
     }

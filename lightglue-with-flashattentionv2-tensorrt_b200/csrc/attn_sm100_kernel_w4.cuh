@@ -84,7 +84,7 @@ template <bool kOutF32>
 __global__ void __launch_bounds__(kThreads, 2)
 lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
                  const __grid_constant__ CUtensorMap tm_v, void* __restrict__ out, int n_q, int n_kv,
-                 int tiles_m) {
+                 int tiles_m, const OutLayout ol) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t bars = smem + kSmemBar;
@@ -94,6 +94,7 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
     const int lane = threadIdx.x & 31;
     const int tile_m = blockIdx.x % tiles_m;
     const int bh = blockIdx.x / tiles_m;
+    const int hi = bh % ol.heads, bi = bh / ol.heads;
     const int num_kv_tiles = (n_kv + kBlockN - 1) / kBlockN;
 
     if (warp == 4 && lane == 0) {
@@ -128,18 +129,18 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
         if (warp == 4 && lane == 0) {
             // ===================================================================== TMA producer
             mbar_arrive_expect_tx(bar(kBarQFull), kTileBytes);
-            tma_load_3d(smem + kSmemQ, &tm_q, bar(kBarQFull), 0, tile_m * kBlockM, bh);
+            tma_load_4d(smem + kSmemQ, &tm_q, bar(kBarQFull), 0, tile_m * kBlockM, hi, bi);
             for (int j = 0; j < num_kv_tiles; ++j) {
                 const int s = j % kStages;
                 const uint32_t par = ((j / kStages) - 1) & 1;
                 if (j >= kStages) mbar_wait_backoff(bar(kBarKEmpty + s), par, LG_ATTN_SPIN_NS);
                 mbar_arrive_expect_tx(bar(kBarKFull + s), kTileBytes);
-                tma_load_3d(smem + kSmemK + s * kTileBytes, &tm_k, bar(kBarKFull + s), 0,
-                            j * kBlockN, bh);
+                tma_load_4d(smem + kSmemK + s * kTileBytes, &tm_k, bar(kBarKFull + s), 0,
+                            j * kBlockN, hi, bi);
                 if (j >= kStages) mbar_wait_backoff(bar(kBarVEmpty + s), par, LG_ATTN_SPIN_NS);
                 mbar_arrive_expect_tx(bar(kBarVFull + s), kTileBytes);
-                tma_load_3d(smem + kSmemV + s * kTileBytes, &tm_v, bar(kBarVFull + s), 0,
-                            j * kBlockN, bh);
+                tma_load_4d(smem + kSmemV + s * kTileBytes, &tm_v, bar(kBarVFull + s), 0,
+                            j * kBlockN, hi, bi);
             }
         } else if (warp == 5 && lane == 0) {
             // ===================================================================== MMA issuer
@@ -289,13 +290,13 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
                 st_shared_v4(stage + lane * 128 + ((c ^ (lane & 7)) << 4), w[0], w[1], w[2], w[3]);
             }
             __syncwarp();
-            __half* o = reinterpret_cast<__half*>(out) + static_cast<size_t>(bh) * n_q * kHeadDim;
+            __half* o = reinterpret_cast<__half*>(out) + (bi * ol.sb + hi * ol.sh);
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
                 const int r = i * 4 + (lane >> 3);
                 const int c = lane & 7;
                 const uint4 v = ld_shared_v4(stage + r * 128 + ((c ^ (r & 7)) << 4));
-                if (row0 + r < n_q) st_global_v4(o + static_cast<size_t>(row0 + r) * kHeadDim + c * 8, v);
+                if (row0 + r < n_q) st_global_v4(o + (row0 + r) * ol.sr + c * 8, v);
             }
         } else {
             // 32 rows x 256 B per warp
@@ -309,13 +310,13 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
                              __float_as_uint(__uint_as_float(orow[4 * c + 3]) * inv_l));
             }
             __syncwarp();
-            float* o = reinterpret_cast<float*>(out) + static_cast<size_t>(bh) * n_q * kHeadDim;
+            float* o = reinterpret_cast<float*>(out) + (bi * ol.sb + hi * ol.sh);
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
                 const int r = i * 2 + (lane >> 4);
                 const int c = lane & 15;
                 const uint4 v = ld_shared_v4(stage + r * 256 + ((c ^ (r & 15)) << 4));
-                if (row0 + r < n_q) st_global_v4(o + static_cast<size_t>(row0 + r) * kHeadDim + c * 4, v);
+                if (row0 + r < n_q) st_global_v4(o + (row0 + r) * ol.sr + c * 4, v);
             }
         }
     }

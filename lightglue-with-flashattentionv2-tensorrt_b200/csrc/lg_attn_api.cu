@@ -55,18 +55,37 @@ int resolve_encode() {
     return 0;
 }
 
-// 3-D map over a contiguous [bh, rows, 64] half tensor: dims (64, rows, bh), box (64, 128, 1),
-// 128-byte swizzle.  Rows past `rows` inside a (batch, head) slice are zero-filled by the TMA unit,
-// which is what makes ragged N / M work without the reference's padded workspace copy.
-int encode_rows_map(CUtensorMap* map, const void* base, int rows, int bh) {
-    const cuuint64_t dims[3] = {static_cast<cuuint64_t>(kHeadDim), static_cast<cuuint64_t>(rows),
-                                static_cast<cuuint64_t>(bh)};
-    const cuuint64_t strides[2] = {static_cast<cuuint64_t>(kHeadDim) * 2,
-                                   static_cast<cuuint64_t>(rows) * kHeadDim * 2};
-    const cuuint32_t box[3] = {static_cast<cuuint32_t>(kHeadDim), static_cast<cuuint32_t>(kBlockN), 1};
-    const cuuint32_t estr[3] = {1, 1, 1};
+// 4-D map over a [batch, heads, rows, 64] half tensor with arbitrary (16-byte aligned) batch / head /
+// row strides: dims (64, rows, heads, batch), box (64, 128, 1, 1), 128-byte swizzle.  Rows past `rows`
+// inside a (batch, head) slice are zero-filled by the TMA unit, which is what makes ragged N / M work
+// without the reference's padded workspace copy; the strides are what lets packed projection outputs
+// ([B, N, 3*256] etc.) feed the kernel without a head-split transpose.
+struct RowStrides {
+    long long batch, head, row;  // elements
+};
+
+RowStrides contiguous_strides(int heads, int rows) {
+    return RowStrides{static_cast<long long>(heads) * rows * kHeadDim, static_cast<long long>(rows) * kHeadDim, kHeadDim};
+}
+
+bool strides_ok(const RowStrides& st, int batch, int heads, int rows, int elem_bytes) {
+    const long long a = 16 / elem_bytes;
+    auto ok = [&](long long v, int extent) { return extent == 1 || (v > 0 && v % a == 0 && v * elem_bytes < (1LL << 40)); };
+    return ok(st.batch, batch) && ok(st.head, heads) && ok(st.row, rows) && (rows == 1 || st.row >= kHeadDim);
+}
+
+int encode_rows_map(CUtensorMap* map, const void* base, int rows, int heads, int batch, const RowStrides& st) {
+    const cuuint64_t dims[4] = {static_cast<cuuint64_t>(kHeadDim), static_cast<cuuint64_t>(rows),
+                                static_cast<cuuint64_t>(heads), static_cast<cuuint64_t>(batch)};
+    // extent-1 dimensions never advance; give them any legal stride
+    const cuuint64_t srow = static_cast<cuuint64_t>(rows > 1 ? st.row : kHeadDim) * 2;
+    const cuuint64_t shead = heads > 1 ? static_cast<cuuint64_t>(st.head) * 2 : srow;
+    const cuuint64_t sbatch = batch > 1 ? static_cast<cuuint64_t>(st.batch) * 2 : srow;
+    const cuuint64_t strides[3] = {srow, shead, sbatch};
+    const cuuint32_t box[4] = {static_cast<cuuint32_t>(kHeadDim), static_cast<cuuint32_t>(kBlockN), 1, 1};
+    const cuuint32_t estr[4] = {1, 1, 1, 1};
     CUresult r = g_encode.load(std::memory_order_acquire)(
-        map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+        map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     return r == CUDA_SUCCESS ? 0 : LG_ATTN_EDRIVER;
@@ -147,6 +166,88 @@ extern "C" int lg_attn_debug_read_trace(unsigned long long* dst, int reset_seq) 
 #define LG_TRACE_SEQ
 #endif
 
+// Shared tail of both public launchers: tensor maps + kernel choice + launch.  FP16 Q/K/V only.
+static int launch_core(const void* qh, const void* kh, const void* vh, void* o, int batch, int heads, int n_q,
+                       int n_kv, bool out_f32, const RowStrides& sq, const RowStrides& sk, const RowStrides& sv,
+                       const RowStrides& so, int device, cudaStream_t stream) {
+    CUtensorMap tm_q, tm_k, tm_v;
+    int rc;
+    if ((rc = encode_rows_map(&tm_q, qh, n_q, heads, batch, sq)) != 0) return rc;
+    if ((rc = encode_rows_map(&tm_k, kh, n_kv, heads, batch, sk)) != 0) return rc;
+    if ((rc = encode_rows_map(&tm_v, vh, n_kv, heads, batch, sv)) != 0) return rc;
+    const OutLayout ol{so.batch, so.head, so.row, heads};
+    const long long bh_ll = static_cast<long long>(batch) * heads;
+    const long long tiles_m_ll = (static_cast<long long>(n_q) + kBlockM - 1) / kBlockM;
+    const int tiles_m = static_cast<int>(tiles_m_ll);
+    cudaError_t e = cudaSuccess;
+
+    // Two kernels (see their headers): full grids take the 4-softmax-warp kernel (best sustained
+    // throughput); grids that cannot fill the GPU take the 8-softmax-warp kernel, which splits each
+    // Q tile's KV range over a cluster of `splits` CTAs (DSMEM combine) and uses programmatic
+    // dependent launch so its prologue overlaps the previous kernel's tail.  splits = the largest
+    // power of two <= min(8, KV tiles) whose clusters are all co-resident (one wave), from
+    // cudaOccupancyMaxActiveClusters at device init (B200: 74 / 33 / 15 clusters of 2 / 4 / 8).
+    const int kv_tiles = (n_kv + kBlockN - 1) / kBlockN;
+    const long long base = bh_ll * tiles_m_ll;
+    const int forced = g_forced_splits.load(std::memory_order_relaxed);
+    const bool full_grid = base >= 2LL * g_sm_count[device] && forced == 0;
+
+    cudaLaunchConfig_t cfg = {};
+    cfg.stream = stream;
+    cudaLaunchAttribute attrs[2];
+    unsigned n_attrs = 0;
+    if (full_grid) {
+        cfg.gridDim = dim3(static_cast<unsigned>(base));
+        cfg.blockDim = dim3(w4::kThreads);
+        cfg.dynamicSmemBytes = w4::kSmemBytes;
+        cfg.attrs = attrs;
+        cfg.numAttrs = 0;
+        e = cudaLaunchKernelEx(&cfg, !out_f32 ? w4::lg_attn_hd64_fwd<false> : w4::lg_attn_hd64_fwd<true>, tm_q,
+                               tm_k, tm_v, o, n_q, n_kv, tiles_m, ol);
+    } else {
+        int splits = 1;
+        if (forced > 0) {
+            splits = forced;
+        } else if (base < g_sm_count[device]) {
+            for (int lg = 1; lg <= 3; ++lg)
+                if ((1 << lg) <= kv_tiles && base <= g_max_clusters[device][lg]) splits = 1 << lg;
+        }
+        while (splits > 1 && splits > kv_tiles) splits /= 2;
+        if (base * splits > 2147483647LL) return LG_ATTN_EINVAL;
+        int flags = 0;
+        if (base * splits <= 2LL * g_sm_count[device]) flags |= w8::kFlagEarlyTrigger;
+        cfg.gridDim = dim3(static_cast<unsigned>(base) * static_cast<unsigned>(splits));
+        cfg.blockDim = dim3(w8::kThreads);
+        cfg.dynamicSmemBytes = w8::kSmemBytes + (splits > 1 ? w8::kSmemSplitExtra : 0);
+        if (splits > 1) {
+            attrs[n_attrs].id = cudaLaunchAttributeClusterDimension;
+            attrs[n_attrs].val.clusterDim.x = static_cast<unsigned>(splits);
+            attrs[n_attrs].val.clusterDim.y = 1;
+            attrs[n_attrs].val.clusterDim.z = 1;
+            ++n_attrs;
+        }
+        if (g_use_pdl.load(std::memory_order_relaxed)) {
+            // this kernel's prologue may overlap the previous kernel's tail (it still waits, at
+            // griddepcontrol.wait, for that kernel to complete before touching memory)
+            attrs[n_attrs].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            attrs[n_attrs].val.programmaticStreamSerializationAllowed = 1;
+            ++n_attrs;
+        }
+        cfg.attrs = attrs;
+        cfg.numAttrs = n_attrs;
+        const bool f32 = out_f32;
+        if (splits > 1) {
+            e = cudaLaunchKernelEx(&cfg, f32 ? w8::lg_attn_hd64_fwd<true, true> : w8::lg_attn_hd64_fwd<false, true>, tm_q, tm_k,
+                                   tm_v, o, n_q, n_kv, tiles_m, splits, flags, ol LG_TRACE_SEQ);
+        } else {
+            e = cudaLaunchKernelEx(&cfg, f32 ? w8::lg_attn_hd64_fwd<true, false> : w8::lg_attn_hd64_fwd<false, false>, tm_q, tm_k,
+                                   tm_v, o, n_q, n_kv, tiles_m, splits, flags, ol LG_TRACE_SEQ);
+        }
+    }
+    if (e != cudaSuccess) return static_cast<int>(e);
+    return static_cast<int>(cudaGetLastError());
+}
+
 extern "C" {
 
 int lg_attn_version(void) { return kAbiVersion; }
@@ -190,7 +291,6 @@ int lg_attn_hd64_launch(const void* q, const void* k, const void* v, void* o, in
     if (rc != 0) return rc;
 
     const int bh = static_cast<int>(bh_ll);
-    const int tiles_m = static_cast<int>(tiles_m_ll);
     const void* qh = q;
     const void* kh = k;
     const void* vh = v;
@@ -228,76 +328,33 @@ int lg_attn_hd64_launch(const void* q, const void* k, const void* v, void* o, in
         vh = vd;
     }
 
-    CUtensorMap tm_q, tm_k, tm_v;
-    if ((rc = encode_rows_map(&tm_q, qh, n_q, bh)) != 0) return rc;
-    if ((rc = encode_rows_map(&tm_k, kh, n_kv, bh)) != 0) return rc;
-    if ((rc = encode_rows_map(&tm_v, vh, n_kv, bh)) != 0) return rc;
+    const RowStrides cq = contiguous_strides(heads, n_q), ckv = contiguous_strides(heads, n_kv);
+    return launch_core(qh, kh, vh, o, batch, heads, n_q, n_kv, io_dtype != LG_ATTN_F16_F16, cq, ckv, ckv, cq, device,
+                       stream);
+}
 
-    // Two kernels (see their headers): full grids take the 4-softmax-warp kernel (best sustained
-    // throughput); grids that cannot fill the GPU take the 8-softmax-warp kernel, which splits each
-    // Q tile's KV range over a cluster of `splits` CTAs (DSMEM combine) and uses programmatic
-    // dependent launch so its prologue overlaps the previous kernel's tail.  splits = the largest
-    // power of two <= min(8, KV tiles) whose clusters are all co-resident (one wave), from
-    // cudaOccupancyMaxActiveClusters at device init (B200: 74 / 33 / 15 clusters of 2 / 4 / 8).
-    const int kv_tiles = (n_kv + kBlockN - 1) / kBlockN;
-    const long long base = bh_ll * tiles_m_ll;
-    const int forced = g_forced_splits.load(std::memory_order_relaxed);
-    const bool full_grid = base >= 2LL * g_sm_count[device] && forced == 0;
-
-    cudaLaunchConfig_t cfg = {};
-    cfg.stream = stream;
-    cudaLaunchAttribute attrs[2];
-    unsigned n_attrs = 0;
-    if (full_grid) {
-        cfg.gridDim = dim3(static_cast<unsigned>(base));
-        cfg.blockDim = dim3(w4::kThreads);
-        cfg.dynamicSmemBytes = w4::kSmemBytes;
-        cfg.attrs = attrs;
-        cfg.numAttrs = 0;
-        e = cudaLaunchKernelEx(&cfg, io_dtype == LG_ATTN_F16_F16 ? w4::lg_attn_hd64_fwd<false> : w4::lg_attn_hd64_fwd<true>, tm_q,
-                               tm_k, tm_v, o, n_q, n_kv, tiles_m);
-    } else {
-        int splits = 1;
-        if (forced > 0) {
-            splits = forced;
-        } else if (base < g_sm_count[device]) {
-            for (int lg = 1; lg <= 3; ++lg)
-                if ((1 << lg) <= kv_tiles && base <= g_max_clusters[device][lg]) splits = 1 << lg;
-        }
-        while (splits > 1 && splits > kv_tiles) splits /= 2;
-        if (base * splits > 2147483647LL) return LG_ATTN_EINVAL;
-        int flags = 0;
-        if (base * splits <= 2LL * g_sm_count[device]) flags |= w8::kFlagEarlyTrigger;
-        cfg.gridDim = dim3(static_cast<unsigned>(base) * static_cast<unsigned>(splits));
-        cfg.blockDim = dim3(w8::kThreads);
-        cfg.dynamicSmemBytes = w8::kSmemBytes + (splits > 1 ? w8::kSmemSplitExtra : 0);
-        if (splits > 1) {
-            attrs[n_attrs].id = cudaLaunchAttributeClusterDimension;
-            attrs[n_attrs].val.clusterDim.x = static_cast<unsigned>(splits);
-            attrs[n_attrs].val.clusterDim.y = 1;
-            attrs[n_attrs].val.clusterDim.z = 1;
-            ++n_attrs;
-        }
-        if (g_use_pdl.load(std::memory_order_relaxed)) {
-            // this kernel's prologue may overlap the previous kernel's tail (it still waits, at
-            // griddepcontrol.wait, for that kernel to complete before touching memory)
-            attrs[n_attrs].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-            attrs[n_attrs].val.programmaticStreamSerializationAllowed = 1;
-            ++n_attrs;
-        }
-        cfg.attrs = attrs;
-        cfg.numAttrs = n_attrs;
-        const bool f32 = io_dtype != LG_ATTN_F16_F16;
-        if (splits > 1) {
-            e = cudaLaunchKernelEx(&cfg, f32 ? w8::lg_attn_hd64_fwd<true, true> : w8::lg_attn_hd64_fwd<false, true>, tm_q, tm_k,
-                                   tm_v, o, n_q, n_kv, tiles_m, splits, flags LG_TRACE_SEQ);
-        } else {
-            e = cudaLaunchKernelEx(&cfg, f32 ? w8::lg_attn_hd64_fwd<true, false> : w8::lg_attn_hd64_fwd<false, false>, tm_q, tm_k,
-                                   tm_v, o, n_q, n_kv, tiles_m, splits, flags LG_TRACE_SEQ);
-        }
-    }
+int lg_attn_hd64_launch_strided(const void* q, const void* k, const void* v, void* o, int batch, int heads,
+                                int n_q, int n_kv, int out_f32, const lg_attn_strides* sq, const lg_attn_strides* sk,
+                                const lg_attn_strides* sv, const lg_attn_strides* so, void* stream_v) {
+    if (q == nullptr || k == nullptr || v == nullptr || o == nullptr) return LG_ATTN_EINVAL;
+    if (sq == nullptr || sk == nullptr || sv == nullptr || so == nullptr) return LG_ATTN_EINVAL;
+    if (batch <= 0 || heads <= 0 || n_q <= 0 || n_kv <= 0 || (out_f32 != 0 && out_f32 != 1)) return LG_ATTN_EINVAL;
+    const long long tiles = (static_cast<long long>(n_q) + kBlockM - 1) / kBlockM;
+    if (static_cast<long long>(batch) * heads * tiles > 2147483647LL) return LG_ATTN_EINVAL;
+    const RowStrides rq{sq->batch, sq->head, sq->row}, rk{sk->batch, sk->head, sk->row};
+    const RowStrides rv{sv->batch, sv->head, sv->row}, ro{so->batch, so->head, so->row};
+    auto aligned16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; };
+    if (!aligned16(q) || !aligned16(k) || !aligned16(v) || !aligned16(o)) return LG_ATTN_EINVAL;
+    if (!strides_ok(rq, batch, heads, n_q, 2) || !strides_ok(rk, batch, heads, n_kv, 2) ||
+        !strides_ok(rv, batch, heads, n_kv, 2) || !strides_ok(ro, batch, heads, n_q, out_f32 ? 4 : 2))
+        return LG_ATTN_EINVAL;
+    int device = 0;
+    cudaError_t e = cudaGetDevice(&device);
     if (e != cudaSuccess) return static_cast<int>(e);
-    return static_cast<int>(cudaGetLastError());
+    int rc = lg_attn_hd64_init_device(device);
+    if (rc != 0) return rc;
+    return launch_core(q, k, v, o, batch, heads, n_q, n_kv, out_f32 != 0, rq, rk, rv, ro, device,
+                       static_cast<cudaStream_t>(stream_v));
 }
 
 int lg_attn_hd64_run_host(const void* q_host, const void* k_host, const void* v_host, void* o_host,

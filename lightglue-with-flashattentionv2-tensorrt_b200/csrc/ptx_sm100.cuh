@@ -86,6 +86,17 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst_smem, const void* tmap,
         : "memory");
 }
 
+// 4-D tiled load (64, rows, heads, batch): lets Q/K/V live in any strided [batch, rows, heads, 64] /
+// [batch, heads, rows, 64] buffer (packed projections) without a layout copy.
+__device__ __forceinline__ void tma_load_4d(uint32_t dst_smem, const void* tmap, uint32_t bar,
+                                            int c0, int c1, int c2, int c3) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes "
+        "[%0], [%1, {%3, %4, %5, %6}], [%2];"
+        ::"r"(dst_smem), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+        : "memory");
+}
+
 // ----------------------------------------------------------------------------- tcgen05
 template <int kCols>
 __device__ __forceinline__ void tmem_alloc(uint32_t dst_smem) {

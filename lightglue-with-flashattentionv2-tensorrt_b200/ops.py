@@ -66,6 +66,36 @@ def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, out_dtype: torc
     return out
 
 
+def _bhr_strides(t: torch.Tensor) -> "B.Strides":
+    return B.Strides(t.stride(0), t.stride(1), t.stride(2))
+
+
+def attention_strided(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
+    """Same attention on FP16 ``[B,H,rows,64]`` VIEWS with arbitrary batch / head / row strides
+    (``lg_attn_hd64_launch_strided``): Q/K/V may point into packed projection outputs and ``out``
+    (FP16 or FP32) into the buffer the next GEMM reads, so the head-split transposes and
+    ``.contiguous()`` copies around every call in the reference (``lightglue.py:139-147,190-199``)
+    disappear.  The last dimension must be contiguous; strides multiples of 16 bytes."""
+    for t in (q, k, v, out):
+        if not t.is_cuda:
+            raise RuntimeError("lg_attn: tensors must live on a CUDA device (no CPU fallback)")
+        if t.dim() != 4 or t.shape[-1] != HEAD_DIM or t.stride(-1) != 1:
+            raise ValueError("lg_attn: expected [B,H,rows,64] views with a contiguous last dimension")
+    if not (q.dtype == k.dtype == v.dtype == torch.float16) or out.dtype not in (torch.float16, torch.float32):
+        raise TypeError("lg_attn: strided entry takes FP16 q,k,v and an FP16 or FP32 out")
+    b, h, n, _ = q.shape
+    m = k.shape[2]
+    if k.shape != v.shape or tuple(k.shape[:2]) != (b, h) or tuple(out.shape) != (b, h, n, HEAD_DIM):
+        raise ValueError("lg_attn: shape mismatch")
+    sq, sk, sv, so = (_bhr_strides(t) for t in (q, k, v, out))
+    with torch.cuda.device(q.device):
+        stream = torch.cuda.current_stream(q.device).cuda_stream
+        rc = B.load().lg_attn_hd64_launch_strided(q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(),
+                                                  b, h, n, m, int(out.dtype == torch.float32), sq, sk, sv, so, stream)
+    B.check(rc, "lg_attn_hd64_launch_strided")
+    return out
+
+
 def attention_host(q, k, v, out_dtype=None, device: int = 0):
     """Host-buffer entry (numpy arrays in, numpy array out) through ``lg_attn_hd64_run_host``."""
     import numpy as np

@@ -259,3 +259,45 @@ def test_against_recompiled_reference_kernels(pkg):
         print(f"N={n} M={m} float={is_float}: reference-kernel max_abs={e_ref:.2e}, new kernel max_abs={e_new:.2e}")
         assert e_new <= orc.TOL_F16_MAX_ABS
         assert orc.max_abs_err(o_new.float().cpu().numpy(), o_ref.float().cpu().numpy()) <= 2 * orc.TOL_F16_MAX_ABS + e_ref
+
+
+# ------------------------------------------------------------------------------------------------
+# strided entry (lg_attn_hd64_launch_strided): packed projection buffers in, next GEMM's buffer out
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("b,n,m", [(1, 1024, 1024), (1, 300, 333), (3, 129, 65), (40, 256, 250), (2, 1, 1)])
+@pytest.mark.parametrize("out_dtype", [torch.float16, torch.float32])
+def test_strided_views_match_contiguous(pkg, b, n, m, out_dtype):
+    """Q from a packed [B,N,3*256] projection (reference layout lightglue.py:139-142 after a weight
+    permutation), K/V from another image's packed buffer, O written head-interleaved into the right
+    half of a [B,N,512] buffer.  Must be bit-identical to the contiguous launcher on the same values."""
+    g = torch.Generator(device="cpu").manual_seed(b * 1000 + n + m)
+    pq = torch.randn(b, n, 3 * 256, generator=g).half().to(DEV)
+    pkv = torch.randn(b, m, 3 * 256, generator=g).half().to(DEV)
+    q = pq[..., 0:256].unflatten(-1, (4, 64)).transpose(1, 2)          # [B,4,N,64] view
+    k = pkv[..., 256:512].unflatten(-1, (4, 64)).transpose(1, 2)
+    v = pkv[..., 512:768].unflatten(-1, (4, 64)).transpose(1, 2)
+    assert not q.is_contiguous() or n == 1
+    obuf = torch.full((b, n, 512), 7.0, dtype=out_dtype, device=DEV)
+    o = obuf[..., 256:].unflatten(-1, (4, 64)).transpose(1, 2)
+    pkg.attention_strided(q, k, v, o)
+    ref = pkg.attention(q.contiguous(), k.contiguous(), v.contiguous(), out_dtype=out_dtype)
+    assert torch.equal(o, ref)
+    assert torch.all(obuf[..., :256] == 7.0)  # the left half (the residual stream) is untouched
+    orc_ref = orc.attention_np(*(t.contiguous().cpu().numpy() for t in (q, k, v)))
+    if out_dtype == torch.float16:
+        assert orc.max_abs_err(o.float().cpu().numpy(), orc_ref) <= orc.TOL_F16_MAX_ABS
+    else:
+        assert orc.rel_err(o.contiguous().cpu().numpy(), orc_ref) <= orc.TOL_F32_REL
+
+
+def test_strided_rejects_bad_layouts(pkg):
+    q = torch.zeros(1, 4, 16, 64, dtype=torch.float16, device=DEV)
+    o = torch.zeros(1, 4, 16, 64, dtype=torch.float16, device=DEV)
+    bad = torch.zeros(1, 4, 16, 68, dtype=torch.float16, device=DEV)[..., :64]  # row stride 136 B: not 16-B aligned
+    with pytest.raises(pkg.LgAttnError) as ei:
+        pkg.attention_strided(bad, q, q, o)
+    assert ei.value.code == 100001
+    with pytest.raises(TypeError):
+        pkg.attention_strided(q.float(), q.float(), q.float(), o)
+    with pytest.raises(RuntimeError):
+        pkg.attention_strided(q.cpu(), q.cpu(), q.cpu(), o.cpu())
