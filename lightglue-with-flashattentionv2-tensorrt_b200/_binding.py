@@ -42,6 +42,15 @@ C_ABI_SYMBOLS = (
     "lg_attn_session_sync",
     "lg_attn_session_destroy",
 )
+# every symbol include/lg_match.h declares
+MATCH_ABI_SYMBOLS = (
+    "lg_match_posenc",
+    "lg_match_rotary",
+    "lg_match_layernorm_gelu",
+    "lg_match_assign_workspace_bytes",
+    "lg_match_assign",
+    "lg_match_assign_launches",
+)
 
 _lib = None
 
@@ -110,6 +119,19 @@ def load() -> ctypes.CDLL:
     lib.lg_attn_session_sync.argtypes = [ctypes.c_void_p]
     lib.lg_attn_session_destroy.restype = None
     lib.lg_attn_session_destroy.argtypes = [ctypes.c_void_p]
+    P, LL, I, F = ctypes.c_void_p, ctypes.c_longlong, ctypes.c_int, ctypes.c_float
+    lib.lg_match_posenc.restype = I
+    lib.lg_match_posenc.argtypes = [P, P, P, LL, P]
+    lib.lg_match_rotary.restype = I
+    lib.lg_match_rotary.argtypes = [P, LL, I, I, P, P]
+    lib.lg_match_layernorm_gelu.restype = I
+    lib.lg_match_layernorm_gelu.argtypes = [P, LL, I, P, P, F, P]
+    lib.lg_match_assign_workspace_bytes.restype = ctypes.c_size_t
+    lib.lg_match_assign_workspace_bytes.argtypes = [I, I, I]
+    lib.lg_match_assign.restype = I
+    lib.lg_match_assign.argtypes = [P, P, P, LL, I, I, I, F, P, P, P, P, ctypes.c_size_t, P]
+    lib.lg_match_assign_launches.restype = I
+    lib.lg_match_assign_launches.argtypes = [I]
     _lib = lib
     return lib
 

@@ -1,0 +1,398 @@
+// Memory-bound glue either side of the attention hot path (C-ABI in include/lg_match.h).
+//
+// HBM-bound elementwise / reduction work: no tensor cores, 128-bit coalesced accesses, grids sized
+// in multiples of the SM count (grid-stride where the row count is large), FP32 arithmetic on FP16
+// storage.  Each kernel replaces a run of eager / TensorRT elementwise launches of the reference
+// (file:line under /root/reference/lightglue_pytorch_with_plugin/):
+//   posenc_kernel           lightglue.py:77-86    Wr(x) -> cos / sin
+//   rotary_kernel           lightglue.py:143-144, 154-165   rotate_half + cached rotary on q, k
+//   layernorm_gelu_kernel   lightglue.py:131-136 (ffn[1], ffn[2])
+//   assignment kernels      lightglue.py:216-224 (sigmoid_log_double_softmax), :253-276 (filter_matches)
+
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdint.h>
+
+#include "../../include/lg_attn.h"
+#include "../../include/lg_match.h"
+
+namespace {
+
+constexpr int kSMs = 148;
+constexpr int kFfnCols = 512;   // 2 * embed_dim (lightglue.py:131)
+constexpr int kAngles = 32;     // head_dim / 2
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// ------------------------------------------------------------------------------------------ posenc
+__global__ void __launch_bounds__(256) posenc_kernel(const float2* __restrict__ kpts, const float2* __restrict__ wr,
+                                                     float2* __restrict__ cs, long long total) {
+    for (long long t = blockIdx.x * 256LL + threadIdx.x; t < total; t += gridDim.x * 256LL) {
+        const long long r = t >> 5;
+        const int i = static_cast<int>(t & 31);
+        const float2 p = kpts[r];
+        const float2 w = wr[i];
+        const float a = fmaf(p.y, w.y, p.x * w.x);
+        float s, c;
+        sincosf(a, &s, &c);
+        cs[t] = make_float2(c, s);
+    }
+}
+
+// ------------------------------------------------------------------------------------------ rotary
+// One thread = 8 halves (4 rotary pairs) of one head of one block of one row.
+__global__ void __launch_bounds__(256) rotary_kernel(__half* __restrict__ buf, long long rows, int ld, int chunks_per_row,
+                                                     const float4* __restrict__ cs) {
+    const long long total = rows * chunks_per_row;
+    for (long long t = blockIdx.x * 256LL + threadIdx.x; t < total; t += gridDim.x * 256LL) {
+        const long long r = t / chunks_per_row;
+        const int c = static_cast<int>(t - r * chunks_per_row);  // 16-byte chunk inside the row's rotary span
+        const int a4 = c & 7;                                    // which 4 angles (chunk inside the 64-wide head)
+        uint4* p = reinterpret_cast<uint4*>(buf + r * ld) + c;
+        uint4 v = *p;
+        const float4 cs0 = cs[(r * kAngles + a4 * 4) / 2];      // (cos0, sin0, cos1, sin1)
+        const float4 cs1 = cs[(r * kAngles + a4 * 4) / 2 + 1];  // (cos2, sin2, cos3, sin3)
+        auto rot = [](uint32_t w, float co, float si) {
+            const float2 ab = __half22float2(*reinterpret_cast<const __half2*>(&w));
+            const __half2 o = __floats2half2_rn(fmaf(ab.x, co, -ab.y * si), fmaf(ab.y, co, ab.x * si));
+            return *reinterpret_cast<const uint32_t*>(&o);
+        };
+        v.x = rot(v.x, cs0.x, cs0.y);
+        v.y = rot(v.y, cs0.z, cs0.w);
+        v.z = rot(v.z, cs1.x, cs1.y);
+        v.w = rot(v.w, cs1.z, cs1.w);
+        *p = v;
+    }
+}
+
+// ------------------------------------------------------------------------------------------ LN + GELU
+// erf by Abramowitz–Stegun 7.1.26 (|err| <= 1.5e-7, far below FP16 output resolution)
+__device__ __forceinline__ float gelu_erf(float x) {
+    const float z = fabsf(x) * 0.70710678118654752f;
+    const float t = __frcp_rn(fmaf(0.3275911f, z, 1.0f));
+    float p = fmaf(1.061405429f, t, -1.453152027f);
+    p = fmaf(p, t, 1.421413741f);
+    p = fmaf(p, t, -0.284496736f);
+    p = fmaf(p, t, 0.254829592f);
+    const float erf_abs = 1.0f - p * t * __expf(-z * z);
+    const float erf_v = copysignf(erf_abs, x);
+    return 0.5f * x * (1.0f + erf_v);
+}
+
+// One warp per row of 512: lane owns columns [8*lane, 8*lane+8) and [256 + 8*lane, ...).
+__global__ void __launch_bounds__(256) layernorm_gelu_kernel(__half* __restrict__ h, long long rows, int ld,
+                                                             const float* __restrict__ gamma,
+                                                             const float* __restrict__ beta, float eps) {
+    const int lane = threadIdx.x & 31;
+    const long long warp0 = blockIdx.x * 8LL + (threadIdx.x >> 5);
+    float g[16], b[16];
+#pragma unroll
+    for (int half_i = 0; half_i < 2; ++half_i) {
+        const float4* gp = reinterpret_cast<const float4*>(gamma + half_i * 256 + lane * 8);
+        const float4* bp = reinterpret_cast<const float4*>(beta + half_i * 256 + lane * 8);
+        const float4 g0 = gp[0], g1 = gp[1], b0 = bp[0], b1 = bp[1];
+        g[8 * half_i + 0] = g0.x; g[8 * half_i + 1] = g0.y; g[8 * half_i + 2] = g0.z; g[8 * half_i + 3] = g0.w;
+        g[8 * half_i + 4] = g1.x; g[8 * half_i + 5] = g1.y; g[8 * half_i + 6] = g1.z; g[8 * half_i + 7] = g1.w;
+        b[8 * half_i + 0] = b0.x; b[8 * half_i + 1] = b0.y; b[8 * half_i + 2] = b0.z; b[8 * half_i + 3] = b0.w;
+        b[8 * half_i + 4] = b1.x; b[8 * half_i + 5] = b1.y; b[8 * half_i + 6] = b1.z; b[8 * half_i + 7] = b1.w;
+    }
+    for (long long r = warp0; r < rows; r += gridDim.x * 8LL) {
+        uint4* p = reinterpret_cast<uint4*>(h + r * ld);
+        uint4 raw[2] = {p[lane], p[32 + lane]};
+        float x[16];
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            const __half2* hp = reinterpret_cast<const __half2*>(&raw[i]);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const float2 f = __half22float2(hp[e]);
+                x[8 * i + 2 * e] = f.x;
+                x[8 * i + 2 * e + 1] = f.y;
+            }
+        }
+        float s = 0.f;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) s += x[i];
+        const float mean = warp_sum(s) * (1.0f / kFfnCols);
+        float q = 0.f;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const float d = x[i] - mean;
+            q = fmaf(d, d, q);
+        }
+        const float rstd = rsqrtf(warp_sum(q) * (1.0f / kFfnCols) + eps);
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            __half2* hp = reinterpret_cast<__half2*>(&raw[i]);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const int k = 8 * i + 2 * e;
+                const float y0 = gelu_erf(fmaf((x[k] - mean) * rstd, g[k], b[k]));
+                const float y1 = gelu_erf(fmaf((x[k + 1] - mean) * rstd, g[k + 1], b[k + 1]));
+                hp[e] = __floats2half2_rn(y0, y1);
+            }
+        }
+        p[lane] = raw[0];
+        p[32 + lane] = raw[1];
+    }
+}
+
+// ------------------------------------------------------------------------------------------ assignment
+__device__ __forceinline__ float log_sigmoid(float z) { return fminf(z, 0.f) - log1pf(expf(-fabsf(z))); }
+
+// (max, sum exp(x - max)) online merge
+__device__ __forceinline__ void lse_merge(float& m, float& s, float m2, float s2) {
+    const float mn = fmaxf(m, m2);
+    if (mn == -INFINITY) { m = mn; s = 0.f; return; }
+    s = s * expf(m - mn) + s2 * expf(m2 - mn);
+    m = mn;
+}
+
+// row_lse[b, i] = logsumexp_j sim[b, i, j]; also lsz (log-sigmoid of the matchability logits).  Warp per row.
+__global__ void __launch_bounds__(256) row_lse_kernel(const float* __restrict__ sim, long long rows, int n1,
+                                                      float* __restrict__ row_lse) {
+    const int lane = threadIdx.x & 31;
+    for (long long r = blockIdx.x * 8LL + (threadIdx.x >> 5); r < rows; r += gridDim.x * 8LL) {
+        const float* p = sim + r * n1;
+        float m = -INFINITY, s = 0.f;
+        for (int j = lane; j < n1; j += 32) {
+            const float x = p[j];
+            if (x > m) { s = s * expf(m - x) + 1.f; m = x; } else { s += expf(x - m); }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float m2 = __shfl_xor_sync(0xffffffffu, m, o), s2 = __shfl_xor_sync(0xffffffffu, s, o);
+            lse_merge(m, s, m2, s2);
+        }
+        if (lane == 0) row_lse[r] = m + logf(s);
+    }
+}
+
+// Column pass over one pair: block = 32 column lanes x 8 row groups; grid (ceil(n1/32), batch).
+// MODE 0: col_lse[b, j] = logsumexp_i sim[b, i, j]
+// MODE 1: best row per column of  2 sim[i,j] - row_lse[i] + lsz0[i]  ->  m1[b, j]
+template <int MODE>
+__global__ void __launch_bounds__(256) col_pass_kernel(const float* __restrict__ sim, int n0, int n1,
+                                                       const float* __restrict__ row_term, float* __restrict__ col_lse,
+                                                       int* __restrict__ m1) {
+    __shared__ float sh_a[8][33];
+    __shared__ float sh_b[8][33];
+    const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
+    const int b = blockIdx.y;
+    const int j = blockIdx.x * 32 + cx;
+    const float* p = sim + static_cast<long long>(b) * n0 * n1;
+    const float* rt = row_term + static_cast<long long>(b) * n0;
+    float m = -INFINITY, s = 0.f;  // MODE 1: m = best value, s = best index (as int bits)
+    int best = 0x7fffffff;
+    if (j < n1) {
+        for (int i = ry; i < n0; i += 8) {
+            const float x = p[static_cast<long long>(i) * n1 + j];
+            if (MODE == 0) {
+                if (x > m) { s = s * expf(m - x) + 1.f; m = x; } else { s += expf(x - m); }
+            } else {
+                const float v = 2.f * x + rt[i];
+                if (v > m) { m = v; best = i; }
+            }
+        }
+    }
+    sh_a[ry][cx] = m;
+    sh_b[ry][cx] = MODE == 0 ? s : __int_as_float(best);
+    __syncthreads();
+    if (ry == 0 && j < n1) {
+        if (MODE == 0) {
+            for (int g = 1; g < 8; ++g) lse_merge(m, s, sh_a[g][cx], sh_b[g][cx]);
+            col_lse[static_cast<long long>(b) * n1 + j] = m + logf(s);
+        } else {
+            for (int g = 1; g < 8; ++g) {
+                const float v = sh_a[g][cx];
+                const int bi = __float_as_int(sh_b[g][cx]);
+                if (v > m || (v == m && bi < best)) { m = v; best = bi; }
+            }
+            m1[static_cast<long long>(b) * n1 + j] = best;
+        }
+    }
+}
+
+// lsz[k] = logsigmoid(z[k * stride]) for both images; row_term[b,i] = lsz0 - row_lse; col_term[b,j] = lsz1 - col_lse
+__global__ void __launch_bounds__(256) terms_kernel(const __half* __restrict__ z, long long z_stride, long long count,
+                                                    const float* __restrict__ lse, float* __restrict__ term) {
+    for (long long t = blockIdx.x * 256LL + threadIdx.x; t < count; t += gridDim.x * 256LL)
+        term[t] = log_sigmoid(__half2float(z[t * z_stride])) - lse[t];
+}
+
+// Warp per row: best column of 2 sim[i,j] + col_term[j]; score0 = that + row_term[i].
+__global__ void __launch_bounds__(256) row_best_kernel(const float* __restrict__ sim, int batch, int n0, int n1,
+                                                       const float* __restrict__ row_term,
+                                                       const float* __restrict__ col_term, int* __restrict__ m0,
+                                                       float* __restrict__ score0) {
+    const int lane = threadIdx.x & 31;
+    const long long rows = static_cast<long long>(batch) * n0;
+    for (long long r = blockIdx.x * 8LL + (threadIdx.x >> 5); r < rows; r += gridDim.x * 8LL) {
+        const long long b = r / n0;
+        const float* p = sim + r * n1;
+        const float* ct = col_term + b * n1;
+        float best = -INFINITY;
+        int bj = 0x7fffffff;
+        for (int j = lane; j < n1; j += 32) {
+            const float v = 2.f * p[j] + ct[j];
+            if (v > best) { best = v; bj = j; }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float v2 = __shfl_xor_sync(0xffffffffu, best, o);
+            const int j2 = __shfl_xor_sync(0xffffffffu, bj, o);
+            if (v2 > best || (v2 == best && j2 < bj)) { best = v2; bj = j2; }
+        }
+        if (lane == 0) {
+            m0[r] = bj;
+            score0[r] = best + row_term[r];
+        }
+    }
+}
+
+// filter_matches (lightglue.py:253-276): mutual check, exp, threshold.
+__global__ void __launch_bounds__(256) mutual_kernel(const int* __restrict__ m0, const int* __restrict__ m1,
+                                                     const float* __restrict__ score0, int batch, int n0, int n1,
+                                                     float threshold, int* __restrict__ matches0,
+                                                     float* __restrict__ mscores0) {
+    const long long rows = static_cast<long long>(batch) * n0;
+    for (long long r = blockIdx.x * 256LL + threadIdx.x; r < rows; r += gridDim.x * 256LL) {
+        const long long b = r / n0;
+        const int i = static_cast<int>(r - b * n0);
+        const int j = m0[r];
+        const bool mutual = m1[b * n1 + j] == i;
+        const float ms = mutual ? expf(score0[r]) : 0.f;
+        mscores0[r] = ms;
+        matches0[r] = ms > threshold ? j : -1;
+    }
+}
+
+// scores[b,i,j] = 2 sim - row_lse_i - col_lse_j + lsz0_i + lsz1_j  (lightglue.py:216-224)
+__global__ void __launch_bounds__(256) scores_kernel(const float4* __restrict__ sim, long long rows, int n0, int n1,
+                                                     const float* __restrict__ row_term,
+                                                     const float* __restrict__ col_term, float4* __restrict__ scores) {
+    const int q = n1 >> 2;  // n1 % 4 == 0 on this path
+    const long long total = rows * q;
+    for (long long t = blockIdx.x * 256LL + threadIdx.x; t < total; t += gridDim.x * 256LL) {
+        const long long r = t / q;
+        const int j4 = static_cast<int>(t - r * q);
+        const long long b = r / n0;
+        const float4 x = sim[t];
+        const float4 c = reinterpret_cast<const float4*>(col_term + b * n1)[j4];
+        const float rt = row_term[r];
+        scores[t] = make_float4(2.f * x.x + rt + c.x, 2.f * x.y + rt + c.y, 2.f * x.z + rt + c.z, 2.f * x.w + rt + c.w);
+    }
+}
+__global__ void __launch_bounds__(256) scores_kernel_scalar(const float* __restrict__ sim, long long rows, int n0, int n1,
+                                                            const float* __restrict__ row_term,
+                                                            const float* __restrict__ col_term,
+                                                            float* __restrict__ scores) {
+    const long long total = rows * n1;
+    for (long long t = blockIdx.x * 256LL + threadIdx.x; t < total; t += gridDim.x * 256LL) {
+        const long long r = t / n1;
+        const int j = static_cast<int>(t - r * n1);
+        const long long b = r / n0;
+        scores[t] = 2.f * sim[t] + row_term[r] + col_term[b * n1 + j];
+    }
+}
+
+unsigned grid_for(long long work_items, int per_block, int waves = 8) {
+    long long blocks = (work_items + per_block - 1) / per_block;
+    const long long cap = static_cast<long long>(kSMs) * waves;  // grid-stride beyond `waves` CTAs per SM
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    return static_cast<unsigned>(blocks);
+}
+
+size_t align256(size_t x) { return (x + 255) & ~static_cast<size_t>(255); }
+
+int last_error() { return static_cast<int>(cudaGetLastError()); }
+
+}  // namespace
+
+extern "C" {
+
+int lg_match_posenc(const float* kpts, const float* wr, float* cs, long long rows, void* stream) {
+    if (kpts == nullptr || wr == nullptr || cs == nullptr || rows <= 0) return LG_ATTN_EINVAL;
+    const long long total = rows * kAngles;
+    posenc_kernel<<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        reinterpret_cast<const float2*>(kpts), reinterpret_cast<const float2*>(wr), reinterpret_cast<float2*>(cs), total);
+    return last_error();
+}
+
+int lg_match_rotary(void* packed_half, long long rows, int ld, int n_blocks, const float* cs, void* stream) {
+    if (packed_half == nullptr || cs == nullptr || rows <= 0 || n_blocks <= 0) return LG_ATTN_EINVAL;
+    if (ld < n_blocks * 256 || (ld & 7) != 0 || (reinterpret_cast<uintptr_t>(packed_half) & 15u) != 0) return LG_ATTN_EINVAL;
+    const int chunks = n_blocks * 32;  // 16-byte chunks per row that carry rotary data
+    rotary_kernel<<<grid_for(rows * chunks, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<__half*>(packed_half), rows, ld, chunks, reinterpret_cast<const float4*>(cs));
+    return last_error();
+}
+
+int lg_match_layernorm_gelu(void* h_half, long long rows, int ld, const float* gamma, const float* beta, float eps,
+                            void* stream) {
+    if (h_half == nullptr || gamma == nullptr || beta == nullptr || rows <= 0) return LG_ATTN_EINVAL;
+    if (ld < kFfnCols || (ld & 7) != 0 || (reinterpret_cast<uintptr_t>(h_half) & 15u) != 0) return LG_ATTN_EINVAL;
+    layernorm_gelu_kernel<<<grid_for(rows, 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<__half*>(h_half), rows, ld, gamma, beta, eps);
+    return last_error();
+}
+
+size_t lg_match_assign_workspace_bytes(int batch, int n0, int n1) {
+    if (batch <= 0 || n0 <= 0 || n1 <= 0) return 0;
+    const size_t r0 = align256(static_cast<size_t>(batch) * n0 * 4), r1 = align256(static_cast<size_t>(batch) * n1 * 4);
+    return 4 * r0 + 3 * r1;  // row_lse, row_term, m0, score0 | col_lse, col_term, m1
+}
+
+int lg_match_assign_launches(int with_scores) { return with_scores ? 8 : 7; }
+
+int lg_match_assign(const float* sim, const void* z0_half, const void* z1_half, long long z_stride, int batch, int n0,
+                    int n1, float threshold, int* matches0, float* mscores0, float* scores, void* workspace,
+                    size_t workspace_bytes, void* stream_v) {
+    if (sim == nullptr || z0_half == nullptr || z1_half == nullptr || matches0 == nullptr || mscores0 == nullptr)
+        return LG_ATTN_EINVAL;
+    if (batch <= 0 || n0 <= 0 || n1 <= 0 || z_stride <= 0 || batch > 65535) return LG_ATTN_EINVAL;
+    if (workspace == nullptr || workspace_bytes < lg_match_assign_workspace_bytes(batch, n0, n1)) return LG_ATTN_EWORKSPACE;
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+    const long long rows0 = static_cast<long long>(batch) * n0, rows1 = static_cast<long long>(batch) * n1;
+    const size_t r0 = align256(static_cast<size_t>(rows0) * 4), r1 = align256(static_cast<size_t>(rows1) * 4);
+    uint8_t* ws = static_cast<uint8_t*>(workspace);
+    float* row_lse = reinterpret_cast<float*>(ws);
+    float* row_term = reinterpret_cast<float*>(ws + r0);
+    int* m0 = reinterpret_cast<int*>(ws + 2 * r0);
+    float* score0 = reinterpret_cast<float*>(ws + 3 * r0);
+    float* col_lse = reinterpret_cast<float*>(ws + 4 * r0);
+    float* col_term = reinterpret_cast<float*>(ws + 4 * r0 + r1);
+    int* m1 = reinterpret_cast<int*>(ws + 4 * r0 + 2 * r1);
+    const dim3 col_grid(static_cast<unsigned>((n1 + 31) / 32), static_cast<unsigned>(batch));
+
+    row_lse_kernel<<<grid_for(rows0, 8), 256, 0, stream>>>(sim, rows0, n1, row_lse);
+    col_pass_kernel<0><<<col_grid, 256, 0, stream>>>(sim, n0, n1, row_lse, col_lse, nullptr);
+    terms_kernel<<<grid_for(rows0, 256), 256, 0, stream>>>(static_cast<const __half*>(z0_half), z_stride, rows0, row_lse,
+                                                           row_term);
+    terms_kernel<<<grid_for(rows1, 256), 256, 0, stream>>>(static_cast<const __half*>(z1_half), z_stride, rows1, col_lse,
+                                                           col_term);
+    row_best_kernel<<<grid_for(rows0, 8), 256, 0, stream>>>(sim, batch, n0, n1, row_term, col_term, m0, score0);
+    col_pass_kernel<1><<<col_grid, 256, 0, stream>>>(sim, n0, n1, row_term, nullptr, m1);
+    mutual_kernel<<<grid_for(rows0, 256), 256, 0, stream>>>(m0, m1, score0, batch, n0, n1, threshold, matches0, mscores0);
+    if (scores != nullptr) {
+        if ((n1 & 3) == 0 && (reinterpret_cast<uintptr_t>(sim) & 15u) == 0 && (reinterpret_cast<uintptr_t>(scores) & 15u) == 0)
+            scores_kernel<<<grid_for(rows0 * (n1 >> 2), 256), 256, 0, stream>>>(
+                reinterpret_cast<const float4*>(sim), rows0, n0, n1, row_term, col_term, reinterpret_cast<float4*>(scores));
+        else
+            scores_kernel_scalar<<<grid_for(rows0 * n1, 256), 256, 0, stream>>>(sim, rows0, n0, n1, row_term, col_term, scores);
+    }
+    return last_error();
+}
+
+}  // extern "C"

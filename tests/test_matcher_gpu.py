@@ -1,0 +1,187 @@
+"""GPU parity tests of the pair matcher (the caller of the attention path) and its glue kernels,
+through the C-ABI of include/lg_match.h, against oracle/matcher_oracle.py and the fixture generated
+from the unmodified reference LightGlue (tests/golden/matcher_forward.npz).
+
+Tolerances: the matcher computes in FP16 storage / FP32 accumulate (like the reference's TensorRT
+FP16 engine, steps.txt:143), the fixture is the reference's FP32 eager model.  Stated bars:
+  * lightglue_scores: max-abs error <= 0.05 log-units and mean-abs <= 0.008 (scores span ~[-20, -5]);
+  * lightglue_descriptors: max-abs <= 0.006 relative to the descriptor max-abs;
+  * match set (mutual nearest neighbours, threshold 0): >= 95 % of the reference's matches reproduced,
+    and every disagreement must be a near-tie in the reference scores (gap < 0.1).
+"""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from oracle import matcher_oracle as mo
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+TOL_SCORES_MAX = 0.05
+TOL_SCORES_MEAN = 0.008
+TOL_DESC_REL = 0.006
+MIN_MATCH_AGREEMENT = 0.95
+
+
+# ------------------------------------------------------------------------------------------------ glue kernels
+@pytest.mark.parametrize("rows", [1, 77, 4096])
+def test_posenc_kernel(pkg, rows):
+    g = torch.Generator().manual_seed(rows)
+    kpts = (torch.rand(rows, 2, generator=g) * 2 - 1)
+    wr = torch.randn(32, 2, generator=g)
+    cs = pkg.matcher.posenc_table(kpts.to(DEV), wr.to(DEV)).cpu()
+    proj = kpts.double() @ wr.double().t()
+    assert float((cs[..., 0].double() - proj.cos()).abs().max()) < 2e-6
+    assert float((cs[..., 1].double() - proj.sin()).abs().max()) < 2e-6
+
+
+@pytest.mark.parametrize("rows,ld,blocks", [(1, 768, 2), (130, 768, 2), (1000, 512, 1), (257, 1024, 3)])
+def test_rotary_kernel_matches_oracle(pkg, rows, ld, blocks):
+    g = torch.Generator().manual_seed(rows + ld)
+    buf = torch.randn(rows, ld, generator=g).half()
+    kpts = torch.rand(1, rows, 2, generator=g) * 2 - 1
+    wr = torch.randn(32, 2, generator=g)
+    cs = pkg.matcher.posenc_table(kpts[0].to(DEV), wr.to(DEV))
+    out = pkg.matcher.rotary_(buf.clone().to(DEV), blocks, cs).cpu()
+    enc = mo.posenc(kpts.double(), wr.double())
+    for blk in range(blocks):
+        t = buf[:, blk * 256:(blk + 1) * 256].double().unflatten(-1, (4, 64)).transpose(0, 1)[None]
+        want = mo.rotary(t, enc)[0].transpose(0, 1).flatten(-2)
+        got = out[:, blk * 256:(blk + 1) * 256].double()
+        assert float((got - want).abs().max()) <= 2e-3  # FP16 rounding of values up to ~6
+        assert float((got - want.half().double()).abs().max()) <= 4e-3
+    assert torch.equal(out[:, blocks * 256:], buf[:, blocks * 256:])  # the rest of the row is untouched
+
+
+@pytest.mark.parametrize("rows,ld", [(1, 512), (9, 512), (1031, 512), (64, 640)])
+def test_layernorm_gelu_kernel(pkg, rows, ld):
+    g = torch.Generator().manual_seed(rows)
+    h = (torch.randn(rows, ld, generator=g) * 3 + 0.5).half()
+    gamma = torch.randn(512, generator=g)
+    beta = torch.randn(512, generator=g)
+    hd = h.clone().to(DEV)
+    pkg.matcher.layernorm_gelu_(hd[:, :512], gamma.to(DEV), beta.to(DEV))
+    want = F.gelu(F.layer_norm(h[:, :512].double(), (512,), gamma.double(), beta.double(), 1e-5))
+    got = hd.cpu()
+    assert float((got[:, :512].double() - want).abs().max()) <= 4e-3
+    assert torch.equal(got[:, 512:], h[:, 512:])
+
+
+@pytest.mark.parametrize("b,n0,n1", [(1, 1, 1), (1, 1, 70), (1, 160, 130), (3, 257, 64), (2, 512, 515), (1, 1024, 1024)])
+def test_assignment_kernels_match_oracle(pkg, b, n0, n1):
+    g = torch.Generator().manual_seed(n0 * 3 + n1)
+    sim = torch.randn(b, n0, n1, generator=g) * 3
+    z = torch.randn(b * (n0 + n1), 8, generator=g).half()  # logits live in a strided column, like MD[:, 256]
+    z0 = z[: b * n0, 3].unflatten(0, (b, n0))
+    z1 = z[b * n0:, 3].unflatten(0, (b, n1))
+    zd = z.to(DEV)
+    m0, ms, scores = pkg.matcher.assign(sim.to(DEV), zd[: b * n0, 3].unflatten(0, (b, n0)),
+                                        zd[b * n0:, 3].unflatten(0, (b, n1)), 0.0, want_scores=True)
+    cert = F.logsigmoid(z0.double())[:, :, None] + F.logsigmoid(z1.double())[:, None, :]
+    want = F.log_softmax(sim.double(), 2) + F.log_softmax(sim.double(), 1) + cert
+    assert float((scores.cpu().double() - want).abs().max()) < 2e-5
+    wm0, wms = mo.filter_matches(want, 0.0)
+    assert torch.equal(m0.cpu().long(), wm0)
+    np.testing.assert_allclose(ms.cpu().numpy(), wms.float().numpy(), rtol=2e-5, atol=1e-30)
+    # with a threshold: identical to thresholding the oracle's mscores
+    thr = float(wms[wms > 0].median()) if (wms > 0).any() else 0.5
+    m0t, _, _ = pkg.matcher.assign(sim.to(DEV), zd[: b * n0, 3].unflatten(0, (b, n0)),
+                                   zd[b * n0:, 3].unflatten(0, (b, n1)), thr)
+    wm0t, _ = mo.filter_matches(want.float(), thr)
+    assert int((m0t.cpu().long() != wm0t).sum()) <= 1  # a score exactly at the threshold may flip
+
+
+# ------------------------------------------------------------------------------------------------ full matcher
+def _agreement(ref_scores: torch.Tensor, got_m0: torch.Tensor):
+    """share of the reference's mutual-NN matches reproduced + the largest reference score gap among
+    disagreements (a disagreement is benign when the reference itself was nearly tied)."""
+    want_m0, _ = mo.filter_matches(ref_scores, 0.0)
+    want, got = want_m0[0], got_m0[0].long().cpu()
+    has = want >= 0
+    agree = float((got[has] == want[has]).float().mean()) if has.any() else 1.0
+    worst_gap = 0.0
+    for i in torch.nonzero(has & (got != want))[:, 0].tolist():
+        row = ref_scores[0, i]
+        alt = got[i] if got[i] >= 0 else row.topk(2).indices[1] if row.numel() > 1 else want[i]
+        worst_gap = max(worst_gap, float(row[want[i]] - row[alt]))
+    return agree, worst_gap
+
+
+def test_matcher_reproduces_reference_fixture(pkg, golden_dir):
+    z = np.load(golden_dir / "matcher_forward.npz")
+    for name in sorted({k.split(".")[0] for k in z.files}):
+        wseed, n_layers, fseed, n0, n1 = (int(v) for v in z[f"{name}.meta"])
+        matcher = pkg.PairMatcher(n_layers=n_layers, seed=wseed, threshold=0.0, device=DEV)
+        k0, k1, d0, d1 = (t.to(DEV) for t in mo.synth_pair(fseed, n0, n1))
+        out = matcher.match(k0, k1, d0, d1, want_scores=True)
+        ref_scores = torch.from_numpy(z[f"{name}.scores"])
+        err = (out["scores"].cpu() - ref_scores).abs()
+        dmax = float(np.abs(z[f"{name}.desc0"]).max())
+        e0 = float((out["desc0"].cpu() - torch.from_numpy(z[f"{name}.desc0"])).abs().max()) / dmax
+        e1 = float((out["desc1"].cpu() - torch.from_numpy(z[f"{name}.desc1"])).abs().max()) / dmax
+        agree, gap = _agreement(ref_scores, out["matches0"])
+        print(f"{name}: scores max {float(err.max()):.4f} mean {float(err.mean()):.5f}; desc rel {e0:.4f} {e1:.4f}; "
+              f"match agreement {agree:.3f} worst gap {gap:.4f}")
+        assert float(err.max()) <= TOL_SCORES_MAX and float(err.mean()) <= TOL_SCORES_MEAN
+        assert e0 <= TOL_DESC_REL and e1 <= TOL_DESC_REL
+        assert agree >= MIN_MATCH_AGREEMENT and gap < 0.1
+
+
+def test_batched_ragged_pairs_match_oracle(pkg):
+    """B pairs at once, N0 != N1, non-tile-multiple: every pair equals the FP32 oracle on that pair,
+    and equals the same pair matched alone (bit-exact: pairs are independent)."""
+    n_layers, b, n0, n1 = 3, 3, 200, 333
+    sd = pkg.reference_init_state_dict(4, n_layers)
+    matcher = pkg.PairMatcher(sd, n_layers=n_layers, threshold=0.0, device=DEV)
+    feats = [mo.synth_pair(50 + i, n0, n1) for i in range(b)]
+    k0, k1, d0, d1 = (torch.cat([f[j] for f in feats]).to(DEV) for j in range(4))
+    out = matcher.match(k0, k1, d0, d1, want_scores=True)
+    scores, m0 = out["scores"].cpu().clone(), out["matches0"].cpu().clone()
+    for i, f in enumerate(feats):
+        want = mo.forward(sd, *f, n_layers=n_layers, threshold=0.0)
+        err = (scores[i] - want["scores"][0]).abs()
+        assert float(err.max()) <= TOL_SCORES_MAX and float(err.mean()) <= TOL_SCORES_MEAN
+        agree, gap = _agreement(want["scores"], m0[i:i + 1])
+        assert agree >= MIN_MATCH_AGREEMENT and gap < 0.1
+        alone = matcher.match(*(t.to(DEV) for t in f), want_scores=True)
+        assert torch.equal(alone["scores"].cpu()[0], scores[i])
+        assert torch.equal(alone["matches0"].cpu()[0], m0[i])
+
+
+def test_graph_replay_equals_eager(pkg):
+    n_layers = 2
+    sd = pkg.reference_init_state_dict(8, n_layers)
+    f = [t.to(DEV) for t in mo.synth_pair(123, 300, 280)]
+    a = pkg.PairMatcher(sd, n_layers=n_layers, device=DEV, use_graph=True).match(*f, want_scores=True)
+    b = pkg.PairMatcher(sd, n_layers=n_layers, device=DEV, use_graph=False).match(*f, want_scores=True)
+    assert torch.equal(a["scores"], b["scores"]) and torch.equal(a["matches0"], b["matches0"])
+    assert a["launches"] == b["launches"] > 0
+
+
+def test_full_size_pair_properties(pkg):
+    """BASELINE configs[4] size (2048 keypoints), too slow for the CPU oracle: size-independent
+    properties.  (1) matches0 / mscores0 are consistent with the returned score matrix (mutual argmax);
+    (2) swapping the two images transposes the score matrix; (3) batch order is irrelevant."""
+    n_layers, b, n = 9, 2, 2048
+    matcher = pkg.PairMatcher(n_layers=n_layers, seed=0, threshold=0.0, device=DEV)
+    feats = [mo.synth_pair(900 + i, n, n, width=1280, height=960) for i in range(b)]
+    k0, k1, d0, d1 = (torch.cat([f[j] for f in feats]).to(DEV) for j in range(4))
+    out = matcher.match(k0, k1, d0, d1, want_scores=True)
+    scores, m0, ms = out["scores"].clone(), out["matches0"].clone(), out["mscores0"].clone()
+    assert torch.isfinite(scores).all()
+    wm0, wms = mo.filter_matches(scores, 0.0)
+    assert torch.equal(m0.long(), wm0)
+    torch.testing.assert_close(ms, wms, rtol=1e-5, atol=0)
+    swapped = matcher.match(k1, k0, d1, d0, want_scores=True)["scores"]
+    assert float((swapped.transpose(1, 2) - scores).abs().max()) <= 2e-2  # different GEMM/attention row order
+    flipped = matcher.match(k0.flip(0), k1.flip(0), d0.flip(0), d1.flip(0), want_scores=True)
+    assert torch.equal(flipped["scores"].flip(0), scores) and torch.equal(flipped["matches0"].flip(0), m0)
+
+
+def test_matcher_refuses_cpu_tensors(pkg):
+    matcher = pkg.PairMatcher(n_layers=1, device=DEV)
+    f = mo.synth_pair(1, 8, 8)
+    with pytest.raises(RuntimeError):
+        matcher.match(*f)
