@@ -125,6 +125,122 @@ def cpu_baseline_sample(reps: int) -> dict:
             "sample": f"{reps} problems of the workload shape (B1 H4 N=M=1024 d64), FP32 torch CPU, {dt*1e3:.2f} ms each"}
 
 
+
+# ------------------------------------------------------------------------------------------------
+# second half of BASELINE.json's metric: LightGlue pairs/s (configs[3], configs[4])
+# ------------------------------------------------------------------------------------------------
+PAIRS_PER_GPU = 64                 # configs[4]: "64 pairs per GPU"
+PAIR_KPTS = (1024, 2048, 4096)     # configs[3] (1x1024x1024 engine shape) and configs[4] (2048 / 4096 sweep)
+
+
+def pairs_sub_batch(kpts: int) -> int:
+    """Pairs per forward: keeps the packed activations of one forward around the L2 size
+    (measured sweep, tools/pairs_sweep.py: 64 / 32 / 8 pairs at 1024 / 2048 / 4096 keypoints)."""
+    return max(1, min(PAIRS_PER_GPU, 65536 // kpts if kpts <= 2048 else 32768 // kpts))
+
+
+def synth_features_host(torch, pairs: int, kpts: int, seed: int):
+    """Freiburg-shaped synthetic SuperPoint features (SURVEY.md §8d D-feat), pinned host tensors:
+    normalised keypoints [2, pairs, kpts, 2] FP32 and L2-normalised descriptors [2, pairs, kpts, 256] FP16."""
+    g = torch.Generator().manual_seed(seed)
+    scale = kpts / 1024.0
+    w, h = 640.0 * scale ** 0.5, 480.0 * scale ** 0.5
+    xy = torch.rand(2, pairs, kpts, 2, generator=g) * torch.tensor([w - 8.0, h - 8.0]) + 4.0
+    kp = ((xy.floor() - torch.tensor([w / 2, h / 2])) / (max(w, h) / 2)).float()
+    d = torch.randn(2, pairs, kpts, 256, generator=g)
+    d = (d / d.norm(dim=-1, keepdim=True)).half()
+    return kp.pin_memory(), d.pin_memory()
+
+
+def cpu_pairs_sample(kpts: int, reps: int = 1) -> dict:
+    """The reference's CPU path for a whole pair (lightglue_pytorch_no_plugin LightGlue.forward + filter_matches),
+    restated by oracle/matcher_oracle.py (pinned on reference-generated fixtures), FP32 torch CPU, all cores."""
+    import torch
+    from lgattn_pkg import pkg
+    from oracle import matcher_oracle as mo
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    sd = pkg.reference_init_state_dict(0, 9)
+    f = mo.synth_pair(1000, kpts, kpts)
+    with torch.no_grad():
+        mo.forward(sd, *[t[:, : min(kpts, 256)] for t in f])  # warm-up on a small pair
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            mo.forward(sd, *f)
+        dt = (time.perf_counter() - t0) / reps
+    return {"value": 1.0 / dt, "unit": "pairs/s", "cores": cores, "kind": "port",
+            "sample": f"{reps} pair(s) of {kpts} keypoints, 9 layers, FP32 torch CPU (oracle port of LightGlue.forward), {dt:.2f} s each"}
+
+
+def pairs_section(pkg, torch, dist, dev, rank: int, world: int, steps: int, with_cpu: bool) -> dict:
+    """LightGlue pairs/s: 64 independent pairs per GPU per step, sharded by rank (no collective in the data
+    path), matched in sub-batches through PairMatcher (CUDA-graph replay).  `value`: features resident in HBM;
+    `e2e`: pinned host features -> H2D -> match -> D2H of matches0 / mscores0, per sub-batch."""
+    out = {}
+    matcher = pkg.PairMatcher(seed=0, device=dev)
+    for kpts in PAIR_KPTS:
+        sub = pairs_sub_batch(kpts)
+        n_sub = PAIRS_PER_GPU // sub
+        kp_h, d_h = synth_features_host(torch, PAIRS_PER_GPU, kpts, 1000 + rank)
+        kp_d, d_d = kp_h.to(dev), d_h.to(dev)
+        plan = matcher.plan(sub, kpts, kpts)
+        m_h = torch.empty(PAIRS_PER_GPU, kpts, dtype=torch.int32).pin_memory()
+        s_h = torch.empty(PAIRS_PER_GPU, kpts, dtype=torch.float32).pin_memory()
+
+        def step_resident():
+            for i in range(n_sub):
+                sl = slice(i * sub, (i + 1) * sub)
+                matcher.match(kp_d[0, sl], kp_d[1, sl], d_d[0, sl], d_d[1, sl])
+
+        def step_e2e():
+            for i in range(n_sub):
+                sl = slice(i * sub, (i + 1) * sub)
+                k0, k1 = kp_h[0, sl].to(dev, non_blocking=True), kp_h[1, sl].to(dev, non_blocking=True)
+                d0, d1 = d_h[0, sl].to(dev, non_blocking=True), d_h[1, sl].to(dev, non_blocking=True)
+                r = matcher.match(k0, k1, d0, d1)
+                m_h[sl].copy_(r["matches0"], non_blocking=True)
+                s_h[sl].copy_(r["mscores0"], non_blocking=True)
+            torch.cuda.synchronize()
+
+        def timed(fn, n):
+            for _ in range(2):
+                fn()
+            torch.cuda.synchronize()
+            if world > 1:
+                dist.barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(n):
+                fn()
+            e1.record()
+            torch.cuda.synchronize()
+            t = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+            if world > 1:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item())
+
+        n_steps = max(1, min(steps, 5))
+        ms = timed(step_resident, n_steps)
+        ms_e2e = timed(step_e2e, n_steps)
+        pps = world * PAIRS_PER_GPU * n_steps / (ms * 1e-3)
+        fl = pkg.matcher.flops_per_pair(kpts, kpts)
+        entry = {"value": pps, "unit": "pairs/s", "pairs_per_step_per_gpu": PAIRS_PER_GPU, "pairs_per_forward": sub,
+                 "ms_per_pair_per_gpu": ms / (PAIRS_PER_GPU * n_steps), "model_tflops_per_gpu": pps / world * fl["total"] / 1e12,
+                 "attention_flop_share": fl["attention"] / fl["total"], "gpu_launches_per_forward": plan.launches,
+                 "e2e": {"value": world * PAIRS_PER_GPU * n_steps / (ms_e2e * 1e-3), "unit": "pairs/s",
+                         "h2d_bytes_per_step": int(kp_h.numel() * 4 + d_h.numel() * 2),
+                         "d2h_bytes_per_step": int(m_h.numel() * 4 + s_h.numel() * 4)},
+                 "matches_per_pair_at_threshold_0.1": float((m_h >= 0).sum()) / PAIRS_PER_GPU}
+        if with_cpu and kpts <= 2048:
+            entry["cpu_baseline"] = cpu_pairs_sample(kpts)
+        out[f"kpts{kpts}"] = entry
+        del kp_d, d_d, plan
+        matcher._plans.clear()
+        torch.cuda.empty_cache()
+    return out
+
+
 def run_reference(args) -> None:
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -140,12 +256,14 @@ def run_reference(args) -> None:
     cb = dict(vals[-1])
     cb["value"] = tf
     cb["sample"] = f"{per_step} problems/step of the workload shape, FP32 torch CPU (oracle port of lightglue.py:82-85)"
+    pairs = {} if args.no_pairs else {"kpts1024": {"cpu_baseline": cpu_pairs_sample(1024)}}
     line = {"impl": "reference", "metric": METRIC, "value": tf, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
             "warmup": warmup, "ms_per_step": wall / steps * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD, "problems_per_step": per_step, "note": "CPU reference arm, rank 0 only"},
             "cpu_baseline": cb,
-            "e2e": {"value": tf, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+            "e2e": {"value": tf, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "pairs": pairs}
     print(json.dumps(line), flush=True)
 
 
@@ -269,6 +387,11 @@ def run_ours(args) -> None:
     if rank == 0 and not args.no_extra:
         extra = extra_shapes(pkg, torch, dev, peaks)
 
+    # ---- LightGlue pairs/s (all ranks take part: pairs are sharded, time is max over ranks)
+    pairs = {}
+    if not args.no_pairs:
+        pairs = pairs_section(pkg, torch, dist, dev, rank, world, args.steps, with_cpu=(rank == 0 and world == 1))
+
     cpu = None
     if rank == 0 and world == 1:
         probe = cpu_baseline_sample(3)
@@ -295,6 +418,7 @@ def run_ours(args) -> None:
                     "steps": e2e_steps, "timing": "host wall clock around submit+sync, pinned host buffers, 4 streams"},
             "clocks": clocks,
             "extra": extra,
+            "pairs": pairs,
         }
         if cpu is not None:
             line["cpu_baseline"] = cpu
@@ -338,6 +462,7 @@ def main() -> None:
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-extra", action="store_true")
+    ap.add_argument("--no-pairs", action="store_true", help="skip the LightGlue pairs/s section")
     ap.add_argument("--traffic", type=float, default=None, help="dram bytes per launch from an ncu capture (profiles/)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
