@@ -181,7 +181,8 @@ def pairs_section(pkg, torch, dist, dev, rank: int, world: int, steps: int, with
     matcher = pkg.PairMatcher(seed=0, device=dev)
     for kpts in PAIR_KPTS:
         sub = pairs_sub_batch(kpts)
-        n_sub = PAIRS_PER_GPU // sub
+        slices = pkg.sharding.sub_batches(PAIRS_PER_GPU, sub)
+        mine = pkg.sharding.pairs_of_rank(PAIRS_PER_GPU * world, world, rank)   # global ids of this rank's pairs
         kp_h, d_h = synth_features_host(torch, PAIRS_PER_GPU, kpts, 1000 + rank)
         kp_d, d_d = kp_h.to(dev), d_h.to(dev)
         plan = matcher.plan(sub, kpts, kpts)
@@ -189,13 +190,13 @@ def pairs_section(pkg, torch, dist, dev, rank: int, world: int, steps: int, with
         s_h = torch.empty(PAIRS_PER_GPU, kpts, dtype=torch.float32).pin_memory()
 
         def step_resident():
-            for i in range(n_sub):
-                sl = slice(i * sub, (i + 1) * sub)
+            for a, b in slices:
+                sl = slice(a, b)
                 matcher.match(kp_d[0, sl], kp_d[1, sl], d_d[0, sl], d_d[1, sl])
 
         def step_e2e():
-            for i in range(n_sub):
-                sl = slice(i * sub, (i + 1) * sub)
+            for a, b in slices:
+                sl = slice(a, b)
                 k0, k1 = kp_h[0, sl].to(dev, non_blocking=True), kp_h[1, sl].to(dev, non_blocking=True)
                 d0, d1 = d_h[0, sl].to(dev, non_blocking=True), d_h[1, sl].to(dev, non_blocking=True)
                 r = matcher.match(k0, k1, d0, d1)
@@ -215,15 +216,17 @@ def pairs_section(pkg, torch, dist, dev, rank: int, world: int, steps: int, with
                 fn()
             e1.record()
             torch.cuda.synchronize()
-            t = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
-            if world > 1:
-                dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            return float(t.item())
+            return pkg.sharding.max_over_ranks(dist if world > 1 else None, e0.elapsed_time(e1), dev)
 
         n_steps = max(1, min(steps, 5))
         ms = timed(step_resident, n_steps)
         ms_e2e = timed(step_e2e, n_steps)
         pps = world * PAIRS_PER_GPU * n_steps / (ms * 1e-3)
+        # results gathered to the host of rank 0: per global pair, how many keypoints found a mutual neighbour
+        mutual = (s_h > 0).sum(dim=1).tolist()
+        gathered = pkg.sharding.gather_to_host(dist if world > 1 else None, dict(zip(mine, mutual)))
+        if rank == 0 and len(gathered) != PAIRS_PER_GPU * world:
+            raise SystemExit("bench.py: host gather lost pairs")
         fl = pkg.matcher.flops_per_pair(kpts, kpts)
         entry = {"value": pps, "unit": "pairs/s", "pairs_per_step_per_gpu": PAIRS_PER_GPU, "pairs_per_forward": sub,
                  "ms_per_pair_per_gpu": ms / (PAIRS_PER_GPU * n_steps), "model_tflops_per_gpu": pps / world * fl["total"] / 1e12,
@@ -231,7 +234,9 @@ def pairs_section(pkg, torch, dist, dev, rank: int, world: int, steps: int, with
                  "e2e": {"value": world * PAIRS_PER_GPU * n_steps / (ms_e2e * 1e-3), "unit": "pairs/s",
                          "h2d_bytes_per_step": int(kp_h.numel() * 4 + d_h.numel() * 2),
                          "d2h_bytes_per_step": int(m_h.numel() * 4 + s_h.numel() * 4)},
-                 "matches_per_pair_at_threshold_0.1": float((m_h >= 0).sum()) / PAIRS_PER_GPU}
+                 "matches_per_pair_at_threshold_0.1": float((m_h >= 0).sum()) / PAIRS_PER_GPU,
+                 "mutual_nn_per_pair": (sum(gathered.values()) / len(gathered)) if rank == 0 else None,
+                 "pairs_gathered_to_host": len(gathered) if rank == 0 else None}
         if with_cpu and kpts <= 2048:
             entry["cpu_baseline"] = cpu_pairs_sample(kpts)
         out[f"kpts{kpts}"] = entry
