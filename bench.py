@@ -194,14 +194,37 @@ def pairs_section(pkg, torch, dist, dev, rank: int, world: int, steps: int, with
                 sl = slice(a, b)
                 matcher.match(kp_d[0, sl], kp_d[1, sl], d_d[0, sl], d_d[1, sl])
 
+        # e2e: a copy stream stages the NEXT sub-batch's features (pinned host -> two device staging slots)
+        # while the compute stream matches the current one; results go back on the compute stream.
+        copy_s = torch.cuda.Stream(device=dev)
+        stage_kp = [torch.empty(2, sub, kpts, 2, dtype=torch.float32, device=dev) for _ in range(2)]
+        stage_d = [torch.empty(2, sub, kpts, 256, dtype=torch.float16, device=dev) for _ in range(2)]
+        ev_in = [torch.cuda.Event() for _ in range(2)]
+        ev_used = [torch.cuda.Event() for _ in range(2)]
+
+        def stage(i):
+            a, b = slices[i]
+            slot = i % 2
+            with torch.cuda.stream(copy_s):
+                copy_s.wait_event(ev_used[slot])            # the forward that read this slot has consumed it
+                for img in (0, 1):                         # contiguous pinned slices: true async DMA copies
+                    stage_kp[slot][img, : b - a].copy_(kp_h[img, a:b], non_blocking=True)
+                    stage_d[slot][img, : b - a].copy_(d_h[img, a:b], non_blocking=True)
+                ev_in[slot].record(copy_s)
+
         def step_e2e():
-            for a, b in slices:
-                sl = slice(a, b)
-                k0, k1 = kp_h[0, sl].to(dev, non_blocking=True), kp_h[1, sl].to(dev, non_blocking=True)
-                d0, d1 = d_h[0, sl].to(dev, non_blocking=True), d_h[1, sl].to(dev, non_blocking=True)
-                r = matcher.match(k0, k1, d0, d1)
-                m_h[sl].copy_(r["matches0"], non_blocking=True)
-                s_h[sl].copy_(r["mscores0"], non_blocking=True)
+            comp = torch.cuda.current_stream(dev)
+            stage(0)
+            for i, (a, b) in enumerate(slices):
+                if i + 1 < len(slices):
+                    stage(i + 1)
+                slot = i % 2
+                comp.wait_event(ev_in[slot])
+                n = b - a
+                r = matcher.match(stage_kp[slot][0, :n], stage_kp[slot][1, :n], stage_d[slot][0, :n], stage_d[slot][1, :n])
+                ev_used[slot].record(comp)
+                m_h[a:b].copy_(r["matches0"], non_blocking=True)
+                s_h[a:b].copy_(r["mscores0"], non_blocking=True)
             torch.cuda.synchronize()
 
         def timed(fn, n):

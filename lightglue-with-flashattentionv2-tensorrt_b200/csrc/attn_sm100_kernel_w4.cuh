@@ -43,7 +43,10 @@ using namespace ptx;
 
 constexpr int kThreads = 256;   // 4 softmax warps + TMA + MMA + TMEM-alloc + spare
 // Q tile + 2 x (K, V) tiles (16 KiB each) + barriers, + 1 KiB slack for manual 1024-B alignment
-constexpr uint32_t kSmemBytes = (1 + 2 * kStages) * 16384 + 1024 + 1024;
+#ifndef LG_ATTN_W4_EXTRA_SMEM
+#define LG_ATTN_W4_EXTRA_SMEM 0   // tuning only: > 31 KiB forces one CTA per SM
+#endif
+constexpr uint32_t kSmemBytes = (1 + 2 * kStages) * 16384 + 1024 + 1024 + LG_ATTN_W4_EXTRA_SMEM;
 
 // ------------------------------------------------------------------------------------------------
 // shared-memory map (offsets from a 1024-byte aligned base; SWIZZLE_128B tiles need that alignment)
@@ -79,6 +82,21 @@ constexpr uint32_t kColP = 192;
 
 constexpr int kRegsSoftmax = 216;
 constexpr int kRegsOther = 40;
+
+// Optional per-tile phase tracing (tuning builds only, -DLG_ATTN_W4_TRACE): clock64 stamps of softmax
+// warp 0 / lane 0 of the first CTAs, read back through lg_attn_debug_read_w4_trace().
+#ifdef LG_ATTN_W4_TRACE
+constexpr int kW4TraceCtas = 592, kW4TraceTiles = 16, kW4TraceEvents = 8;
+__device__ long long g_w4_trace[kW4TraceCtas][kW4TraceTiles][kW4TraceEvents];
+__device__ unsigned g_w4_smid[kW4TraceCtas];
+#define W4_TRACE(j, ev)                                                                       \
+    do {                                                                                      \
+        if (warp == 0 && lane == 0 && blockIdx.x < kW4TraceCtas && (j) < kW4TraceTiles)       \
+            g_w4_trace[blockIdx.x][(j)][(ev)] = clock64();                                    \
+    } while (0)
+#else
+#define W4_TRACE(j, ev)
+#endif
 
 template <bool kOutF32>
 __global__ void __launch_bounds__(kThreads, 2)
@@ -200,9 +218,18 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
         float m_used = -INFINITY;  // row max the exponent is referenced to (raw score units)
         float l_sum = 0.f;
 
+#ifdef LG_ATTN_W4_TRACE
+        if (warp == 0 && lane == 0 && blockIdx.x < kW4TraceCtas) {
+            unsigned smid;
+            asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+            g_w4_smid[blockIdx.x] = smid;
+        }
+#endif
         for (int j = 0; j < num_kv_tiles; ++j) {
+            W4_TRACE(j, 0);
             mbar_wait(bar(kBarSFull), j & 1);
             tc_fence_after();
+            W4_TRACE(j, 1);
             uint32_t sr[kBlockN];
 #pragma unroll
             for (int c = 0; c < kBlockN / 32; ++c) tmem_ld_x32(t_s + 32u * c, sr + 32 * c);
@@ -210,6 +237,7 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(bar(kBarSEmpty));
+            W4_TRACE(j, 2);
 
             // ragged KV tail: columns past n_kv get -inf (TMA zero-filled K rows gave S = 0 there)
             const int valid = n_kv - j * kBlockN;
@@ -236,15 +264,18 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
                 }
             }
             const float neg_m = -m_used * kScaleLog2;
+            W4_TRACE(j, 3);
 
             // P = exp2(s*c - m*c) as packed FP16 pairs + the FP32 row sum (softmax_math.cuh)
             uint32_t pk[kBlockN / 2];
             const float tile_sum = softmax_exp_pass<kBlockN>(sr, pk, neg_m);
 
+            W4_TRACE(j, 4);
             if (j > 0) {
                 mbar_wait(bar(kBarPVDone), (j - 1) & 1);  // P buffer free, O(j-1) final
                 tc_fence_after();
             }
+            W4_TRACE(j, 5);
             tmem_st_x32(t_p, pk);
             tmem_st_x32(t_p + 32u, pk + 32);
             if (rescale) {
@@ -265,6 +296,7 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(bar(kBarPFull));
+            W4_TRACE(j, 6);
         }
 
         // ------------------------------------------------------------------------------- epilogue

@@ -152,6 +152,13 @@ bool valid_dtype(int d) { return d == LG_ATTN_F16_F16 || d == LG_ATTN_F32_F32 ||
 
 }  // namespace
 
+#ifdef LG_ATTN_W4_TRACE
+extern "C" int lg_attn_debug_read_w4_trace(long long* dst, unsigned* smid) {
+    cudaError_t e = cudaMemcpyFromSymbol(dst, lgattn::w4::g_w4_trace, sizeof(lgattn::w4::g_w4_trace));
+    if (e == cudaSuccess) e = cudaMemcpyFromSymbol(smid, lgattn::w4::g_w4_smid, sizeof(lgattn::w4::g_w4_smid));
+    return static_cast<int>(e);
+}
+#endif
 #ifdef LG_ATTN_TRACE
 static std::atomic<int> g_trace_seq{0};
 #define LG_TRACE_SEQ , g_trace_seq.fetch_add(1)

@@ -85,7 +85,8 @@ __device__ __forceinline__ float gelu_erf(float x) {
     p *= t;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"((z * -1.4426950408889634f) * z));
     const float erf_abs = fmaf(-p, e, 1.0f);
-    return fmaf(z * 0.70710678118654752f, erf_abs, 0.5f * x);
+    const float hx = 0.5f * x;
+    return fmaf(fabsf(hx), erf_abs, hx);
 }
 
 // One warp per row of 512: lane owns columns [8*lane, 8*lane+8) and [256 + 8*lane, ...).
@@ -147,115 +148,180 @@ __global__ void __launch_bounds__(256) layernorm_gelu_kernel(__half* __restrict_
 }
 
 // ------------------------------------------------------------------------------------------ assignment
+// Four streaming passes over sim [B, n0, n1] FP32 (row lse, column lse, row best, column best), each a
+// pure read at L2 / HBM speed: 128-bit loads when n1 % 4 == 0 (VEC = 4), rows unrolled for memory-level
+// parallelism, column passes split over row blocks (partials combined by a tiny second kernel) so the
+// grid fills 148 SMs at any batch size.
 __device__ __forceinline__ float log_sigmoid(float z) { return fminf(z, 0.f) - log1pf(expf(-fabsf(z))); }
 
 // (max, sum exp(x - max)) online merge
 __device__ __forceinline__ void lse_merge(float& m, float& s, float m2, float s2) {
     const float mn = fmaxf(m, m2);
     if (mn == -INFINITY) { m = mn; s = 0.f; return; }
-    s = s * expf(m - mn) + s2 * expf(m2 - mn);
+    s = s * __expf(m - mn) + s2 * __expf(m2 - mn);
     m = mn;
 }
+__device__ __forceinline__ void lse_push(float& m, float& s, float x) {
+    if (x > m) { s = s * __expf(m - x) + 1.f; m = x; } else { s += __expf(x - m); }
+}
 
-// row_lse[b, i] = logsumexp_j sim[b, i, j]; also lsz (log-sigmoid of the matchability logits).  Warp per row.
-__global__ void __launch_bounds__(256) row_lse_kernel(const float* __restrict__ sim, long long rows, int n1,
-                                                      float* __restrict__ row_lse) {
+template <int VEC>
+__device__ __forceinline__ void load_vec(const float* p, float (&v)[VEC]) {
+    if constexpr (VEC == 4) {
+        const float4 t = *reinterpret_cast<const float4*>(p);
+        v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+    } else {
+        v[0] = *p;
+    }
+}
+
+constexpr int kColRowsPerCta = 256;  // rows of sim one column-pass CTA walks (8 row groups x 32 rows)
+
+// Warp per row.  MODE 0: row_term[r] = logsigmoid(z0[r]) - logsumexp_j sim[r, j]
+//                MODE 1: m0[r] = argmax_j (2 sim[r, j] + col_term[j]), score0[r] = that max + row_term[r]
+template <int MODE, int VEC>
+__global__ void __launch_bounds__(256) row_pass_kernel(const float* __restrict__ sim, int n0, int n1, long long rows,
+                                                       const __half* __restrict__ z0, long long z_stride,
+                                                       const float* __restrict__ col_term, float* __restrict__ row_term,
+                                                       int* __restrict__ m0, float* __restrict__ score0) {
     const int lane = threadIdx.x & 31;
     for (long long r = blockIdx.x * 8LL + (threadIdx.x >> 5); r < rows; r += gridDim.x * 8LL) {
         const float* p = sim + r * n1;
+        const float* ct = MODE == 1 ? col_term + (r / n0) * n1 : nullptr;
         float m = -INFINITY, s = 0.f;
-        for (int j = lane; j < n1; j += 32) {
-            const float x = p[j];
-            if (x > m) { s = s * expf(m - x) + 1.f; m = x; } else { s += expf(x - m); }
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            const float m2 = __shfl_xor_sync(0xffffffffu, m, o), s2 = __shfl_xor_sync(0xffffffffu, s, o);
-            lse_merge(m, s, m2, s2);
-        }
-        if (lane == 0) row_lse[r] = m + logf(s);
-    }
-}
-
-// Column pass over one pair: block = 32 column lanes x 8 row groups; grid (ceil(n1/32), batch).
-// MODE 0: col_lse[b, j] = logsumexp_i sim[b, i, j]
-// MODE 1: best row per column of  2 sim[i,j] - row_lse[i] + lsz0[i]  ->  m1[b, j]
-template <int MODE>
-__global__ void __launch_bounds__(256) col_pass_kernel(const float* __restrict__ sim, int n0, int n1,
-                                                       const float* __restrict__ row_term, float* __restrict__ col_lse,
-                                                       int* __restrict__ m1) {
-    __shared__ float sh_a[8][33];
-    __shared__ float sh_b[8][33];
-    const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
-    const int b = blockIdx.y;
-    const int j = blockIdx.x * 32 + cx;
-    const float* p = sim + static_cast<long long>(b) * n0 * n1;
-    const float* rt = row_term + static_cast<long long>(b) * n0;
-    float m = -INFINITY, s = 0.f;  // MODE 1: m = best value, s = best index (as int bits)
-    int best = 0x7fffffff;
-    if (j < n1) {
-        for (int i = ry; i < n0; i += 8) {
-            const float x = p[static_cast<long long>(i) * n1 + j];
-            if (MODE == 0) {
-                if (x > m) { s = s * expf(m - x) + 1.f; m = x; } else { s += expf(x - m); }
-            } else {
-                const float v = 2.f * x + rt[i];
-                if (v > m) { m = v; best = i; }
-            }
-        }
-    }
-    sh_a[ry][cx] = m;
-    sh_b[ry][cx] = MODE == 0 ? s : __int_as_float(best);
-    __syncthreads();
-    if (ry == 0 && j < n1) {
-        if (MODE == 0) {
-            for (int g = 1; g < 8; ++g) lse_merge(m, s, sh_a[g][cx], sh_b[g][cx]);
-            col_lse[static_cast<long long>(b) * n1 + j] = m + logf(s);
-        } else {
-            for (int g = 1; g < 8; ++g) {
-                const float v = sh_a[g][cx];
-                const int bi = __float_as_int(sh_b[g][cx]);
-                if (v > m || (v == m && bi < best)) { m = v; best = bi; }
-            }
-            m1[static_cast<long long>(b) * n1 + j] = best;
-        }
-    }
-}
-
-// lsz[k] = logsigmoid(z[k * stride]) for both images; row_term[b,i] = lsz0 - row_lse; col_term[b,j] = lsz1 - col_lse
-__global__ void __launch_bounds__(256) terms_kernel(const __half* __restrict__ z, long long z_stride, long long count,
-                                                    const float* __restrict__ lse, float* __restrict__ term) {
-    for (long long t = blockIdx.x * 256LL + threadIdx.x; t < count; t += gridDim.x * 256LL)
-        term[t] = log_sigmoid(__half2float(z[t * z_stride])) - lse[t];
-}
-
-// Warp per row: best column of 2 sim[i,j] + col_term[j]; score0 = that + row_term[i].
-__global__ void __launch_bounds__(256) row_best_kernel(const float* __restrict__ sim, int batch, int n0, int n1,
-                                                       const float* __restrict__ row_term,
-                                                       const float* __restrict__ col_term, int* __restrict__ m0,
-                                                       float* __restrict__ score0) {
-    const int lane = threadIdx.x & 31;
-    const long long rows = static_cast<long long>(batch) * n0;
-    for (long long r = blockIdx.x * 8LL + (threadIdx.x >> 5); r < rows; r += gridDim.x * 8LL) {
-        const long long b = r / n0;
-        const float* p = sim + r * n1;
-        const float* ct = col_term + b * n1;
-        float best = -INFINITY;
         int bj = 0x7fffffff;
-        for (int j = lane; j < n1; j += 32) {
-            const float v = 2.f * p[j] + ct[j];
-            if (v > best) { best = v; bj = j; }
+#pragma unroll 4
+        for (int j = lane * VEC; j < n1; j += 32 * VEC) {
+            float x[VEC];
+            load_vec<VEC>(p + j, x);
+            if (MODE == 0) {
+                float mx = x[0];
+#pragma unroll
+                for (int e = 1; e < VEC; ++e) mx = fmaxf(mx, x[e]);
+                if (mx > m) { s *= __expf(m - mx); m = mx; }
+#pragma unroll
+                for (int e = 0; e < VEC; ++e) s += __expf(x[e] - m);
+            } else {
+                float c[VEC];
+                load_vec<VEC>(ct + j, c);
+#pragma unroll
+                for (int e = 0; e < VEC; ++e) {
+                    const float v = fmaf(2.f, x[e], c[e]);
+                    if (v > m) { m = v; bj = j + e; }
+                }
+            }
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
-            const float v2 = __shfl_xor_sync(0xffffffffu, best, o);
-            const int j2 = __shfl_xor_sync(0xffffffffu, bj, o);
-            if (v2 > best || (v2 == best && j2 < bj)) { best = v2; bj = j2; }
+            const float m2 = __shfl_xor_sync(0xffffffffu, m, o);
+            if (MODE == 0) {
+                const float s2 = __shfl_xor_sync(0xffffffffu, s, o);
+                lse_merge(m, s, m2, s2);
+            } else {
+                const int j2 = __shfl_xor_sync(0xffffffffu, bj, o);
+                if (m2 > m || (m2 == m && j2 < bj)) { m = m2; bj = j2; }
+            }
         }
         if (lane == 0) {
-            m0[r] = bj;
-            score0[r] = best + row_term[r];
+            if (MODE == 0) {
+                row_term[r] = log_sigmoid(__half2float(z0[r * z_stride])) - (m + logf(s));
+            } else {
+                m0[r] = bj;
+                score0[r] = m + row_term[r];
+            }
         }
+    }
+}
+
+// Column pass, partial over one block of kColRowsPerCta rows: block = 32 column lanes (VEC columns each)
+// x 8 row groups; grid (ceil(n1 / (32 VEC)), row blocks, batch).
+// MODE 0: (max, sum exp) of sim[:, j] over the row block           -> part_a, part_b [B, S, n1]
+// MODE 1: best (value, row) of 2 sim[i, j] + row_term[i] over it   -> part_a, part_b (row as int bits)
+template <int MODE, int VEC>
+__global__ void __launch_bounds__(256) col_partial_kernel(const float* __restrict__ sim, int n0, int n1,
+                                                          const float* __restrict__ row_term,
+                                                          float* __restrict__ part_a, float* __restrict__ part_b) {
+    __shared__ float sh_a[8][32 * VEC + 1];
+    __shared__ float sh_b[8][32 * VEC + 1];
+    const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
+    const int b = blockIdx.z, sp = blockIdx.y;
+    const int j0 = (blockIdx.x * 32 + cx) * VEC;
+    const int r_begin = sp * kColRowsPerCta;
+    const int r_end = min(n0, r_begin + kColRowsPerCta);
+    const float* p = sim + static_cast<long long>(b) * n0 * n1 + j0;
+    const float* rt = row_term + static_cast<long long>(b) * n0;
+    float m[VEC], s[VEC];
+    int best[VEC];
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) { m[e] = -INFINITY; s[e] = 0.f; best[e] = 0x7fffffff; }
+    if (j0 < n1) {
+#pragma unroll 4
+        for (int i = r_begin + ry; i < r_end; i += 8) {
+            float x[VEC];
+            load_vec<VEC>(p + static_cast<long long>(i) * n1, x);
+            if (MODE == 0) {
+#pragma unroll
+                for (int e = 0; e < VEC; ++e) lse_push(m[e], s[e], x[e]);
+            } else {
+                const float t = rt[i];
+#pragma unroll
+                for (int e = 0; e < VEC; ++e) {
+                    const float v = fmaf(2.f, x[e], t);
+                    if (v > m[e]) { m[e] = v; best[e] = i; }
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) {
+        sh_a[ry][cx * VEC + e] = m[e];
+        sh_b[ry][cx * VEC + e] = MODE == 0 ? s[e] : __int_as_float(best[e]);
+    }
+    __syncthreads();
+    // 32 * VEC columns, one per thread of the first VEC warps
+    const int col = threadIdx.x;
+    const int j = blockIdx.x * 32 * VEC + col;
+    if (col < 32 * VEC && j < n1) {
+        float ma = sh_a[0][col], sb = sh_b[0][col];
+        int bi = __float_as_int(sb);
+        for (int g = 1; g < 8; ++g) {
+            if (MODE == 0) {
+                lse_merge(ma, sb, sh_a[g][col], sh_b[g][col]);
+            } else {
+                const float v = sh_a[g][col];
+                const int i2 = __float_as_int(sh_b[g][col]);
+                if (v > ma || (v == ma && i2 < bi)) { ma = v; bi = i2; }
+            }
+        }
+        const long long o = (static_cast<long long>(b) * gridDim.y + sp) * n1 + j;
+        part_a[o] = ma;
+        part_b[o] = MODE == 0 ? sb : __int_as_float(bi);
+    }
+}
+
+// Combine the row-block partials of a column.  MODE 0: col_term[b, j] = logsigmoid(z1) - logsumexp_i sim[i, j];
+// MODE 1: m1[b, j] = best row.
+template <int MODE>
+__global__ void __launch_bounds__(256) col_combine_kernel(const float* __restrict__ part_a, const float* __restrict__ part_b,
+                                                          int n_parts, int n1, long long cols,
+                                                          const __half* __restrict__ z1, long long z_stride,
+                                                          float* __restrict__ col_term, int* __restrict__ m1) {
+    for (long long t = blockIdx.x * 256LL + threadIdx.x; t < cols; t += gridDim.x * 256LL) {
+        const long long b = t / n1;
+        const long long base = b * n_parts * n1 + (t - b * n1);
+        float ma = part_a[base], sb = part_b[base];
+        int bi = __float_as_int(sb);
+        for (int g = 1; g < n_parts; ++g) {
+            const float a2 = part_a[base + static_cast<long long>(g) * n1], b2 = part_b[base + static_cast<long long>(g) * n1];
+            if (MODE == 0) {
+                lse_merge(ma, sb, a2, b2);
+            } else {
+                const int i2 = __float_as_int(b2);
+                if (a2 > ma || (a2 == ma && i2 < bi)) { ma = a2; bi = i2; }
+            }
+        }
+        if (MODE == 0) col_term[t] = log_sigmoid(__half2float(z1[t * z_stride])) - (ma + logf(sb));
+        else m1[t] = bi;
     }
 }
 
@@ -352,7 +418,9 @@ int lg_match_layernorm_gelu(void* h_half, long long rows, int ld, const float* g
 size_t lg_match_assign_workspace_bytes(int batch, int n0, int n1) {
     if (batch <= 0 || n0 <= 0 || n1 <= 0) return 0;
     const size_t r0 = align256(static_cast<size_t>(batch) * n0 * 4), r1 = align256(static_cast<size_t>(batch) * n1 * 4);
-    return 4 * r0 + 3 * r1;  // row_lse, row_term, m0, score0 | col_lse, col_term, m1
+    const size_t parts = (static_cast<size_t>(n0) + kColRowsPerCta - 1) / kColRowsPerCta;
+    // row_term, m0, score0 | col_term, m1 | two partial planes [batch, row blocks, n1]
+    return 3 * r0 + 2 * r1 + 2 * align256(static_cast<size_t>(batch) * parts * n1 * 4);
 }
 
 int lg_match_assign_launches(int with_scores) { return with_scores ? 8 : 7; }
@@ -367,27 +435,44 @@ int lg_match_assign(const float* sim, const void* z0_half, const void* z1_half, 
     cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
     const long long rows0 = static_cast<long long>(batch) * n0, rows1 = static_cast<long long>(batch) * n1;
     const size_t r0 = align256(static_cast<size_t>(rows0) * 4), r1 = align256(static_cast<size_t>(rows1) * 4);
+    const int parts = (n0 + kColRowsPerCta - 1) / kColRowsPerCta;
+    if (parts > 65535) return LG_ATTN_EINVAL;
+    const size_t pp = align256(static_cast<size_t>(batch) * parts * n1 * 4);
     uint8_t* ws = static_cast<uint8_t*>(workspace);
-    float* row_lse = reinterpret_cast<float*>(ws);
-    float* row_term = reinterpret_cast<float*>(ws + r0);
-    int* m0 = reinterpret_cast<int*>(ws + 2 * r0);
-    float* score0 = reinterpret_cast<float*>(ws + 3 * r0);
-    float* col_lse = reinterpret_cast<float*>(ws + 4 * r0);
-    float* col_term = reinterpret_cast<float*>(ws + 4 * r0 + r1);
-    int* m1 = reinterpret_cast<int*>(ws + 4 * r0 + 2 * r1);
-    const dim3 col_grid(static_cast<unsigned>((n1 + 31) / 32), static_cast<unsigned>(batch));
+    float* row_term = reinterpret_cast<float*>(ws);
+    int* m0 = reinterpret_cast<int*>(ws + r0);
+    float* score0 = reinterpret_cast<float*>(ws + 2 * r0);
+    float* col_term = reinterpret_cast<float*>(ws + 3 * r0);
+    int* m1 = reinterpret_cast<int*>(ws + 3 * r0 + r1);
+    float* part_a = reinterpret_cast<float*>(ws + 3 * r0 + 2 * r1);
+    float* part_b = reinterpret_cast<float*>(ws + 3 * r0 + 2 * r1 + pp);
+    const __half* z0 = static_cast<const __half*>(z0_half);
+    const __half* z1 = static_cast<const __half*>(z1_half);
+    const bool vec = (n1 & 3) == 0 && (reinterpret_cast<uintptr_t>(sim) & 15u) == 0;
+    const int cols_per_cta = vec ? 128 : 32;
+    const dim3 col_grid(static_cast<unsigned>((n1 + cols_per_cta - 1) / cols_per_cta), static_cast<unsigned>(parts),
+                        static_cast<unsigned>(batch));
+    const unsigned row_grid = grid_for(rows0, 8, 16), cmb_grid = grid_for(rows1, 256);
 
-    row_lse_kernel<<<grid_for(rows0, 8), 256, 0, stream>>>(sim, rows0, n1, row_lse);
-    col_pass_kernel<0><<<col_grid, 256, 0, stream>>>(sim, n0, n1, row_lse, col_lse, nullptr);
-    terms_kernel<<<grid_for(rows0, 256), 256, 0, stream>>>(static_cast<const __half*>(z0_half), z_stride, rows0, row_lse,
-                                                           row_term);
-    terms_kernel<<<grid_for(rows1, 256), 256, 0, stream>>>(static_cast<const __half*>(z1_half), z_stride, rows1, col_lse,
-                                                           col_term);
-    row_best_kernel<<<grid_for(rows0, 8), 256, 0, stream>>>(sim, batch, n0, n1, row_term, col_term, m0, score0);
-    col_pass_kernel<1><<<col_grid, 256, 0, stream>>>(sim, n0, n1, row_term, nullptr, m1);
+    if (vec) {
+        row_pass_kernel<0, 4><<<row_grid, 256, 0, stream>>>(sim, n0, n1, rows0, z0, z_stride, nullptr, row_term, nullptr, nullptr);
+        col_partial_kernel<0, 4><<<col_grid, 256, 0, stream>>>(sim, n0, n1, row_term, part_a, part_b);
+    } else {
+        row_pass_kernel<0, 1><<<row_grid, 256, 0, stream>>>(sim, n0, n1, rows0, z0, z_stride, nullptr, row_term, nullptr, nullptr);
+        col_partial_kernel<0, 1><<<col_grid, 256, 0, stream>>>(sim, n0, n1, row_term, part_a, part_b);
+    }
+    col_combine_kernel<0><<<cmb_grid, 256, 0, stream>>>(part_a, part_b, parts, n1, rows1, z1, z_stride, col_term, nullptr);
+    if (vec) {
+        row_pass_kernel<1, 4><<<row_grid, 256, 0, stream>>>(sim, n0, n1, rows0, z0, z_stride, col_term, row_term, m0, score0);
+        col_partial_kernel<1, 4><<<col_grid, 256, 0, stream>>>(sim, n0, n1, row_term, part_a, part_b);
+    } else {
+        row_pass_kernel<1, 1><<<row_grid, 256, 0, stream>>>(sim, n0, n1, rows0, z0, z_stride, col_term, row_term, m0, score0);
+        col_partial_kernel<1, 1><<<col_grid, 256, 0, stream>>>(sim, n0, n1, row_term, part_a, part_b);
+    }
+    col_combine_kernel<1><<<cmb_grid, 256, 0, stream>>>(part_a, part_b, parts, n1, rows1, z1, z_stride, nullptr, m1);
     mutual_kernel<<<grid_for(rows0, 256), 256, 0, stream>>>(m0, m1, score0, batch, n0, n1, threshold, matches0, mscores0);
     if (scores != nullptr) {
-        if ((n1 & 3) == 0 && (reinterpret_cast<uintptr_t>(sim) & 15u) == 0 && (reinterpret_cast<uintptr_t>(scores) & 15u) == 0)
+        if (vec && (reinterpret_cast<uintptr_t>(scores) & 15u) == 0)
             scores_kernel<<<grid_for(rows0 * (n1 >> 2), 256), 256, 0, stream>>>(
                 reinterpret_cast<const float4*>(sim), rows0, n0, n1, row_term, col_term, reinterpret_cast<float4*>(scores));
         else
