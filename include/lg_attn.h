@@ -65,14 +65,18 @@ int lg_attn_hd64_launch(const void* q, const void* k, const void* v, void* o,
  * lightglue_pytorch_with_plugin/lightglue.py:139-147, 154-156, 190-199).  Q, K, V are FP16; element
  * (b, h, r, c) of a tensor lives at base + b*batch + h*head + r*row + c (strides in ELEMENTS, the 64
  * head-dim elements contiguous).  Strides must be multiples of 16 bytes, pointers 16-byte aligned.
- * out_f32: 0 -> FP16 output, 1 -> FP32 output.  No workspace.  Same guarantees as lg_attn_hd64_launch. */
+ * out_f32: 0 -> FP16 output, 1 -> FP32 output.  kv_batch_shift (0 <= shift < batch): batch entry b of Q
+ * attends to batch entry (b + shift) mod batch of K and V; with two image sets stacked along the batch
+ * dimension, shift = batch / 2 runs both directions of CrossBlock.forward (lightglue.py:188-199) in one
+ * launch.  No workspace.  Same guarantees as lg_attn_hd64_launch. */
 typedef struct lg_attn_strides {
     long long batch, head, row;
 } lg_attn_strides;
 int lg_attn_hd64_launch_strided(const void* q, const void* k, const void* v, void* o,
                                 int batch, int heads, int n_q, int n_kv, int out_f32,
                                 const lg_attn_strides* sq, const lg_attn_strides* sk,
-                                const lg_attn_strides* sv, const lg_attn_strides* so, void* stream);
+                                const lg_attn_strides* sv, const lg_attn_strides* so,
+                                int kv_batch_shift, void* stream);
 
 /* Convenience for non-CUDA hosts (ctypes / cgo): HOST buffers in, HOST buffer out.
  * Allocates device scratch, copies H2D, launches, copies D2H, synchronises.  Not for the

@@ -100,7 +100,7 @@ def load() -> ctypes.CDLL:
         ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
         ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
         ctypes.POINTER(Strides), ctypes.POINTER(Strides), ctypes.POINTER(Strides), ctypes.POINTER(Strides),
-        ctypes.c_void_p,
+        ctypes.c_int, ctypes.c_void_p,
     ]
     lib.lg_attn_hd64_run_host.restype = ctypes.c_int
     lib.lg_attn_hd64_run_host.argtypes = [

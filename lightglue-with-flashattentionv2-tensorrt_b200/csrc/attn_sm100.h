@@ -11,9 +11,13 @@ constexpr int kStages = 2;      // K/V shared-memory ring depth
 
 // Where a (batch, head) slice of O starts and how far apart its rows are, in ELEMENTS of the output
 // type.  Contiguous [B,H,N,64] (the plugin layout): sb = H*N*64, sh = N*64, sr = 64.
+// kv_shift: K/V of batch entry b are read from batch entry (b + kv_shift) mod batch — lets both directions
+// of a cross-attention between two stacked image sets run as ONE launch (kv_shift = batch / 2).
 struct OutLayout {
     long long sb, sh, sr;
     int heads;
+    int batch;
+    int kv_shift;
 };
 
 }  // namespace lgattn

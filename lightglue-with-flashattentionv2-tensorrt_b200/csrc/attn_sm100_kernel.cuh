@@ -157,6 +157,7 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
     const int tile_m = work % tiles_m;
     const int bh = work / tiles_m;
     const int hi = bh % ol.heads, bi = bh / ol.heads;
+    const int bk = bi + ol.kv_shift >= ol.batch ? bi + ol.kv_shift - ol.batch : bi + ol.kv_shift;  // batch entry of K / V
     const int total_kv_tiles = (n_kv + kBlockN - 1) / kBlockN;
     const int kv_base = total_kv_tiles / num_splits, kv_rem = total_kv_tiles % num_splits;
     const int num_kv_tiles = kv_base + (split < kv_rem ? 1 : 0);            // >= 1 (host: splits <= tiles)
@@ -189,9 +190,9 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
         tma_load_4d(smem + kSmemQ, &tm_q, bar(kBarQFull), 0, tile_m * kBlockM, hi, bi);
         for (int j = 0; j < prologue_tiles; ++j) {
             mbar_arrive_expect_tx(bar(kBarKFull + j), kTileBytes);
-            tma_load_4d(smem_k(j), &tm_k, bar(kBarKFull + j), 0, (kv_tile0 + j) * kBlockN, hi, bi);
+            tma_load_4d(smem_k(j), &tm_k, bar(kBarKFull + j), 0, (kv_tile0 + j) * kBlockN, hi, bk);
             mbar_arrive_expect_tx(bar(kBarVFull + j), kTileBytes);
-            tma_load_4d(smem_v(j), &tm_v, bar(kBarVFull + j), 0, (kv_tile0 + j) * kBlockN, hi, bi);
+            tma_load_4d(smem_v(j), &tm_v, bar(kBarVFull + j), 0, (kv_tile0 + j) * kBlockN, hi, bk);
         }
         LG_TRACE(13);
     }
@@ -223,10 +224,10 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
                 const uint32_t par = ((j / kStages) - 1) & 1;
                 mbar_wait_backoff(bar(kBarKEmpty + s), par, LG_ATTN_SPIN_NS);
                 mbar_arrive_expect_tx(bar(kBarKFull + s), kTileBytes);
-                tma_load_4d(smem_k(s), &tm_k, bar(kBarKFull + s), 0, (kv_tile0 + j) * kBlockN, hi, bi);
+                tma_load_4d(smem_k(s), &tm_k, bar(kBarKFull + s), 0, (kv_tile0 + j) * kBlockN, hi, bk);
                 mbar_wait_backoff(bar(kBarVEmpty + s), par, LG_ATTN_SPIN_NS);
                 mbar_arrive_expect_tx(bar(kBarVFull + s), kTileBytes);
-                tma_load_4d(smem_v(s), &tm_v, bar(kBarVFull + s), 0, (kv_tile0 + j) * kBlockN, hi, bi);
+                tma_load_4d(smem_v(s), &tm_v, bar(kBarVFull + s), 0, (kv_tile0 + j) * kBlockN, hi, bk);
             }
         } else if (warp == kSoftmaxWarps + 1 && lane == 0) {
             // ===================================================================== MMA issuer

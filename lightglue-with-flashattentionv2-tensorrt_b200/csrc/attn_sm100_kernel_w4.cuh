@@ -113,6 +113,7 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
     const int tile_m = blockIdx.x % tiles_m;
     const int bh = blockIdx.x / tiles_m;
     const int hi = bh % ol.heads, bi = bh / ol.heads;
+    const int bk = bi + ol.kv_shift >= ol.batch ? bi + ol.kv_shift - ol.batch : bi + ol.kv_shift;  // batch entry of K / V
     const int num_kv_tiles = (n_kv + kBlockN - 1) / kBlockN;
 
     if (warp == 4 && lane == 0) {
@@ -154,11 +155,11 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
                 if (j >= kStages) mbar_wait_backoff(bar(kBarKEmpty + s), par, LG_ATTN_SPIN_NS);
                 mbar_arrive_expect_tx(bar(kBarKFull + s), kTileBytes);
                 tma_load_4d(smem + kSmemK + s * kTileBytes, &tm_k, bar(kBarKFull + s), 0,
-                            j * kBlockN, hi, bi);
+                            j * kBlockN, hi, bk);
                 if (j >= kStages) mbar_wait_backoff(bar(kBarVEmpty + s), par, LG_ATTN_SPIN_NS);
                 mbar_arrive_expect_tx(bar(kBarVFull + s), kTileBytes);
                 tma_load_4d(smem + kSmemV + s * kTileBytes, &tm_v, bar(kBarVFull + s), 0,
-                            j * kBlockN, hi, bi);
+                            j * kBlockN, hi, bk);
             }
         } else if (warp == 5 && lane == 0) {
             // ===================================================================== MMA issuer

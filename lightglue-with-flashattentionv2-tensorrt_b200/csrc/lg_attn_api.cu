@@ -176,13 +176,13 @@ extern "C" int lg_attn_debug_read_trace(unsigned long long* dst, int reset_seq) 
 // Shared tail of both public launchers: tensor maps + kernel choice + launch.  FP16 Q/K/V only.
 static int launch_core(const void* qh, const void* kh, const void* vh, void* o, int batch, int heads, int n_q,
                        int n_kv, bool out_f32, const RowStrides& sq, const RowStrides& sk, const RowStrides& sv,
-                       const RowStrides& so, int device, cudaStream_t stream) {
+                       const RowStrides& so, int kv_shift, int device, cudaStream_t stream) {
     CUtensorMap tm_q, tm_k, tm_v;
     int rc;
     if ((rc = encode_rows_map(&tm_q, qh, n_q, heads, batch, sq)) != 0) return rc;
     if ((rc = encode_rows_map(&tm_k, kh, n_kv, heads, batch, sk)) != 0) return rc;
     if ((rc = encode_rows_map(&tm_v, vh, n_kv, heads, batch, sv)) != 0) return rc;
-    const OutLayout ol{so.batch, so.head, so.row, heads};
+    const OutLayout ol{so.batch, so.head, so.row, heads, batch, kv_shift};
     const long long bh_ll = static_cast<long long>(batch) * heads;
     const long long tiles_m_ll = (static_cast<long long>(n_q) + kBlockM - 1) / kBlockM;
     const int tiles_m = static_cast<int>(tiles_m_ll);
@@ -336,16 +336,17 @@ int lg_attn_hd64_launch(const void* q, const void* k, const void* v, void* o, in
     }
 
     const RowStrides cq = contiguous_strides(heads, n_q), ckv = contiguous_strides(heads, n_kv);
-    return launch_core(qh, kh, vh, o, batch, heads, n_q, n_kv, io_dtype != LG_ATTN_F16_F16, cq, ckv, ckv, cq, device,
+    return launch_core(qh, kh, vh, o, batch, heads, n_q, n_kv, io_dtype != LG_ATTN_F16_F16, cq, ckv, ckv, cq, 0, device,
                        stream);
 }
 
 int lg_attn_hd64_launch_strided(const void* q, const void* k, const void* v, void* o, int batch, int heads,
                                 int n_q, int n_kv, int out_f32, const lg_attn_strides* sq, const lg_attn_strides* sk,
-                                const lg_attn_strides* sv, const lg_attn_strides* so, void* stream_v) {
+                                const lg_attn_strides* sv, const lg_attn_strides* so, int kv_batch_shift, void* stream_v) {
     if (q == nullptr || k == nullptr || v == nullptr || o == nullptr) return LG_ATTN_EINVAL;
     if (sq == nullptr || sk == nullptr || sv == nullptr || so == nullptr) return LG_ATTN_EINVAL;
     if (batch <= 0 || heads <= 0 || n_q <= 0 || n_kv <= 0 || (out_f32 != 0 && out_f32 != 1)) return LG_ATTN_EINVAL;
+    if (kv_batch_shift < 0 || kv_batch_shift >= batch) return LG_ATTN_EINVAL;
     const long long tiles = (static_cast<long long>(n_q) + kBlockM - 1) / kBlockM;
     if (static_cast<long long>(batch) * heads * tiles > 2147483647LL) return LG_ATTN_EINVAL;
     const RowStrides rq{sq->batch, sq->head, sq->row}, rk{sk->batch, sk->head, sk->row};
@@ -360,7 +361,7 @@ int lg_attn_hd64_launch_strided(const void* q, const void* k, const void* v, voi
     if (e != cudaSuccess) return static_cast<int>(e);
     int rc = lg_attn_hd64_init_device(device);
     if (rc != 0) return rc;
-    return launch_core(q, k, v, o, batch, heads, n_q, n_kv, out_f32 != 0, rq, rk, rv, ro, device,
+    return launch_core(q, k, v, o, batch, heads, n_q, n_kv, out_f32 != 0, rq, rk, rv, ro, kv_batch_shift, device,
                        static_cast<cudaStream_t>(stream_v));
 }
 

@@ -21,7 +21,7 @@ B200-first layout (no translation of the reference's tensor choreography):
   (``x_true = x + c_l``) and folded into every consumer's bias, so the residual GEMM accumulates in place;
 * GEMMs are plain cuBLAS calls (``torch.addmm`` / ``torch.bmm``); everything else is the hand-written
   sm_100a code behind ``include/lg_attn.h`` / ``include/lg_match.h``: strided attention (36 calls per
-  pair), rotary in place, LayerNorm+GELU in place, assignment + mutual-NN filter;
+  pair, issued as 18 launches when both images carry the same keypoint count), rotary in place, LayerNorm+GELU in place, assignment + mutual-NN filter;
 * the whole forward for a (B, N0, N1) shape is captured once into a CUDA graph and replayed.
 
 There is no CPU path: tensors must be on a CUDA device and the C-ABI library must be built.
@@ -268,6 +268,10 @@ class _Plan:
         self.graph: torch.cuda.CUDAGraph | None = None
         self.launches = 0
 
+    def stacked(self, t: torch.Tensor) -> torch.Tensor:
+        """[2B, N, cols] view of both images' rows (only when N0 == N1): image 1 of pair b is entry B + b."""
+        return t[: 2 * self.b * self.n0].unflatten(0, (2 * self.b, self.n0))
+
     def image_rows(self, t: torch.Tensor, img: int) -> torch.Tensor:
         """[B, N_img, cols] view of the rows of one image."""
         n = self.n0 if img == 0 else self.n1
@@ -314,21 +318,33 @@ class PairMatcher:
             torch.addmm(self_blk.b_in, x, self_blk.w_in_t, out=p.proj)
             rotary_(p.proj, 2, p.cs)
             launches += 2
-            for img in (0, 1):
-                pj = p.image_rows(p.proj, img)
+            if p.n0 == p.n1:   # both images are one uniform [2B, N, .] batch: a single launch
+                pj = p.stacked(p.proj)
                 attention_strided(_heads_view(pj, 0), _heads_view(pj, DIM), _heads_view(pj, 2 * DIM),
-                                  _heads_view(p.image_rows(p.xc, img), DIM))
+                                  _heads_view(p.stacked(p.xc), DIM))
                 launches += 1
+            else:
+                for img in (0, 1):
+                    pj = p.image_rows(p.proj, img)
+                    attention_strided(_heads_view(pj, 0), _heads_view(pj, DIM), _heads_view(pj, 2 * DIM),
+                                      _heads_view(p.image_rows(p.xc, img), DIM))
+                    launches += 1
             launches += self._ffn(p, self_blk)
             # ---- cross attention, both directions (lightglue.py:188-206)
             pc = p.proj.view(-1)[: p.rows * 2 * DIM].view(p.rows, 2 * DIM)
             torch.addmm(cross_blk.b_in, x, cross_blk.w_in_t, out=pc)
             launches += 1
-            for img in (0, 1):
-                mine, other = p.image_rows(pc, img), p.image_rows(pc, 1 - img)
-                attention_strided(_heads_view(mine, 0), _heads_view(other, 0), _heads_view(other, DIM),
-                                  _heads_view(p.image_rows(p.xc, img), DIM))
+            if p.n0 == p.n1:   # batch entry b attends to entry (b + B) mod 2B: both directions in one launch
+                st = p.stacked(pc)
+                attention_strided(_heads_view(st, 0), _heads_view(st, 0), _heads_view(st, DIM),
+                                  _heads_view(p.stacked(p.xc), DIM), kv_batch_shift=p.b)
                 launches += 1
+            else:
+                for img in (0, 1):
+                    mine, other = p.image_rows(pc, img), p.image_rows(pc, 1 - img)
+                    attention_strided(_heads_view(mine, 0), _heads_view(other, 0), _heads_view(other, DIM),
+                                      _heads_view(p.image_rows(p.xc, img), DIM))
+                    launches += 1
             launches += self._ffn(p, cross_blk)
         # ---- assignment (lightglue.py:236-246) + filter (:253-276)
         torch.addmm(w.bf, x, w.wf_t, out=p.md)

@@ -70,12 +70,14 @@ def _bhr_strides(t: torch.Tensor) -> "B.Strides":
     return B.Strides(t.stride(0), t.stride(1), t.stride(2))
 
 
-def attention_strided(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
+def attention_strided(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, out: torch.Tensor,
+                      kv_batch_shift: int = 0) -> torch.Tensor:
     """Same attention on FP16 ``[B,H,rows,64]`` VIEWS with arbitrary batch / head / row strides
     (``lg_attn_hd64_launch_strided``): Q/K/V may point into packed projection outputs and ``out``
     (FP16 or FP32) into the buffer the next GEMM reads, so the head-split transposes and
     ``.contiguous()`` copies around every call in the reference (``lightglue.py:139-147,190-199``)
-    disappear.  The last dimension must be contiguous; strides multiples of 16 bytes."""
+    disappear.  The last dimension must be contiguous; strides multiples of 16 bytes.
+    ``kv_batch_shift``: batch entry ``b`` of ``q`` attends to entry ``(b + shift) % B`` of ``k`` / ``v``."""
     for t in (q, k, v, out):
         if not t.is_cuda:
             raise RuntimeError("lg_attn: tensors must live on a CUDA device (no CPU fallback)")
@@ -91,7 +93,8 @@ def attention_strided(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, out: to
     with torch.cuda.device(q.device):
         stream = torch.cuda.current_stream(q.device).cuda_stream
         rc = B.load().lg_attn_hd64_launch_strided(q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(),
-                                                  b, h, n, m, int(out.dtype == torch.float32), sq, sk, sv, so, stream)
+                                                  b, h, n, m, int(out.dtype == torch.float32), sq, sk, sv, so,
+                                                  int(kv_batch_shift), stream)
     B.check(rc, "lg_attn_hd64_launch_strided")
     return out
 

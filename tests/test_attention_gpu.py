@@ -301,3 +301,20 @@ def test_strided_rejects_bad_layouts(pkg):
         pkg.attention_strided(q.float(), q.float(), q.float(), o)
     with pytest.raises(RuntimeError):
         pkg.attention_strided(q.cpu(), q.cpu(), q.cpu(), o.cpu())
+
+
+@pytest.mark.parametrize("b2,n", [(2, 1024), (6, 200), (64, 256)])
+def test_strided_kv_batch_shift_is_cross_attention_in_one_launch(pkg, b2, n):
+    """Two image sets stacked along the batch dimension; shift = B/2 makes entry b attend to the other
+    image's K/V (CrossBlock.forward, lightglue.py:188-199): identical to two explicit launches."""
+    g = torch.Generator(device="cpu").manual_seed(b2 + n)
+    pc = torch.randn(b2, n, 512, generator=g).half().to(DEV)
+    qk = pc[..., :256].unflatten(-1, (4, 64)).transpose(1, 2)
+    v = pc[..., 256:].unflatten(-1, (4, 64)).transpose(1, 2)
+    out = torch.zeros(b2, n, 256, dtype=torch.float16, device=DEV)
+    o = out.unflatten(-1, (4, 64)).transpose(1, 2)
+    pkg.attention_strided(qk, qk, v, o, kv_batch_shift=b2 // 2)
+    want = pkg.attention(qk.contiguous(), qk.roll(-(b2 // 2), 0).contiguous(), v.roll(-(b2 // 2), 0).contiguous())
+    assert torch.equal(o, want)
+    with pytest.raises(pkg.LgAttnError):
+        pkg.attention_strided(qk, qk, v, o, kv_batch_shift=b2)
