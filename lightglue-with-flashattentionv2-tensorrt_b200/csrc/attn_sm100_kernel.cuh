@@ -22,11 +22,12 @@
 // TMEM columns: S [0,128) fp32 | O [128,192) fp32 | P [192,256) packed fp16 pairs.
 //
 // Split-KV (latency shapes, e.g. B=1 N=M=1024: 32 Q tiles for 148 SMs): `num_splits` CTAs of one
-// thread-block cluster share a Q tile and take consecutive KV ranges.  Each CTA stages its
-// unnormalised partial (O, m, l) in its own shared memory and bulk-copies (cp.async.bulk through
-// DSMEM, mbarrier complete_tx) the rows owned by each peer into that peer's receive area; every CTA
-// then rescales / sums / normalises / stores the 128/num_splits rows it owns.  One launch, no
-// workspace, no second kernel.
+// thread-block cluster share a Q tile and take consecutive KV ranges.  Every thread stores its slice
+// of the unnormalised partial (O, m, l) straight into the receive area of the cluster CTA that owns
+// the row (st.shared::cluster), a release/acquire cluster barrier publishes them, and every CTA then
+// rescales / sums / normalises / stores the 128/num_splits rows it owns.  One launch, no workspace,
+// no second kernel.  (Measured timeline, tools/trace_timeline.py: the 24 KiB a CTA sends cross at the
+// ~20 B/clk DSMEM rate, ~1.2 us — the largest single item after the two KV tiles themselves.)
 //
 // Programmatic dependent launch: the prologue (barrier init, TMEM alloc, descriptor prefetch) runs
 // before griddepcontrol.wait, so in a back-to-back chain it overlaps the previous kernel's tail.
@@ -86,7 +87,7 @@ enum : uint32_t {
 constexpr uint32_t kSmemTmemSlot = kSmemBar + 8 * kNumBars;
 // row-max / row-sum exchange between the two column halves: [parity][half][row] floats
 constexpr uint32_t kSmemExch = (kSmemTmemSlot + 16 + 15u) & ~15u;
-// split-KV: this CTA's own per-row (m, l), source of the bulk copies to the peers
+// split-KV: (unused since the direct-store combine; kept so the receive areas keep their offsets)
 constexpr uint32_t kSmemStat = kSmemExch + 2 * 2 * kBlockM * 4;
 // split-KV receive area, (m, l) part: [source split][owned row] float2  (1 KiB for any split count)
 constexpr uint32_t kSmemCombStat = kSmemStat + kBlockM * 8;
@@ -181,7 +182,6 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
         mbar_init(bar(kBarPVDone), 1);
         mbar_init(bar(kBarComb), 1);
         fence_mbar_init();
-        if (num_splits > 1) mbar_arrive_expect_tx(bar(kBarComb), kCombBytes);
         // Everything above is independent of earlier kernels in the stream; the loads are not.
         pdl_wait_prior_grids();
         LG_TRACE(12);
@@ -398,36 +398,29 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
 
         if (num_splits > 1) {
             // ================================================================= split-KV combine
-            // 1. stage the UNNORMALISED partial O row (fp32, [128][64]) and its (m, l) locally
-            if (half == 0) st_shared_v2f(smem + kSmemStat + row * 8, m_used, l_row);
-#pragma unroll
-            for (int c = 0; c < 8; ++c)
-                st_shared_v4(smem + kSmemStage + row * 256 + (((half * 8 + c) ^ (row & 15)) << 4), orow[4 * c + 0],
-                             orow[4 * c + 1], orow[4 * c + 2], orow[4 * c + 3]);
-            fence_proxy_async_smem();                      // generic-proxy writes -> bulk-copy engine
-            if (threadIdx.x == 0) LG_TRACE(10);
-            cluster_wait();                                // barrier #1: every peer's kBarComb is armed
-            asm volatile("bar.sync 5, 256;" ::: "memory");  // all softmax threads have staged
-            if (threadIdx.x == 0) LG_TRACE(11);
-            // 2. one thread bulk-copies, to every cluster CTA, the block of rows that CTA owns
+            // 1. every thread stores its UNNORMALISED partial O slice (fp32, 32 of the row's 64 columns) and
+            //    the row's (m, l) straight into the receive area of the cluster CTA that owns the row
+            //    (st.shared::cluster, 16-B chunks XOR-swizzled by owned row).  Direct DSMEM stores replace a
+            //    local staging pass + bulk copies + a transaction barrier (7.8 -> 7.55 us per B=1 launch).
             const int rows_per = kBlockM / num_splits;
             const uint32_t recv_o = smem + kSmemCombO;
-            if (threadIdx.x == 0) {
-                for (int owner = 0; owner < num_splits; ++owner) {
-                    const uint32_t peer_bar = dsmem_addr(bar(kBarComb), owner);
-                    bulk_copy_smem_to_cluster(dsmem_addr(recv_o + split * rows_per * 256, owner),
-                                              smem + kSmemStage + owner * rows_per * 256, rows_per * 256, peer_bar);
-                    bulk_copy_smem_to_cluster(dsmem_addr(smem + kSmemCombStat + split * rows_per * 8, owner),
-                                              smem + kSmemStat + owner * rows_per * 8, rows_per * 8, peer_bar);
-                }
-                LG_TRACE(6);
+            const int owner = row / rows_per, lr_mine = row - owner * rows_per;
+            const int slot_mine = split * rows_per + lr_mine;
+            cluster_wait();                                // barrier #1: every peer CTA is running
+            if (threadIdx.x == 0) LG_TRACE(11);
+            {
+                const uint32_t dst_o = dsmem_addr(recv_o + slot_mine * 256, owner);
+#pragma unroll
+                for (int c = 0; c < 8; ++c)
+                    st_dsmem_v4(dst_o + (((half * 8 + c) ^ (lr_mine & 15)) << 4), orow[4 * c + 0], orow[4 * c + 1],
+                                orow[4 * c + 2], orow[4 * c + 3]);
+                if (half == 0) st_dsmem_v2(dsmem_addr(smem + kSmemCombStat + slot_mine * 8, owner), m_used, l_row);
             }
-            // 3. wait until every split's block for the rows this CTA owns has landed, then combine
-            mbar_wait(bar(kBarComb), 0);
-            // cluster barrier #2 (exit): nobody may leave while a peer's bulk copy could still be reading
-            // its shared memory; once every CTA has seen its own receive barrier complete, all copies
-            // are done.  Arrive here, wait after the stores.
+            if (threadIdx.x == 0) LG_TRACE(6);
+            // 2. cluster barrier #2 (release / acquire): every split's slices for the rows this CTA owns have
+            //    landed.  After it nobody touches a peer's shared memory, so CTAs may exit independently.
             cluster_arrive();
+            cluster_wait();
             if (threadIdx.x == 0) LG_TRACE(7);
             for (int task = threadIdx.x; task < rows_per * 8; task += kSoftmaxWarps * 32) {
                 const int lr = task >> 3;  // owned row
@@ -482,7 +475,6 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
                     st_global_v4(reinterpret_cast<float*>(out) + off + 4, w1);
                 }
             }
-            cluster_wait();
         } else if constexpr (!kOutF32) {
             const float inv_l = 1.0f / l_row;
             const uint32_t stage = smem + kSmemStage + warp * (32 * 64);  // 32 rows x 64 B per warp
