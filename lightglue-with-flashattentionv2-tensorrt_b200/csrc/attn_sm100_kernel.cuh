@@ -408,14 +408,27 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
             const int slot_mine = split * rows_per + lr_mine;
             cluster_wait();                                // barrier #1: every peer CTA is running
             if (threadIdx.x == 0) LG_TRACE(11);
-            {
+            if constexpr (kOutF32) {
                 const uint32_t dst_o = dsmem_addr(recv_o + slot_mine * 256, owner);
 #pragma unroll
                 for (int c = 0; c < 8; ++c)
                     st_dsmem_v4(dst_o + (((half * 8 + c) ^ (lr_mine & 15)) << 4), orow[4 * c + 0], orow[4 * c + 1],
                                 orow[4 * c + 2], orow[4 * c + 3]);
-                if (half == 0) st_dsmem_v2(dsmem_addr(smem + kSmemCombStat + slot_mine * 8, owner), m_used, l_row);
+            } else {
+                // FP16 output: the partial travels as FP16 of O_s / l_s (same magnitude as the result, so the
+                // extra rounding is of the order of the output rounding itself) — half the DSMEM bytes, which
+                // cross at only ~20 B/clk per SM
+                const float inv_own = 1.0f / l_row;
+                const uint32_t dst_o = dsmem_addr(recv_o + slot_mine * 128, owner);
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+                    st_dsmem_v4(dst_o + (((half * 4 + c) ^ (lr_mine & 7)) << 4),
+                                pack_half2(__uint_as_float(orow[8 * c + 0]) * inv_own, __uint_as_float(orow[8 * c + 1]) * inv_own),
+                                pack_half2(__uint_as_float(orow[8 * c + 2]) * inv_own, __uint_as_float(orow[8 * c + 3]) * inv_own),
+                                pack_half2(__uint_as_float(orow[8 * c + 4]) * inv_own, __uint_as_float(orow[8 * c + 5]) * inv_own),
+                                pack_half2(__uint_as_float(orow[8 * c + 6]) * inv_own, __uint_as_float(orow[8 * c + 7]) * inv_own));
             }
+            if (half == 0) st_dsmem_v2(dsmem_addr(smem + kSmemCombStat + slot_mine * 8, owner), m_used, l_row);
             if (threadIdx.x == 0) LG_TRACE(6);
             // 2. cluster barrier #2 (release / acquire): every split's slices for the rows this CTA owns have
             //    landed.  After it nobody touches a peer's shared memory, so CTAs may exit independently.
@@ -438,9 +451,19 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
                         ms[sp] = st.x;
                         ls[sp] = st.y;
                         m_glob = fmaxf(m_glob, st.x);
-                        const uint32_t src = recv_o + slot * 256;
-                        v0[sp] = ld_shared_v4f(src + (((2 * cp) ^ (lr & 15)) << 4));
-                        v1[sp] = ld_shared_v4f(src + (((2 * cp + 1) ^ (lr & 15)) << 4));
+                        if constexpr (kOutF32) {
+                            const uint32_t src = recv_o + slot * 256;
+                            v0[sp] = ld_shared_v4f(src + (((2 * cp) ^ (lr & 15)) << 4));
+                            v1[sp] = ld_shared_v4f(src + (((2 * cp + 1) ^ (lr & 15)) << 4));
+                        } else {
+                            const uint4 hv = ld_shared_v4(recv_o + slot * 128 + ((cp ^ (lr & 7)) << 4));
+                            const float2 f0 = __half22float2(*reinterpret_cast<const __half2*>(&hv.x));
+                            const float2 f1 = __half22float2(*reinterpret_cast<const __half2*>(&hv.y));
+                            const float2 f2 = __half22float2(*reinterpret_cast<const __half2*>(&hv.z));
+                            const float2 f3 = __half22float2(*reinterpret_cast<const __half2*>(&hv.w));
+                            v0[sp] = make_float4(f0.x, f0.y, f1.x, f1.y);
+                            v1[sp] = make_float4(f2.x, f2.y, f3.x, f3.y);
+                        }
                     }
                 }
                 float l_tot = 0.f;
@@ -448,8 +471,9 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
 #pragma unroll
                 for (int sp = 0; sp < kMaxSplits; ++sp) {
                     if (sp < num_splits) {
-                        const float a = ex2_approx((ms[sp] - m_glob) * kScaleLog2);
+                        float a = ex2_approx((ms[sp] - m_glob) * kScaleLog2);
                         l_tot = fmaf(ls[sp], a, l_tot);
+                        if constexpr (!kOutF32) a *= ls[sp];   // FP16 partials arrive normalised by their own l
                         acc[0] = fmaf(v0[sp].x, a, acc[0]); acc[1] = fmaf(v0[sp].y, a, acc[1]);
                         acc[2] = fmaf(v0[sp].z, a, acc[2]); acc[3] = fmaf(v0[sp].w, a, acc[3]);
                         acc[4] = fmaf(v1[sp].x, a, acc[4]); acc[5] = fmaf(v1[sp].y, a, acc[5]);
