@@ -388,7 +388,7 @@ def run_ours(args) -> None:
     qh.copy_(q)
     kh.copy_(k)
     vh.copy_(v)
-    sess = pkg.HostSession(B, H, N, M, pkg.F16_F16, n_slots=4, device=local)
+    sess = pkg.HostSession(B, H, N, M, pkg.F16_F16, n_slots=int(os.environ.get("LG_E2E_SLOTS", "4")), device=local)
     qs, ks, vs, os_ = q[0].numel() * 2, k[0].numel() * 2, v[0].numel() * 2, o[0].numel() * 2
 
     def e2e_step():
