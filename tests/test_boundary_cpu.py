@@ -32,6 +32,28 @@ def test_header_symbols_are_exported(pkg, lib):
     assert lib.lg_attn_version() == 1
 
 
+def test_glue_header_symbols_are_exported(pkg, lib):
+    """include/lg_match.h (glue kernels either side of the path): every declared symbol is exported and bound."""
+    header = (ROOT / "include" / "lg_match.h").read_text()
+    declared = set(re.findall(r"^(?:int|size_t)\s+(lg_match_[a-z0-9_]+)\s*\(", header, flags=re.M))
+    assert declared == set(pkg._binding.MATCH_ABI_SYMBOLS)
+    out = subprocess.run(["nm", "-D", "--defined-only", str(pkg._binding.lib_path())], capture_output=True, text=True,
+                         check=True).stdout
+    exported = set(re.findall(r" T (\w+)", out))
+    for sym in declared:
+        assert sym in exported, sym
+        assert getattr(lib, sym) is not None
+    # argument errors are reported, never fatal, and need no GPU
+    assert lib.lg_match_posenc(None, None, None, 4, None) == pkg._binding.EINVAL
+    assert lib.lg_match_rotary(None, 4, 768, 2, None, None) == pkg._binding.EINVAL
+    assert lib.lg_match_layernorm_gelu(None, 4, 512, None, None, 1e-5, None) == pkg._binding.EINVAL
+    assert lib.lg_match_assign_workspace_bytes(0, 8, 8) == 0
+    assert lib.lg_match_assign_workspace_bytes(2, 300, 200) >= 4 * 2 * (3 * 300 + 2 * 200)
+    one = ctypes.c_void_p(256)
+    assert lib.lg_match_assign(one, one, one, 1, 1, 8, 8, 0.1, one, one, None, None, 0, None) == pkg._binding.EWORKSPACE
+    assert lib.lg_match_assign_launches(0) == 7 and lib.lg_match_assign_launches(1) == 8
+
+
 def test_library_is_sm100a_native(pkg):
     """The shipped kernel is tcgen05/TMA code for sm_100a (SASS mnemonics, B200_PROFILING.md)."""
     sass = subprocess.run(["cuobjdump", "-sass", str(pkg._binding.lib_path())], capture_output=True, text=True).stdout
