@@ -266,6 +266,21 @@ def pairs_section(pkg, torch, dist, dev, rank: int, world: int, steps: int, with
         del kp_d, d_d, plan
         matcher._plans.clear()
         torch.cuda.empty_cache()
+    # configs[3]: one 1x1024x1024 pair at a time (the reference engine's shape), CUDA-graph replay latency
+    kp_h, d_h = synth_features_host(torch, 1, 1024, 4242 + rank)
+    kp_d, d_d = kp_h.to(dev), d_h.to(dev)
+    for _ in range(5):
+        matcher.match(kp_d[0], kp_d[1], d_d[0], d_d[1])
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 50
+    e0.record()
+    for _ in range(reps):
+        matcher.match(kp_d[0], kp_d[1], d_d[0], d_d[1])
+    e1.record()
+    torch.cuda.synchronize()
+    out["single_pair_1024"] = {"ms_per_pair": e0.elapsed_time(e1) / reps, "unit": "ms", "pairs_per_forward": 1,
+                               "note": "B=1 CUDA-graph replay incl. input copies into the plan; reference engine on Jetson Orin: 40.39 ms (BASELINE.md)"}
     return out
 
 

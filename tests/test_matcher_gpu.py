@@ -185,3 +185,15 @@ def test_matcher_refuses_cpu_tensors(pkg):
     f = mo.synth_pair(1, 8, 8)
     with pytest.raises(RuntimeError):
         matcher.match(*f)
+
+
+def test_nine_layer_ragged_pair_matches_oracle(pkg):
+    """Full depth (9 layers), ragged and non-tile-multiple keypoint counts, against the FP32 CPU oracle."""
+    sd = pkg.reference_init_state_dict(0, 9)
+    f = mo.synth_pair(31337, 600, 517)
+    out = pkg.PairMatcher(sd, n_layers=9, threshold=0.0, device=DEV).match(*(t.to(DEV) for t in f), want_scores=True)
+    want = mo.forward(sd, *f, n_layers=9, threshold=0.0)
+    err = (out["scores"].cpu() - want["scores"]).abs()
+    assert float(err.max()) <= TOL_SCORES_MAX and float(err.mean()) <= TOL_SCORES_MEAN
+    agree, gap = _agreement(want["scores"], out["matches0"])
+    assert agree >= MIN_MATCH_AGREEMENT and gap < 0.1
