@@ -396,9 +396,10 @@ def run_ours(args) -> None:
 
     # ---- end-to-end: host buffers through the C-ABI session (H2D + launch + D2H per problem)
     e2e_steps = max(1, min(args.steps, 10))
-    qh = torch.empty(CALLS, B, H, N, D, dtype=torch.float16).pin_memory()
-    kh = torch.empty(CALLS, B, H, M, D, dtype=torch.float16).pin_memory()
-    vh = torch.empty(CALLS, B, H, M, D, dtype=torch.float16).pin_memory()
+    # one pinned host buffer per step: problem i holds q | k | v adjacently (the session then moves them with one copy)
+    assert N == M
+    qkvh = torch.empty(CALLS, 3, B, H, N, D, dtype=torch.float16).pin_memory()
+    qh, kh, vh = qkvh[:, 0], qkvh[:, 1], qkvh[:, 2]
     oh = torch.empty(CALLS, B, H, N, D, dtype=torch.float16).pin_memory()
     qh.copy_(q)
     kh.copy_(k)
@@ -408,7 +409,8 @@ def run_ours(args) -> None:
 
     def e2e_step():
         for i in range(CALLS):
-            sess.submit(qh.data_ptr() + i * qs, kh.data_ptr() + i * ks, vh.data_ptr() + i * vs, oh.data_ptr() + i * os_, B, N, M)
+            base = qkvh.data_ptr() + i * (qs + ks + vs)
+            sess.submit(base, base + qs, base + qs + ks, oh.data_ptr() + i * os_, B, N, M)
         sess.sync()
 
     for _ in range(3):
@@ -460,7 +462,8 @@ def run_ours(args) -> None:
                          "hbm_floor_us": BYTES_PER_CALL / (peaks["hbm_gbs"] * 1e9) * 1e6,
                          "note": "latency-bound shape: 32 Q tiles x 4 KV splits = 128 CTAs on 148 SMs; duration = timed region / launches (includes launch gaps)"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": CALLS * (qs + ks + vs), "d2h_bytes_per_step": CALLS * os_,
-                    "steps": e2e_steps, "timing": "host wall clock around submit+sync, pinned host buffers, 4 streams"},
+                    "steps": e2e_steps, "timing": "host wall clock around submit+sync, pinned host buffers, 4 streams",
+                    "note": "PCIe-bound: 2 MiB cross the Gen5 x16 link per 1.07 GFLOP problem (tools/e2e_probe.py: host issue 13 us, total 45 us per problem = 46 GB/s)"},
             "clocks": clocks,
             "extra": extra,
             "pairs": pairs,

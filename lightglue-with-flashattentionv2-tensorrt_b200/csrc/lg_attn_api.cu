@@ -464,9 +464,18 @@ int lg_attn_session_submit(lg_attn_session* s, const void* q_host, const void* k
     const size_t out_es = (s->io_dtype == LG_ATTN_F16_F16) ? 2 : 4;
     const size_t bh = static_cast<size_t>(batch) * s->heads;
     cudaStream_t st = s->streams[i];
-    e = cudaMemcpyAsync(dq, q_host, bh * n_q * kHeadDim * in_es, cudaMemcpyHostToDevice, st);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(dk, k_host, bh * n_kv * kHeadDim * in_es, cudaMemcpyHostToDevice, st);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(dv, v_host, bh * n_kv * kHeadDim * in_es, cudaMemcpyHostToDevice, st);
+    const size_t qb = bh * n_q * kHeadDim * in_es, kvb = bh * n_kv * kHeadDim * in_es;
+    const uint8_t* qh8 = static_cast<const uint8_t*>(q_host);
+    if (static_cast<const uint8_t*>(k_host) == qh8 + qb && static_cast<const uint8_t*>(v_host) == qh8 + qb + kvb &&
+        qb == s->q_bytes && kvb == s->kv_bytes) {
+        // q | k | v adjacent in host memory and the slot is exactly this shape: one 3x larger PCIe transfer
+        // (0.5 MiB copies reach ~2/3 of the link rate of 1.5 MiB ones on this box)
+        e = cudaMemcpyAsync(dq, q_host, qb + 2 * kvb, cudaMemcpyHostToDevice, st);
+    } else {
+        e = cudaMemcpyAsync(dq, q_host, qb, cudaMemcpyHostToDevice, st);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(dk, k_host, kvb, cudaMemcpyHostToDevice, st);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(dv, v_host, kvb, cudaMemcpyHostToDevice, st);
+    }
     if (e != cudaSuccess) return static_cast<int>(e);
     int rc = lg_attn_hd64_launch(dq, dk, dv, dout, batch, s->heads, n_q, n_kv, s->io_dtype,
                                  s->ws_bytes ? dws : nullptr, s->ws_bytes, st);

@@ -31,7 +31,10 @@ using namespace ptx;
 // softmax(x/8): exp(0.125*(s-m)) = exp2((s-m) * 0.125 * log2(e))
 constexpr float kScaleLog2 = 0.125f * 1.4426950408889634f;
 // lazy rescale: keep the stale row max while the new one is < 2^kTau larger (P stays < 2^8 in fp16)
-constexpr float kTau = 8.0f;
+#ifndef LG_ATTN_TAU
+#define LG_ATTN_TAU 8.0f
+#endif
+constexpr float kTau = LG_ATTN_TAU;
 
 // ---- polynomial exp2 on the FMA pipes -----------------------------------------------------------
 // x = s*c - m*c lies in (-inf, kTau].  y = sat((x + 120) / 128) in [0, 1] comes out of ONE saturating

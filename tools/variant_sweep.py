@@ -23,6 +23,9 @@ VARIANTS = {
     "p3": ["-DLG_ATTN_POLY_OF_8=3"],
     "p2_scalar_scale": ["-DLG_ATTN_PACKED_SCALE=0"],
     "p2_scalar_sum": ["-DLG_ATTN_PACKED_SUM=0"],
+    "spin32": ["-DLG_ATTN_SPIN_NS=32"],
+    "spin128": ["-DLG_ATTN_SPIN_NS=128"],
+    "tau6": ["-DLG_ATTN_TAU=6.0f"],
 }
 
 
