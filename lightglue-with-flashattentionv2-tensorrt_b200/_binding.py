@@ -52,6 +52,19 @@ MATCH_ABI_SYMBOLS = (
     "lg_match_assign_launches",
 )
 
+# every symbol include/lg_matcher.h declares
+MATCHER_ABI_SYMBOLS = (
+    "lg_matcher_create",
+    "lg_matcher_blob_bytes",
+    "lg_matcher_plan",
+    "lg_matcher_match",
+    "lg_matcher_match_host",
+    "lg_matcher_launches",
+    "lg_matcher_destroy",
+)
+ECUBLAS = 100010
+EBLOB = 100011
+
 _lib = None
 
 
@@ -132,6 +145,20 @@ def load() -> ctypes.CDLL:
     lib.lg_match_assign.argtypes = [P, P, P, LL, I, I, I, F, P, P, P, P, ctypes.c_size_t, P]
     lib.lg_match_assign_launches.restype = I
     lib.lg_match_assign_launches.argtypes = [I]
+    lib.lg_matcher_create.restype = I
+    lib.lg_matcher_create.argtypes = [ctypes.POINTER(ctypes.c_void_p), I, I, P, ctypes.c_size_t, F]
+    lib.lg_matcher_blob_bytes.restype = ctypes.c_size_t
+    lib.lg_matcher_blob_bytes.argtypes = [I]
+    lib.lg_matcher_plan.restype = I
+    lib.lg_matcher_plan.argtypes = [P, I, I, I]
+    lib.lg_matcher_match.restype = I
+    lib.lg_matcher_match.argtypes = [P, P, P, P, P, I, I, I, P, P, P]
+    lib.lg_matcher_match_host.restype = I
+    lib.lg_matcher_match_host.argtypes = [P, P, P, P, P, I, I, I, P, P]
+    lib.lg_matcher_launches.restype = I
+    lib.lg_matcher_launches.argtypes = [P]
+    lib.lg_matcher_destroy.restype = None
+    lib.lg_matcher_destroy.argtypes = [P]
     _lib = lib
     return lib
 

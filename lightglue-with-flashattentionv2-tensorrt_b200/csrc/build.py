@@ -19,12 +19,12 @@ CSRC = Path(__file__).resolve().parent
 BUILD = CSRC / "build"
 LIB = BUILD / "liblightglue_attention_plugin.so"
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
-SOURCES = [CSRC / "lg_attn_api.cu", CSRC / "lg_match_kernels.cu", CSRC / "plugin" / "lightglue_attention_plugin.cpp",
+SOURCES = [CSRC / "lg_attn_api.cu", CSRC / "lg_match_kernels.cu", CSRC / "lg_matcher.cu", CSRC / "plugin" / "lightglue_attention_plugin.cpp",
            CSRC / "plugin" / "mock_trt_host.cpp"]
 HEADERS = [CSRC / "attn_sm100_kernel.cuh", CSRC / "attn_sm100_kernel_w4.cuh", CSRC / "softmax_math.cuh",
            CSRC / "cvt_f32_f16.cuh", CSRC / "attn_sm100.h", CSRC / "ptx_sm100.cuh",
            CSRC / "plugin" / "lightglue_attention_plugin.h", CSRC / "plugin" / "mock_nvinfer" / "NvInfer.h",
-           CSRC.parent.parent / "include" / "lg_attn.h", CSRC.parent.parent / "include" / "lg_match.h"]
+           CSRC.parent.parent / "include" / "lg_attn.h", CSRC.parent.parent / "include" / "lg_match.h", CSRC.parent.parent / "include" / "lg_matcher.h"]
 
 
 def find_tensorrt_include() -> Path | None:
@@ -62,7 +62,7 @@ def build(force: bool = False, verbose: bool = False, defs: list[str] | None = N
     lib.parent.mkdir(parents=True, exist_ok=True)
     trt_inc = find_tensorrt_include()
     inc = ["-I", str(trt_inc)] if trt_inc else ["-I", str(CSRC / "plugin" / "mock_nvinfer")]
-    libs = ["-lnvinfer"] if trt_inc else []
+    libs = (["-lnvinfer"] if trt_inc else []) + ["-lcublasLt"]
     cmd = [nvcc(), *ARCH, "-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-fvisibility=default",
            "-shared", "-cudart", "shared", *inc, *(defs or []), "-o", str(lib), *map(str, SOURCES), *libs]
     if verbose:

@@ -512,6 +512,8 @@ const char* lg_attn_error_string(int code) {
         case LG_ATTN_EWORKSPACE: return "lg_attn: workspace missing or too small";
         case LG_ATTN_EDRIVER: return "lg_attn: cuTensorMapEncodeTiled unavailable or failed";
         case LG_ATTN_EARCH: return "lg_attn: device is not compute capability 10.x (sm_100a required)";
+        case 100010: return "lg_matcher: a cuBLASLt call failed";
+        case 100011: return "lg_matcher: malformed weight blob";
         default: return cudaGetErrorString(static_cast<cudaError_t>(code));
     }
 }

@@ -165,6 +165,91 @@ class MatcherWeights:
         self.c_final = vec(c)  # add to the stored residual stream to obtain lightglue_descriptors_{0,1}
 
 
+def weights_blob(w: "MatcherWeights") -> bytes:
+    """The packed weight blob of the native engine (include/lg_matcher.h; layout in csrc/lg_matcher.cu):
+    header, posenc.Wr, per layer the self then the cross block (w_in_t, b_in, w1_t, b1, gamma, beta, w2_t),
+    final projection, its bias, accumulated bias c — every array padded to 256 bytes."""
+    import struct
+
+    import numpy as np
+
+    def pad(b: bytes) -> bytes:
+        return b + b"\0" * (-len(b) % 256)
+
+    def arr(t: torch.Tensor) -> bytes:
+        return pad(np.ascontiguousarray(t.detach().cpu().numpy()).tobytes())
+
+    out = [pad(b"LGMATCH1" + struct.pack("<ii", w.n_layers, 0)), arr(w.wr)]
+    for self_blk, cross_blk in w.blocks:
+        for blk in (self_blk, cross_blk):
+            out += [arr(blk.w_in_t), arr(blk.b_in), arr(blk.w1_t), arr(blk.b1), arr(blk.gamma), arr(blk.beta), arr(blk.w2_t)]
+    out += [arr(w.wf_t), arr(w.bf), arr(w.c_final)]
+    return b"".join(out)
+
+
+class NativeMatcher:
+    """ctypes front end of the native C++ engine (``lg_matcher_*``): same contract as ``PairMatcher.match`` but no
+    torch in the call path — device pointers (or pinned host buffers) in, matches0 / mscores0 out."""
+
+    def __init__(self, state_dict: dict | None = None, n_layers: int = 9, device: int = 0, threshold: float = 0.1,
+                 seed: int = 0):
+        import ctypes
+
+        self._lib = B.load()
+        sd = state_dict if state_dict is not None else reference_init_state_dict(seed, n_layers)
+        blob = weights_blob(MatcherWeights(sd, n_layers, device="cpu"))
+        if len(blob) != self._lib.lg_matcher_blob_bytes(n_layers):
+            raise RuntimeError("weight blob size mismatch")
+        self._h = ctypes.c_void_p()
+        self.device = device
+        B.check(self._lib.lg_matcher_create(ctypes.byref(self._h), device, n_layers, blob, len(blob), threshold),
+                "lg_matcher_create")
+
+    def plan(self, pairs: int, n0: int, n1: int) -> int:
+        B.check(self._lib.lg_matcher_plan(self._h, pairs, n0, n1), "lg_matcher_plan")
+        return self._lib.lg_matcher_launches(self._h)
+
+    def match(self, kpts0: torch.Tensor, kpts1: torch.Tensor, desc0: torch.Tensor, desc1: torch.Tensor) -> dict:
+        """CUDA tensors: kpts FP32 [B,N,2], desc FP16 [B,N,256] (contiguous).  Enqueued on the current stream."""
+        b, n0, _ = kpts0.shape
+        n1 = kpts1.shape[1]
+        for t, dt in ((kpts0, torch.float32), (kpts1, torch.float32), (desc0, torch.float16), (desc1, torch.float16)):
+            if not t.is_cuda or t.dtype != dt or not t.is_contiguous():
+                raise ValueError("NativeMatcher.match: contiguous CUDA tensors, kpts float32 and desc float16")
+        m0 = torch.empty(b, n0, dtype=torch.int32, device=kpts0.device)
+        ms = torch.empty(b, n0, dtype=torch.float32, device=kpts0.device)
+        with torch.cuda.device(kpts0.device):
+            B.check(self._lib.lg_matcher_match(self._h, kpts0.data_ptr(), kpts1.data_ptr(), desc0.data_ptr(), desc1.data_ptr(),
+                                               b, n0, n1, m0.data_ptr(), ms.data_ptr(),
+                                               torch.cuda.current_stream(kpts0.device).cuda_stream), "lg_matcher_match")
+        return {"matches0": m0, "mscores0": ms}
+
+    def match_host(self, kpts0, kpts1, desc0, desc1):
+        """numpy arrays / pinned CPU tensors in, numpy arrays out (H2D, forward, D2H, synchronise)."""
+        import numpy as np
+
+        k0, k1 = (np.ascontiguousarray(np.asarray(t), dtype=np.float32) for t in (kpts0, kpts1))
+        d0, d1 = (np.ascontiguousarray(np.asarray(t), dtype=np.float16) for t in (desc0, desc1))
+        b, n0, _ = k0.shape
+        n1 = k1.shape[1]
+        m0 = np.empty((b, n0), dtype=np.int32)
+        ms = np.empty((b, n0), dtype=np.float32)
+        B.check(self._lib.lg_matcher_match_host(self._h, k0.ctypes.data, k1.ctypes.data, d0.ctypes.data, d1.ctypes.data,
+                                                b, n0, n1, m0.ctypes.data, ms.ctypes.data), "lg_matcher_match_host")
+        return {"matches0": m0, "mscores0": ms}
+
+    def close(self) -> None:
+        if getattr(self, "_h", None):
+            self._lib.lg_matcher_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 # ------------------------------------------------------------------------------------------------
 # glue-kernel wrappers (device pointers + current stream; include/lg_match.h)
 # ------------------------------------------------------------------------------------------------

@@ -54,6 +54,27 @@ def test_glue_header_symbols_are_exported(pkg, lib):
     assert lib.lg_match_assign_launches(0) == 7 and lib.lg_match_assign_launches(1) == 8
 
 
+def test_native_matcher_header_symbols_and_blob(pkg, lib):
+    """include/lg_matcher.h (native C++ pair-matcher engine): symbols, blob size contract, blob validation."""
+    header = (ROOT / "include" / "lg_matcher.h").read_text()
+    declared = set(re.findall(r"^(?:int|size_t|void)\s+(lg_matcher_[a-z0-9_]+)\s*\(", header, flags=re.M))
+    assert declared == set(pkg._binding.MATCHER_ABI_SYMBOLS)
+    out = subprocess.run(["nm", "-D", "--defined-only", str(pkg._binding.lib_path())], capture_output=True, text=True,
+                         check=True).stdout
+    exported = set(re.findall(r" T (\w+)", out))
+    assert declared <= exported
+    m = pkg.matcher
+    for n_layers in (1, 3):
+        w = m.MatcherWeights(m.reference_init_state_dict(2, n_layers), n_layers, device="cpu")
+        assert len(m.weights_blob(w)) == lib.lg_matcher_blob_bytes(n_layers)
+    h = ctypes.c_void_p()
+    blob = m.weights_blob(w)
+    assert lib.lg_matcher_create(ctypes.byref(h), 0, 3, blob, len(blob) - 256, 0.1) == pkg._binding.EBLOB
+    assert lib.lg_matcher_create(ctypes.byref(h), 0, 3, b"XXXXXXXX" + blob[8:], len(blob), 0.1) == pkg._binding.EBLOB
+    assert lib.lg_matcher_create(ctypes.byref(h), 0, 0, blob, len(blob), 0.1) == pkg._binding.EINVAL
+    assert lib.lg_matcher_launches(None) == 0
+
+
 def test_library_is_sm100a_native(pkg):
     """The shipped kernel is tcgen05/TMA code for sm_100a (SASS mnemonics, B200_PROFILING.md)."""
     sass = subprocess.run(["cuobjdump", "-sass", str(pkg._binding.lib_path())], capture_output=True, text=True).stdout

@@ -197,3 +197,49 @@ def test_nine_layer_ragged_pair_matches_oracle(pkg):
     assert float(err.max()) <= TOL_SCORES_MAX and float(err.mean()) <= TOL_SCORES_MEAN
     agree, gap = _agreement(want["scores"], out["matches0"])
     assert agree >= MIN_MATCH_AGREEMENT and gap < 0.1
+
+
+# ------------------------------------------------------------------------------------------------ native C++ engine
+def test_native_engine_reproduces_reference_fixture(pkg, golden_dir):
+    """lg_matcher_* (C++ / cuBLASLt, no torch in the call path) against the reference-generated fixture: the
+    match set must agree with the reference's, and with the Python-driven matcher on the same weights."""
+    z = np.load(golden_dir / "matcher_forward.npz")
+    for name in sorted({k.split(".")[0] for k in z.files}):
+        wseed, n_layers, fseed, n0, n1 = (int(v) for v in z[f"{name}.meta"])
+        sd = pkg.reference_init_state_dict(wseed, n_layers)
+        eng = pkg.NativeMatcher(sd, n_layers=n_layers, threshold=0.0, device=0)
+        k0, k1, d0, d1 = mo.synth_pair(fseed, n0, n1)
+        out = eng.match(k0.to(DEV), k1.to(DEV), d0.half().to(DEV), d1.half().to(DEV))
+        ref_scores = torch.from_numpy(z[f"{name}.scores"])
+        agree, gap = _agreement(ref_scores, out["matches0"])
+        assert agree >= MIN_MATCH_AGREEMENT and gap < 0.1, (name, agree, gap)
+        # mscores0 of the agreed matches: exp(score) within the score tolerance
+        want_m0, want_ms = mo.filter_matches(ref_scores, 0.0)
+        same = (out["matches0"].cpu().long() == want_m0) & (want_m0 >= 0)
+        rel = (out["mscores0"].cpu()[same] / want_ms[same] - 1).abs()
+        assert rel.numel() == 0 or float(rel.max()) <= 2 * TOL_SCORES_MAX
+        py = pkg.PairMatcher(sd, n_layers=n_layers, threshold=0.0, device=DEV).match(
+            k0.to(DEV), k1.to(DEV), d0.to(DEV), d1.to(DEV))
+        assert float((py["matches0"] == out["matches0"]).float().mean()) >= 0.98
+        eng.close()
+
+
+def test_native_engine_host_buffers_batches_and_replanning(pkg):
+    n_layers = 2
+    sd = pkg.reference_init_state_dict(9, n_layers)
+    eng = pkg.NativeMatcher(sd, n_layers=n_layers, threshold=0.0, device=0)
+    for (b, n0, n1) in [(3, 200, 333), (2, 256, 256), (1, 1, 70)]:
+        feats = [mo.synth_pair(70 + i, n0, n1) for i in range(b)]
+        k0, k1, d0, d1 = (torch.cat([f[j] for f in feats]) for j in range(4))
+        launches = eng.plan(b, n0, n1)
+        assert launches == (1 + n_layers * (13 if n0 != n1 else 11) + 9)
+        host = eng.match_host(k0.numpy(), k1.numpy(), d0.half().numpy(), d1.half().numpy())
+        dev = eng.match(k0.to(DEV), k1.to(DEV), d0.half().to(DEV), d1.half().to(DEV))
+        torch.cuda.synchronize()
+        assert np.array_equal(host["matches0"], dev["matches0"].cpu().numpy())
+        assert np.array_equal(host["mscores0"], dev["mscores0"].cpu().numpy())
+        for i, f in enumerate(feats):
+            want = mo.forward(sd, *f, n_layers=n_layers, threshold=0.0)
+            agree, gap = _agreement(want["scores"], dev["matches0"][i:i + 1])
+            assert agree >= MIN_MATCH_AGREEMENT and gap < 0.1
+    eng.close()
