@@ -21,7 +21,7 @@ LIB = BUILD / "liblightglue_attention_plugin.so"
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 SOURCES = [CSRC / "lg_attn_api.cu", CSRC / "lg_match_kernels.cu", CSRC / "lg_matcher.cu", CSRC / "plugin" / "lightglue_attention_plugin.cpp",
            CSRC / "plugin" / "mock_trt_host.cpp"]
-HEADERS = [CSRC / "attn_sm100_kernel.cuh", CSRC / "attn_sm100_kernel_w4.cuh", CSRC / "softmax_math.cuh",
+HEADERS = [CSRC / "tools" / "lg_pair_bench.cpp", CSRC / "attn_sm100_kernel.cuh", CSRC / "attn_sm100_kernel_w4.cuh", CSRC / "softmax_math.cuh",
            CSRC / "cvt_f32_f16.cuh", CSRC / "attn_sm100.h", CSRC / "ptx_sm100.cuh",
            CSRC / "plugin" / "lightglue_attention_plugin.h", CSRC / "plugin" / "mock_nvinfer" / "NvInfer.h",
            CSRC.parent.parent / "include" / "lg_attn.h", CSRC.parent.parent / "include" / "lg_match.h", CSRC.parent.parent / "include" / "lg_matcher.h"]
@@ -73,7 +73,24 @@ def build(force: bool = False, verbose: bool = False, defs: list[str] | None = N
         raise RuntimeError("nvcc failed: " + " ".join(cmd))
     if verbose:
         sys.stderr.write(r.stderr)
+    if out is None:
+        build_pair_bench()
     return lib
+
+
+PAIR_BENCH = BUILD / "lg_pair_bench"
+
+
+def build_pair_bench() -> Path:
+    """The native multi-GPU pair-matching harness (csrc/tools/lg_pair_bench.cpp), linked against the library."""
+    src = CSRC / "tools" / "lg_pair_bench.cpp"
+    cmd = [nvcc(), "-O2", "-std=c++17", "-x", "cu", *ARCH, "-cudart", "shared", "-o", str(PAIR_BENCH), str(src),
+           "-L", str(BUILD), "-l:" + LIB.name, "-Xlinker", "-rpath,$ORIGIN"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        sys.stderr.write(r.stdout + r.stderr)
+        raise RuntimeError("nvcc failed: " + " ".join(cmd))
+    return PAIR_BENCH
 
 
 if __name__ == "__main__":

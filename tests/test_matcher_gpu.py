@@ -243,3 +243,21 @@ def test_native_engine_host_buffers_batches_and_replanning(pkg):
             agree, gap = _agreement(want["scores"], dev["matches0"][i:i + 1])
             assert agree >= MIN_MATCH_AGREEMENT and gap < 0.1
     eng.close()
+
+
+def test_native_pair_bench_binary(pkg, tmp_path):
+    """The C++ harness (csrc/tools/lg_pair_bench.cpp) end to end: blob file -> forked worker -> JSON line."""
+    import json
+    import subprocess
+
+    exe = pkg._binding.lib_path().parent / "lg_pair_bench"
+    assert exe.exists(), "build() did not produce lg_pair_bench"
+    m = pkg.matcher
+    blob = tmp_path / "w.blob"
+    blob.write_bytes(m.weights_blob(m.MatcherWeights(m.reference_init_state_dict(0, 2), 2, device="cpu")))
+    r = subprocess.run([str(exe), "--blob", str(blob), "--layers", "2", "--gpus", "1", "--kpts", "256", "--pairs", "6",
+                        "--sub", "4", "--steps", "2"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    line = json.loads(r.stdout.strip().splitlines()[-1])
+    assert line["unit"] == "pairs/s" and line["value"] > 0 and line["n_gpus"] == 1 and line["kpts"] == 256
+    assert 0 < line["mutual_nn_per_pair"] <= 256
