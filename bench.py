@@ -179,6 +179,7 @@ def pairs_section(pkg, torch, dist, dev, rank: int, world: int, steps: int, with
     `e2e`: pinned host features -> H2D -> match -> D2H of matches0 / mscores0, per sub-batch."""
     out = {}
     matcher = pkg.PairMatcher(seed=0, device=dev)
+    native = pkg.NativeMatcher(seed=0, device=dev.index or 0)
     for kpts in PAIR_KPTS:
         sub = pairs_sub_batch(kpts)
         slices = pkg.sharding.sub_batches(PAIRS_PER_GPU, sub)
@@ -241,9 +242,24 @@ def pairs_section(pkg, torch, dist, dev, rank: int, world: int, steps: int, with
             torch.cuda.synchronize()
             return pkg.sharding.max_over_ranks(dist if world > 1 else None, e0.elapsed_time(e1), dev)
 
+        # the same end-to-end step through the native C++ engine (include/lg_matcher.h): pinned host pointers in,
+        # pinned host pointers out, no torch in the call path (synchronous per sub-batch)
+        lib = pkg.load()
+
+        def step_native():
+            for a, b in slices:
+                rc = lib.lg_matcher_match_host(native._h, kp_h[0, a:b].data_ptr(), kp_h[1, a:b].data_ptr(),
+                                               d_h[0, a:b].data_ptr(), d_h[1, a:b].data_ptr(), b - a, kpts, kpts,
+                                               m_h[a:b].data_ptr(), s_h[a:b].data_ptr())
+                if rc != 0:
+                    raise RuntimeError(pkg._binding.error_string(rc))
+
         n_steps = max(1, min(steps, 5))
         ms = timed(step_resident, n_steps)
         ms_e2e = timed(step_e2e, n_steps)
+        m_py = m_h.clone()
+        ms_native = timed(step_native, n_steps)
+        native_agree = float((m_h == m_py).float().mean())
         pps = world * PAIRS_PER_GPU * n_steps / (ms * 1e-3)
         # results gathered to the host of rank 0: per global pair, how many keypoints found a mutual neighbour
         mutual = (s_h > 0).sum(dim=1).tolist()
@@ -257,6 +273,8 @@ def pairs_section(pkg, torch, dist, dev, rank: int, world: int, steps: int, with
                  "e2e": {"value": world * PAIRS_PER_GPU * n_steps / (ms_e2e * 1e-3), "unit": "pairs/s",
                          "h2d_bytes_per_step": int(kp_h.numel() * 4 + d_h.numel() * 2),
                          "d2h_bytes_per_step": int(m_h.numel() * 4 + s_h.numel() * 4)},
+                 "e2e_native_engine": {"value": world * PAIRS_PER_GPU * n_steps / (ms_native * 1e-3), "unit": "pairs/s",
+                                       "matches0_equal_to_python_driven": native_agree},
                  "matches_per_pair_at_threshold_0.1": float((m_h >= 0).sum()) / PAIRS_PER_GPU,
                  "mutual_nn_per_pair": (sum(gathered.values()) / len(gathered)) if rank == 0 else None,
                  "pairs_gathered_to_host": len(gathered) if rank == 0 else None}
