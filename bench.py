@@ -243,16 +243,17 @@ def pairs_section(pkg, torch, dist, dev, rank: int, world: int, steps: int, with
             return pkg.sharding.max_over_ranks(dist if world > 1 else None, e0.elapsed_time(e1), dev)
 
         # the same end-to-end step through the native C++ engine (include/lg_matcher.h): pinned host pointers in,
-        # pinned host pointers out, no torch in the call path (synchronous per sub-batch)
+        # pinned host pointers out, no torch in the call path (inputs of sub-batch i+1 staged under forward i)
         lib = pkg.load()
 
         def step_native():
             for a, b in slices:
-                rc = lib.lg_matcher_match_host(native._h, kp_h[0, a:b].data_ptr(), kp_h[1, a:b].data_ptr(),
+                rc = lib.lg_matcher_submit_host(native._h, kp_h[0, a:b].data_ptr(), kp_h[1, a:b].data_ptr(),
                                                d_h[0, a:b].data_ptr(), d_h[1, a:b].data_ptr(), b - a, kpts, kpts,
                                                m_h[a:b].data_ptr(), s_h[a:b].data_ptr())
                 if rc != 0:
                     raise RuntimeError(pkg._binding.error_string(rc))
+            pkg._binding.check(lib.lg_matcher_sync(native._h), "lg_matcher_sync")
 
         n_steps = max(1, min(steps, 5))
         ms = timed(step_resident, n_steps)

@@ -50,6 +50,13 @@ int lg_matcher_match(lg_matcher* m, const float* kpts0, const float* kpts1, cons
 int lg_matcher_match_host(lg_matcher* m, const float* kpts0, const float* kpts1, const void* desc0_half,
                           const void* desc1_half, int pairs, int n0, int n1, int* matches0, float* mscores0);
 
+/* Asynchronous host-buffer path for streams of sub-batches: submit() stages the (pinned) host inputs on a copy
+ * stream into one of two device slots while the previous forward still runs, then enqueues forward + D2H and
+ * returns; outputs are valid after lg_matcher_sync().  Host buffers must stay untouched until then. */
+int lg_matcher_submit_host(lg_matcher* m, const float* kpts0, const float* kpts1, const void* desc0_half,
+                           const void* desc1_half, int pairs, int n0, int n1, int* matches0, float* mscores0);
+int lg_matcher_sync(lg_matcher* m);
+
 /* Kernel launches inside one captured forward of the current plan (0 before planning). */
 int lg_matcher_launches(const lg_matcher* m);
 

@@ -59,6 +59,8 @@ MATCHER_ABI_SYMBOLS = (
     "lg_matcher_plan",
     "lg_matcher_match",
     "lg_matcher_match_host",
+    "lg_matcher_submit_host",
+    "lg_matcher_sync",
     "lg_matcher_launches",
     "lg_matcher_destroy",
 )
@@ -155,6 +157,10 @@ def load() -> ctypes.CDLL:
     lib.lg_matcher_match.argtypes = [P, P, P, P, P, I, I, I, P, P, P]
     lib.lg_matcher_match_host.restype = I
     lib.lg_matcher_match_host.argtypes = [P, P, P, P, P, I, I, I, P, P]
+    lib.lg_matcher_submit_host.restype = I
+    lib.lg_matcher_submit_host.argtypes = [P, P, P, P, P, I, I, I, P, P]
+    lib.lg_matcher_sync.restype = I
+    lib.lg_matcher_sync.argtypes = [P]
     lib.lg_matcher_launches.restype = I
     lib.lg_matcher_launches.argtypes = [P]
     lib.lg_matcher_destroy.restype = None

@@ -153,9 +153,12 @@ struct lg_matcher {
     cudaGraph_t graph = nullptr;
     cudaGraphExec_t exec = nullptr;
     int launches = 0;
-    // staging for match_host
-    void* host_stage = nullptr;
-    size_t host_stage_bytes = 0;
+    // asynchronous host-buffer path: a copy stream fills one of two device staging slots while the
+    // compute stream runs the previous sub-batch (slot layout: kpts0 | kpts1 | desc0 | desc1)
+    cudaStream_t copy_stream = nullptr;
+    uint8_t* stage[2] = {nullptr, nullptr};
+    cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_free[2] = {nullptr, nullptr};
+    unsigned long long submits = 0;
 };
 
 namespace {
@@ -168,6 +171,10 @@ void free_plan(lg_matcher* m) {
     for (Gemm* g : {&m->g_qkv, &m->g_cross_in, &m->g_ffn1, &m->g_ffn2, &m->g_final, &m->g_sim}) g->destroy();
     if (m->pool) cudaFree(m->pool);
     m->pool = nullptr;
+    for (int i = 0; i < 2; ++i) {
+        if (m->stage[i]) cudaFree(m->stage[i]);
+        m->stage[i] = nullptr;
+    }
     m->pairs = m->n0 = m->n1 = 0;
     m->launches = 0;
 }
@@ -271,6 +278,11 @@ int lg_matcher_create(lg_matcher** out, int device, int n_layers, const void* we
     e = cudaMalloc(&m->blob, weights_bytes);
     if (e == cudaSuccess) e = cudaMemcpy(m->blob, weights_host, weights_bytes, cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&m->copy_stream, cudaStreamNonBlocking);
+    for (int i = 0; i < 2 && e == cudaSuccess; ++i) {
+        e = cudaEventCreateWithFlags(&m->ev_in[i], cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&m->ev_free[i], cudaEventDisableTiming);
+    }
     if (e != cudaSuccess) { lg_matcher_destroy(m); return static_cast<int>(e); }
     // carve the device copy
     uint8_t* p = m->blob + align256(sizeof(BlobHeader));
@@ -328,6 +340,10 @@ int lg_matcher_plan(lg_matcher* m, int pairs, int n0, int n1) {
     m->assign_ws_bytes = b_aws;
     m->lt_ws = take(kLtWorkspace);
     m->pairs = pairs; m->n0 = n0; m->n1 = n1; m->rows = R;
+    for (int i = 0; i < 2; ++i) {
+        e = cudaMalloc(&m->stage[i], align256(R * 8) + static_cast<size_t>(R) * kDim * 2);
+        if (e != cudaSuccess) { m->stage[i] = nullptr; return static_cast<int>(e); }
+    }
     e = cudaMemsetAsync(m->pool, 0, total, m->stream);   // finite values everywhere (XC's right half is read by the first ffn)
     if (e != cudaSuccess) return static_cast<int>(e);
 
@@ -419,12 +435,58 @@ int lg_matcher_match_host(lg_matcher* m, const float* kpts0, const float* kpts1,
     return static_cast<int>(cudaStreamSynchronize(m->stream));
 }
 
+int lg_matcher_submit_host(lg_matcher* m, const float* kpts0, const float* kpts1, const void* desc0_half,
+                           const void* desc1_half, int pairs, int n0, int n1, int* matches0, float* mscores0) {
+    if (m == nullptr || kpts0 == nullptr || kpts1 == nullptr || desc0_half == nullptr || desc1_half == nullptr ||
+        matches0 == nullptr || mscores0 == nullptr)
+        return LG_ATTN_EINVAL;
+    if (m->pool == nullptr || m->pairs != pairs || m->n0 != n0 || m->n1 != n1) {
+        int rc = lg_matcher_sync(m);      // a shape change drains the pipeline, then re-plans
+        if (rc == 0) rc = lg_matcher_plan(m, pairs, n0, n1);
+        if (rc != 0) return rc;
+    }
+    cudaError_t e = cudaSetDevice(m->device);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    const int slot = static_cast<int>(m->submits++ & 1);
+    const long long r0 = static_cast<long long>(pairs) * n0, r1 = static_cast<long long>(pairs) * n1;
+    uint8_t* sk = m->stage[slot];
+    uint8_t* sd = sk + align256((r0 + r1) * 8);
+    // copy stream: wait until the forward that last read this slot has consumed it, then stage the inputs
+    e = cudaStreamWaitEvent(m->copy_stream, m->ev_free[slot], 0);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(sk, kpts0, r0 * 8, cudaMemcpyHostToDevice, m->copy_stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(sk + r0 * 8, kpts1, r1 * 8, cudaMemcpyHostToDevice, m->copy_stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(sd, desc0_half, r0 * kDim * 2, cudaMemcpyHostToDevice, m->copy_stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(sd + r0 * kDim * 2, desc1_half, r1 * kDim * 2, cudaMemcpyHostToDevice, m->copy_stream);
+    if (e == cudaSuccess) e = cudaEventRecord(m->ev_in[slot], m->copy_stream);
+    // compute stream: staged inputs -> plan buffers (on-device), forward, results to the host
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(m->stream, m->ev_in[slot], 0);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(m->kpts, sk, (r0 + r1) * 8, cudaMemcpyDeviceToDevice, m->stream);
+    if (e == cudaSuccess) e = cudaMemcpy2DAsync(m->xc, kFfn * 2, sd, kDim * 2, kDim * 2, r0 + r1, cudaMemcpyDeviceToDevice, m->stream);
+    if (e == cudaSuccess) e = cudaEventRecord(m->ev_free[slot], m->stream);
+    if (e == cudaSuccess) e = cudaGraphLaunch(m->exec, m->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(matches0, m->matches, r0 * 4, cudaMemcpyDeviceToHost, m->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(mscores0, m->mscores, r0 * 4, cudaMemcpyDeviceToHost, m->stream);
+    return static_cast<int>(e);
+}
+
+int lg_matcher_sync(lg_matcher* m) {
+    if (m == nullptr) return LG_ATTN_EINVAL;
+    cudaError_t e = cudaStreamSynchronize(m->copy_stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(m->stream);
+    return static_cast<int>(e);
+}
+
 void lg_matcher_destroy(lg_matcher* m) {
     if (m == nullptr) return;
     (void)cudaSetDevice(m->device);
     if (m->stream) (void)cudaStreamSynchronize(m->stream);
     free_plan(m);
     if (m->stream) (void)cudaStreamDestroy(m->stream);
+    if (m->copy_stream) (void)cudaStreamDestroy(m->copy_stream);
+    for (int i = 0; i < 2; ++i) {
+        if (m->ev_in[i]) (void)cudaEventDestroy(m->ev_in[i]);
+        if (m->ev_free[i]) (void)cudaEventDestroy(m->ev_free[i]);
+    }
     if (m->blob) (void)cudaFree(m->blob);
     if (m->lt) cublasLtDestroy(m->lt);
     delete m;

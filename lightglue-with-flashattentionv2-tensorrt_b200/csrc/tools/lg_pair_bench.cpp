@@ -8,7 +8,7 @@
 // counts and its elapsed time to the parent over a pipe, and the parent prints ONE JSON line (job time = the
 // slowest worker's).  Features are synthetic SuperPoint-shaped: normalised keypoints,
 // L2-normalised 256-d FP16 descriptors, in pinned host memory; the timed region covers H2D + forward + D2H
-// through lg_matcher_match_host.  Pure C++ over the C-ABI (include/lg_matcher.h): no Python, torch or TensorRT.
+// through lg_matcher_submit_host / lg_matcher_sync (inputs of sub-batch i+1 staged under forward i).  Pure C++ over the C-ABI (include/lg_matcher.h): no Python, torch or TensorRT.
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <sys/wait.h>
@@ -72,10 +72,11 @@ static int worker(const Args& a, int rank, const std::vector<char>& blob, Worker
     auto step = [&]() {
         for (int s = 0; s < a.pairs && rc == 0; s += sub) {
             const int b = (a.pairs - s) < sub ? (a.pairs - s) : sub;
-            rc = lg_matcher_match_host(eng, k0 + static_cast<size_t>(s) * n * 2, k1 + static_cast<size_t>(s) * n * 2,
+            rc = lg_matcher_submit_host(eng, k0 + static_cast<size_t>(s) * n * 2, k1 + static_cast<size_t>(s) * n * 2,
                                        d0 + static_cast<size_t>(s) * n * 256, d1 + static_cast<size_t>(s) * n * 256, b, n, n,
                                        m0 + static_cast<size_t>(s) * n, ms + static_cast<size_t>(s) * n);
         }
+        if (rc == 0) rc = lg_matcher_sync(eng);   // one step = all of this rank's pairs matched and back on the host
     };
     step();  // warm-up (also re-plans a short last sub-batch once)
     step();

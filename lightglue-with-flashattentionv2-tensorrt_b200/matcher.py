@@ -238,6 +238,21 @@ class NativeMatcher:
                                                 b, n0, n1, m0.ctypes.data, ms.ctypes.data), "lg_matcher_match_host")
         return {"matches0": m0, "mscores0": ms}
 
+    def submit_host(self, kpts0, kpts1, desc0, desc1, matches0, mscores0) -> None:
+        """Asynchronous `match_host` on caller-owned (ideally pinned) C-contiguous arrays / CPU tensors: inputs are
+        staged under the previous forward; `matches0` / `mscores0` are valid after `sync()`."""
+
+        def ptr(x):
+            return x.data_ptr() if isinstance(x, torch.Tensor) else x.ctypes.data
+
+        b, n0 = int(kpts0.shape[0]), int(kpts0.shape[1])
+        n1 = int(kpts1.shape[1])
+        B.check(self._lib.lg_matcher_submit_host(self._h, ptr(kpts0), ptr(kpts1), ptr(desc0), ptr(desc1), b, n0, n1,
+                                                 ptr(matches0), ptr(mscores0)), "lg_matcher_submit_host")
+
+    def sync(self) -> None:
+        B.check(self._lib.lg_matcher_sync(self._h), "lg_matcher_sync")
+
     def close(self) -> None:
         if getattr(self, "_h", None):
             self._lib.lg_matcher_destroy(self._h)

@@ -245,6 +245,35 @@ def test_native_engine_host_buffers_batches_and_replanning(pkg):
     eng.close()
 
 
+def test_native_engine_async_submit_pipeline_matches_synchronous_path(pkg):
+    """lg_matcher_submit_host / lg_matcher_sync: several sub-batches in flight (two staging slots reused, a ragged
+    last sub-batch that re-plans) give exactly what the synchronous host call gives for each sub-batch."""
+    n_layers = 2
+    sd = pkg.reference_init_state_dict(4, n_layers)
+    eng = pkg.NativeMatcher(sd, n_layers=n_layers, threshold=0.0, device=0)
+    ref = pkg.NativeMatcher(sd, n_layers=n_layers, threshold=0.0, device=0)
+    pairs, sub, n = 11, 3, 192
+    feats = [mo.synth_pair(300 + i, n, n) for i in range(pairs)]
+    k0, k1, d0, d1 = (torch.cat([f[j] for f in feats]) for j in range(4))
+    k0, k1 = k0.contiguous().pin_memory(), k1.contiguous().pin_memory()
+    d0, d1 = d0.half().contiguous().pin_memory(), d1.half().contiguous().pin_memory()
+    m0 = torch.full((pairs, n), -7, dtype=torch.int32).pin_memory()
+    ms = torch.full((pairs, n), -7.0, dtype=torch.float32).pin_memory()
+    for _ in range(2):                      # second round reuses the slots after a drain
+        m0.fill_(-7)
+        for a in range(0, pairs, sub):
+            b = min(pairs, a + sub)
+            eng.submit_host(k0[a:b], k1[a:b], d0[a:b], d1[a:b], m0[a:b], ms[a:b])
+        eng.sync()
+        for a in range(0, pairs, sub):
+            b = min(pairs, a + sub)
+            want = ref.match_host(k0[a:b].numpy(), k1[a:b].numpy(), d0[a:b].numpy(), d1[a:b].numpy())
+            assert np.array_equal(m0[a:b].numpy(), want["matches0"])
+            assert np.array_equal(ms[a:b].numpy(), want["mscores0"])
+    eng.close()
+    ref.close()
+
+
 def test_native_pair_bench_binary(pkg, tmp_path):
     """The C++ harness (csrc/tools/lg_pair_bench.cpp) end to end: blob file -> forked worker -> JSON line."""
     import json
