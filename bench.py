@@ -246,8 +246,12 @@ def pairs_section(pkg, torch, dist, dev, rank: int, world: int, steps: int, with
         # pinned host pointers out, no torch in the call path (inputs of sub-batch i+1 staged under forward i)
         lib = pkg.load()
 
+        # a single-forward step gives the engine nothing to overlap with: split it in two for this leg
+        half = max(1, PAIRS_PER_GPU // 2)
+        native_slices = slices if len(slices) > 1 else [(a, min(PAIRS_PER_GPU, a + half)) for a in range(0, PAIRS_PER_GPU, half)]
+
         def step_native():
-            for a, b in slices:
+            for a, b in native_slices:
                 rc = lib.lg_matcher_submit_host(native._h, kp_h[0, a:b].data_ptr(), kp_h[1, a:b].data_ptr(),
                                                d_h[0, a:b].data_ptr(), d_h[1, a:b].data_ptr(), b - a, kpts, kpts,
                                                m_h[a:b].data_ptr(), s_h[a:b].data_ptr())
@@ -275,6 +279,7 @@ def pairs_section(pkg, torch, dist, dev, rank: int, world: int, steps: int, with
                          "h2d_bytes_per_step": int(kp_h.numel() * 4 + d_h.numel() * 2),
                          "d2h_bytes_per_step": int(m_h.numel() * 4 + s_h.numel() * 4)},
                  "e2e_native_engine": {"value": world * PAIRS_PER_GPU * n_steps / (ms_native * 1e-3), "unit": "pairs/s",
+                                       "pairs_per_forward": native_slices[0][1] - native_slices[0][0],
                                        "matches0_equal_to_python_driven": native_agree},
                  "matches_per_pair_at_threshold_0.1": float((m_h >= 0).sum()) / PAIRS_PER_GPU,
                  "mutual_nn_per_pair": (sum(gathered.values()) / len(gathered)) if rank == 0 else None,

@@ -253,6 +253,24 @@ int forward(lg_matcher* m, cudaStream_t st, int* launches_out) {
 
 }  // namespace
 
+namespace {
+// Descriptor rows [rows,256] FP16 (contiguous) -> left half of XC (row pitch 1024 B).  A pitched copy-engine
+// transfer of 512 B rows runs far below HBM speed; 16 B per thread, one row per warp, is bandwidth-bound.
+__global__ void __launch_bounds__(256) place_desc_kernel(const uint4* __restrict__ src, uint4* __restrict__ xc, long long n_vec) {
+    for (long long i = blockIdx.x * 256ll + threadIdx.x; i < n_vec; i += static_cast<long long>(gridDim.x) * 256)
+        xc[(i >> 5) * 64 + (i & 31)] = src[i];
+}
+
+cudaError_t place_desc(const void* src, __half* xc, long long rows, cudaStream_t st) {
+    const long long n_vec = rows * 32;
+    if (n_vec == 0) return cudaSuccess;
+    const long long blocks = (n_vec + 255) / 256;
+    place_desc_kernel<<<static_cast<unsigned>(blocks < 148 * 16 ? blocks : 148 * 16), 256, 0, st>>>(
+        static_cast<const uint4*>(src), reinterpret_cast<uint4*>(xc), n_vec);
+    return cudaGetLastError();
+}
+}  // namespace
+
 extern "C" {
 
 size_t lg_matcher_blob_bytes(int n_layers) { return n_layers > 0 ? blob_bytes(n_layers) : 0; }
@@ -403,8 +421,14 @@ static int enqueue(lg_matcher* m, const float* kpts0, const float* kpts1, const 
     cudaError_t e = cudaMemcpyAsync(m->kpts, kpts0, r0 * 8, in_kind, st);
     if (e == cudaSuccess) e = cudaMemcpyAsync(m->kpts + r0 * 2, kpts1, r1 * 8, in_kind, st);
     // descriptors land in the left half of XC (row pitch 1024 B); input_proj is the identity for 256-d descriptors
-    if (e == cudaSuccess) e = cudaMemcpy2DAsync(m->xc, kFfn * 2, desc0, kDim * 2, kDim * 2, r0, in_kind, st);
-    if (e == cudaSuccess) e = cudaMemcpy2DAsync(m->xc + r0 * kFfn, kFfn * 2, desc1, kDim * 2, kDim * 2, r1, in_kind, st);
+    const bool aligned16 = ((reinterpret_cast<uintptr_t>(desc0) | reinterpret_cast<uintptr_t>(desc1)) & 15) == 0;
+    if (in_kind == cudaMemcpyDeviceToDevice && aligned16) {
+        if (e == cudaSuccess) e = place_desc(desc0, m->xc, r0, st);
+        if (e == cudaSuccess) e = place_desc(desc1, m->xc + r0 * kFfn, r1, st);
+    } else {
+        if (e == cudaSuccess) e = cudaMemcpy2DAsync(m->xc, kFfn * 2, desc0, kDim * 2, kDim * 2, r0, in_kind, st);
+        if (e == cudaSuccess) e = cudaMemcpy2DAsync(m->xc + r0 * kFfn, kFfn * 2, desc1, kDim * 2, kDim * 2, r1, in_kind, st);
+    }
     if (e == cudaSuccess) e = cudaGraphLaunch(m->exec, st);
     if (e == cudaSuccess) e = cudaMemcpyAsync(matches0, m->matches, r0 * 4, out_kind, st);
     if (e == cudaSuccess) e = cudaMemcpyAsync(mscores0, m->mscores, r0 * 4, out_kind, st);
@@ -461,7 +485,7 @@ int lg_matcher_submit_host(lg_matcher* m, const float* kpts0, const float* kpts1
     // compute stream: staged inputs -> plan buffers (on-device), forward, results to the host
     if (e == cudaSuccess) e = cudaStreamWaitEvent(m->stream, m->ev_in[slot], 0);
     if (e == cudaSuccess) e = cudaMemcpyAsync(m->kpts, sk, (r0 + r1) * 8, cudaMemcpyDeviceToDevice, m->stream);
-    if (e == cudaSuccess) e = cudaMemcpy2DAsync(m->xc, kFfn * 2, sd, kDim * 2, kDim * 2, r0 + r1, cudaMemcpyDeviceToDevice, m->stream);
+    if (e == cudaSuccess) e = place_desc(sd, m->xc, r0 + r1, m->stream);
     if (e == cudaSuccess) e = cudaEventRecord(m->ev_free[slot], m->stream);
     if (e == cudaSuccess) e = cudaGraphLaunch(m->exec, m->stream);
     if (e == cudaSuccess) e = cudaMemcpyAsync(matches0, m->matches, r0 * 4, cudaMemcpyDeviceToHost, m->stream);
