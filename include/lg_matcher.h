@@ -9,6 +9,10 @@
  * `matcher.py` (one packed FP16 activation matrix, folded projections — see DESIGN.md §8).
  *
  * All functions return 0 or a cudaError_t / cublasStatus_t-derived / LG_ATTN_E* code; none aborts.
+ * An engine owns ONE set of plan buffers: calls on one engine are not thread-safe, and the stream path
+ * (lg_matcher_match) must not be mixed with in-flight lg_matcher_submit_host work without a sync between them.
+ * Create one engine per GPU / per concurrent stream of work.  A shape change re-plans (device-wide
+ * synchronisation, allocation, graph capture): keep shapes stable on the hot path.
  */
 #ifndef LG_MATCHER_H_
 #define LG_MATCHER_H_

@@ -328,13 +328,8 @@ int lg_matcher_create(lg_matcher** out, int device, int n_layers, const void* we
     return 0;
 }
 
-int lg_matcher_plan(lg_matcher* m, int pairs, int n0, int n1) {
-    if (m == nullptr || pairs <= 0 || n0 <= 0 || n1 <= 0) return LG_ATTN_EINVAL;
-    if (m->pool != nullptr && m->pairs == pairs && m->n0 == n0 && m->n1 == n1) return 0;
-    cudaError_t e = cudaSetDevice(m->device);
-    if (e != cudaSuccess) return static_cast<int>(e);
-    (void)cudaStreamSynchronize(m->stream);
-    free_plan(m);
+static int build_plan(lg_matcher* m, int pairs, int n0, int n1) {
+    cudaError_t e;
     const long long R = static_cast<long long>(pairs) * (n0 + n1);
     const size_t b_kpts = align256(R * 2 * 4), b_cs = align256(R * 64 * 4), b_xc = align256(R * kFfn * 2),
                  b_proj = align256(R * 3 * kDim * 2), b_hid = align256(R * kFfn * 2), b_md = align256(R * kMdCols * 2),
@@ -397,6 +392,7 @@ int lg_matcher_plan(lg_matcher* m, int pairs, int n0, int n1) {
         cublasLtMatmulPreferenceDestroy(pref);
         if (st != CUBLAS_STATUS_SUCCESS || found == 0) return LG_MATCHER_ECUBLAS;
         g.algo = res.algo;
+        g.have_algo = true;
     }
     // ---- warm-up (eager) then capture
     if ((rc = forward(m, m->stream, nullptr)) != 0) return rc;
@@ -410,6 +406,26 @@ int lg_matcher_plan(lg_matcher* m, int pairs, int n0, int n1) {
     if (e != cudaSuccess) return static_cast<int>(e);
     e = cudaGraphInstantiate(&m->exec, m->graph, 0);
     return static_cast<int>(e);
+}
+
+int lg_matcher_plan(lg_matcher* m, int pairs, int n0, int n1) {
+    if (m == nullptr || pairs <= 0 || n0 <= 0 || n1 <= 0) return LG_ATTN_EINVAL;
+    if (m->exec != nullptr && m->pairs == pairs && m->n0 == n0 && m->n1 == n1) return 0;
+    cudaError_t e = cudaSetDevice(m->device);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    if (m->pool != nullptr) {
+        // the old plan's buffers may still be in use by a forward enqueued on the caller's stream
+        e = cudaDeviceSynchronize();
+        if (e != cudaSuccess) return static_cast<int>(e);
+    }
+    free_plan(m);
+    const int rc = build_plan(m, pairs, n0, n1);
+    if (rc != 0) {          // never leave a half-built plan behind: the next call must re-plan, not launch it
+        (void)cudaStreamSynchronize(m->stream);
+        free_plan(m);
+        (void)cudaGetLastError();   // a failed allocation must not surface later as a launch error
+    }
+    return rc;
 }
 
 int lg_matcher_launches(const lg_matcher* m) { return m ? m->launches : 0; }
@@ -464,7 +480,7 @@ int lg_matcher_submit_host(lg_matcher* m, const float* kpts0, const float* kpts1
     if (m == nullptr || kpts0 == nullptr || kpts1 == nullptr || desc0_half == nullptr || desc1_half == nullptr ||
         matches0 == nullptr || mscores0 == nullptr)
         return LG_ATTN_EINVAL;
-    if (m->pool == nullptr || m->pairs != pairs || m->n0 != n0 || m->n1 != n1) {
+    if (m->exec == nullptr || m->pairs != pairs || m->n0 != n0 || m->n1 != n1) {
         int rc = lg_matcher_sync(m);      // a shape change drains the pipeline, then re-plans
         if (rc == 0) rc = lg_matcher_plan(m, pairs, n0, n1);
         if (rc != 0) return rc;

@@ -274,6 +274,23 @@ def test_native_engine_async_submit_pipeline_matches_synchronous_path(pkg):
     ref.close()
 
 
+def test_native_engine_survives_a_failed_plan(pkg):
+    """A plan that cannot be allocated returns an error code (no abort, no half-built plan); the engine then
+    plans and matches a normal shape as if nothing had happened."""
+    n_layers = 1
+    sd = pkg.reference_init_state_dict(2, n_layers)
+    eng = pkg.NativeMatcher(sd, n_layers=n_layers, threshold=0.0, device=0)
+    with pytest.raises(RuntimeError):
+        eng.plan(4096, 8192, 8192)          # the score matrix alone would be 1 TiB
+    assert pkg.load().lg_matcher_launches(eng._h) == 0
+    k0, k1, d0, d1 = mo.synth_pair(5, 96, 80)
+    got = eng.match_host(k0.numpy(), k1.numpy(), d0.half().numpy(), d1.half().numpy())
+    want = mo.forward(sd, k0, k1, d0, d1, n_layers=n_layers, threshold=0.0)
+    agree, gap = _agreement(want["scores"], torch.from_numpy(got["matches0"]))
+    assert agree >= MIN_MATCH_AGREEMENT and gap < 0.1
+    eng.close()
+
+
 def test_native_pair_bench_binary(pkg, tmp_path):
     """The C++ harness (csrc/tools/lg_pair_bench.cpp) end to end: blob file -> forked worker -> JSON line."""
     import json
