@@ -45,6 +45,11 @@ enum lg_attn_io_dtype {
 /* ABI version of this header (bumped on any signature change). */
 int lg_attn_version(void);
 
+/* Test / tuning hook (no reference counterpart): which of the two full-grid kernels lg_attn_hd64_launch* picks.
+ * -1 automatic (default: persistent CTAs when a Q tile spans <= 8 KV tiles, else one Q tile per CTA),
+ * 0 one Q tile per CTA, 1 persistent CTAs.  Same results either way; also settable as LG_ATTN_PERSIST. */
+int lg_attn_debug_set_throughput_kernel(int mode);
+
 /* Per-device one-time setup (shared-memory opt-in, driver entry point lookup). Idempotent and
  * thread-safe; lg_attn_hd64_launch() calls it lazily, but call it before stream capture.
  * Replaces the static-initialiser cudaFuncSetAttribute of the reference (…fp16out.cu:242-250). */

@@ -30,6 +30,7 @@ EARCH = 100004
 # every symbol include/lg_attn.h declares (tests check the .so exports exactly these)
 C_ABI_SYMBOLS = (
     "lg_attn_version",
+    "lg_attn_debug_set_throughput_kernel",
     "lg_attn_hd64_init_device",
     "lg_attn_hd64_workspace_bytes",
     "lg_attn_hd64_launch",
@@ -100,6 +101,8 @@ def load() -> ctypes.CDLL:
     lib = ctypes.CDLL(str(path), mode=ctypes.RTLD_GLOBAL)
     lib.lg_attn_version.restype = ctypes.c_int
     lib.lg_attn_version.argtypes = []
+    lib.lg_attn_debug_set_throughput_kernel.restype = ctypes.c_int
+    lib.lg_attn_debug_set_throughput_kernel.argtypes = [ctypes.c_int]
     lib.lg_attn_hd64_init_device.restype = ctypes.c_int
     lib.lg_attn_hd64_init_device.argtypes = [ctypes.c_int]
     lib.lg_attn_hd64_workspace_bytes.restype = ctypes.c_size_t

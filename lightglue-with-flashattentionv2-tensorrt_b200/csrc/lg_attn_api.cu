@@ -9,7 +9,8 @@
 
 #include "attn_sm100.h"
 #include "attn_sm100_kernel.cuh"     // lgattn::w8 — latency shapes, split-KV clusters, PDL
-#include "attn_sm100_kernel_w4.cuh"  // lgattn::w4 — full grids (throughput)
+#include "attn_sm100_kernel_w4.cuh"  // lgattn::w4 — full grids, one Q tile per CTA (kept for A/B: LG_ATTN_PERSIST=0)
+#include "attn_sm100_kernel_w4p.cuh" // lgattn::w4p — full grids, persistent CTAs (throughput)
 #include "cvt_f32_f16.cuh"
 
 #include <cuda.h>
@@ -41,6 +42,9 @@ int g_sm_count[kMaxDevices];              // written once per device under g_ini
 int g_max_clusters[kMaxDevices][4];       // co-resident clusters of 1 << i CTAs (same publication rule)
 std::atomic<int> g_forced_splits{0};      // tuning override (LG_ATTN_SPLITS), 0 = automatic
 std::atomic<int> g_use_pdl{1};            // LG_ATTN_PDL=0 disables programmatic dependent launch
+std::atomic<int> g_use_persist{-1};       // full grids: -1 = automatic (persistent CTAs when a Q tile has few KV tiles),
+                                          // 0 / 1 = force the one-tile-per-CTA / persistent kernel (LG_ATTN_PERSIST, tests)
+constexpr int kPersistMaxKvTiles = 8;     // measured crossover (B200): +4 % at 8 KV tiles, -1 % at 16 and 32
 
 int resolve_encode() {
     if (g_encode.load(std::memory_order_acquire) != nullptr) return 0;
@@ -102,6 +106,7 @@ int init_device_locked(int device) {
         if (v == 1 || v == 2 || v == 4 || v == 8) g_forced_splits.store(v, std::memory_order_relaxed);
     }
     if (const char* env = getenv("LG_ATTN_PDL")) g_use_pdl.store(atoi(env) != 0 ? 1 : 0, std::memory_order_relaxed);
+    if (const char* env = getenv("LG_ATTN_PERSIST")) g_use_persist.store(atoi(env) < 0 ? -1 : (atoi(env) != 0 ? 1 : 0), std::memory_order_relaxed);
     int rc = resolve_encode();
     if (rc != 0) return rc;
     int prev = -1;
@@ -118,6 +123,8 @@ int init_device_locked(int device) {
     e = cudaSuccess;
     opt_in(reinterpret_cast<const void*>(w4::lg_attn_hd64_fwd<false>), w4::kSmemBytes);
     opt_in(reinterpret_cast<const void*>(w4::lg_attn_hd64_fwd<true>), w4::kSmemBytes);
+    opt_in(reinterpret_cast<const void*>(w4p::lg_attn_hd64_fwd<false>), w4p::kSmemBytes);
+    opt_in(reinterpret_cast<const void*>(w4p::lg_attn_hd64_fwd<true>), w4p::kSmemBytes);
     opt_in(reinterpret_cast<const void*>(w8::lg_attn_hd64_fwd<false, false>), w8::kSmemBytes);
     opt_in(reinterpret_cast<const void*>(w8::lg_attn_hd64_fwd<true, false>), w8::kSmemBytes);
     opt_in(reinterpret_cast<const void*>(w8::lg_attn_hd64_fwd<false, true>), w8::kSmemBytes + w8::kSmemSplitExtra);
@@ -154,8 +161,14 @@ bool valid_dtype(int d) { return d == LG_ATTN_F16_F16 || d == LG_ATTN_F32_F32 ||
 
 #ifdef LG_ATTN_W4_TRACE
 extern "C" int lg_attn_debug_read_w4_trace(long long* dst, unsigned* smid) {
-    cudaError_t e = cudaMemcpyFromSymbol(dst, lgattn::w4::g_w4_trace, sizeof(lgattn::w4::g_w4_trace));
-    if (e == cudaSuccess) e = cudaMemcpyFromSymbol(smid, lgattn::w4::g_w4_smid, sizeof(lgattn::w4::g_w4_smid));
+    cudaError_t e;
+    if (g_use_persist.load() != 0) {
+        e = cudaMemcpyFromSymbol(dst, lgattn::w4p::g_w4p_trace, sizeof(lgattn::w4p::g_w4p_trace));
+        if (e == cudaSuccess) e = cudaMemcpyFromSymbol(smid, lgattn::w4p::g_w4p_smid, sizeof(lgattn::w4p::g_w4p_smid));
+    } else {
+        e = cudaMemcpyFromSymbol(dst, lgattn::w4::g_w4_trace, sizeof(lgattn::w4::g_w4_trace));
+        if (e == cudaSuccess) e = cudaMemcpyFromSymbol(smid, lgattn::w4::g_w4_smid, sizeof(lgattn::w4::g_w4_smid));
+    }
     return static_cast<int>(e);
 }
 #endif
@@ -203,7 +216,18 @@ static int launch_core(const void* qh, const void* kh, const void* vh, void* o, 
     cfg.stream = stream;
     cudaLaunchAttribute attrs[2];
     unsigned n_attrs = 0;
-    if (full_grid) {
+    const int persist_mode = g_use_persist.load(std::memory_order_relaxed);
+    const bool persist = persist_mode < 0 ? kv_tiles <= kPersistMaxKvTiles : persist_mode != 0;
+    if (full_grid && persist) {
+        // persistent: 2 resident CTAs per SM walk the Q tiles blockIdx.x + i * gridDim.x
+        cfg.gridDim = dim3(static_cast<unsigned>(2 * g_sm_count[device]));
+        cfg.blockDim = dim3(w4p::kThreads);
+        cfg.dynamicSmemBytes = w4p::kSmemBytes;
+        cfg.attrs = attrs;
+        cfg.numAttrs = 0;
+        e = cudaLaunchKernelEx(&cfg, !out_f32 ? w4p::lg_attn_hd64_fwd<false> : w4p::lg_attn_hd64_fwd<true>, tm_q,
+                               tm_k, tm_v, o, n_q, n_kv, tiles_m, static_cast<int>(base), ol);
+    } else if (full_grid) {
         cfg.gridDim = dim3(static_cast<unsigned>(base));
         cfg.blockDim = dim3(w4::kThreads);
         cfg.dynamicSmemBytes = w4::kSmemBytes;
@@ -258,6 +282,12 @@ static int launch_core(const void* qh, const void* kh, const void* vh, void* o, 
 extern "C" {
 
 int lg_attn_version(void) { return kAbiVersion; }
+
+int lg_attn_debug_set_throughput_kernel(int mode) {
+    if (mode < -1 || mode > 1) return LG_ATTN_EINVAL;
+    g_use_persist.store(mode, std::memory_order_relaxed);
+    return 0;
+}
 
 int lg_attn_hd64_init_device(int device) {
     if (device < 0 || device >= kMaxDevices) return LG_ATTN_EINVAL;

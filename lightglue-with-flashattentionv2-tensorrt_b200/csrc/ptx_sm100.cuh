@@ -53,6 +53,22 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
     return ok != 0;
 }
 
+// Non-blocking probe (try_wait may suspend the thread until the phase flips or a time limit expires; test_wait
+// returns at once) — for probing a barrier early and only falling back to mbar_wait if it was not ready yet.
+__device__ __forceinline__ bool mbar_test_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}\n"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     while (!mbar_try_wait(bar, parity)) {
     }
@@ -61,9 +77,30 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
 // Same wait for the single-thread producer / MMA-issuer warps, whose waits are long and have slack:
 // back off with nanosleep between polls so their spin does not take issue slots from the softmax
 // warps that share the scheduler (the spin was ~18 % of all issued instructions).
+#ifndef LG_ATTN_WAIT_SUSPEND_NS
+#define LG_ATTN_WAIT_SUSPEND_NS 0   // > 0: service warps wait inside mbarrier.try_wait (suspend-time hint, ns) instead of polling
+#endif
+__device__ __forceinline__ bool mbar_try_wait_suspend(uint32_t bar, uint32_t parity, uint32_t hint_ns) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}\n"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity), "r"(hint_ns)
+        : "memory");
+    return ok != 0;
+}
 __device__ __forceinline__ void mbar_wait_backoff(uint32_t bar, uint32_t parity, uint32_t ns) {
+#if LG_ATTN_WAIT_SUSPEND_NS > 0
+    while (!mbar_try_wait_suspend(bar, parity, LG_ATTN_WAIT_SUSPEND_NS)) {
+    }
+#else
     if (mbar_try_wait(bar, parity)) return;
     while (!mbar_try_wait(bar, parity)) __nanosleep(ns);
+#endif
 }
 
 // named barrier among `count` threads (ids 1..15; id 0 is __syncthreads)

@@ -318,3 +318,52 @@ def test_strided_kv_batch_shift_is_cross_attention_in_one_launch(pkg, b2, n):
     assert torch.equal(o, want)
     with pytest.raises(pkg.LgAttnError):
         pkg.attention_strided(qk, qk, v, o, kv_batch_shift=b2)
+
+
+# full grids (>= 2 CTAs per SM): the launcher picks one of two throughput kernels — persistent CTAs walking several
+# Q tiles, or one Q tile per CTA.  Both must give the same answers on every edge the persistent loop adds: a single
+# KV tile per Q tile (first QK is also the last), ragged N and M, Q tiles of different (batch, head) in one CTA.
+FULL_GRID = [(100, 100, 1), (80, 128, 128), (75, 129, 129), (40, 256, 250), (80, 777, 1000), (40, 300, 2047), (10, 1024, 1153)]
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+@pytest.mark.parametrize("b,n,m", FULL_GRID)
+def test_full_grid_kernels_match_oracle(pkg, mode, b, n, m):
+    lib = pkg.load()
+    assert lib.lg_attn_debug_set_throughput_kernel(mode) == 0
+    try:
+        q, k, v = orc.make_qkv(b + n + m, b, 4, n, m)
+        tq, tk, tv = _to_dev(q, k, v)
+        pad = 2048
+        for out_dt, tol, err in ((torch.float16, orc.TOL_F16_MAX_ABS, orc.max_abs_err), (torch.float32, orc.TOL_F32_REL, orc.rel_err)):
+            buf = torch.full((b * 4 * n * 64 + pad,), -77.0, dtype=out_dt, device=DEV)
+            out = buf[: b * 4 * n * 64].view(b, 4, n, 64)
+            pkg.attention(tq, tk, tv, out_dtype=out_dt, out=out)
+            assert (buf[b * 4 * n * 64:] == -77.0).all()          # nothing written past the last row
+            for bi in (0, b // 2, b - 1):
+                ref = orc.attention_np(q[bi:bi + 1], k[bi:bi + 1], v[bi:bi + 1])
+                assert err(out[bi:bi + 1].float().cpu().numpy(), ref) <= tol, (out_dt, bi)
+    finally:
+        lib.lg_attn_debug_set_throughput_kernel(-1)
+
+
+def test_full_grid_kernels_agree_bitwise(pkg):
+    """Same arithmetic in the same order: the persistent and the one-tile-per-CTA kernel produce identical bits,
+    also through the strided entry with kv_batch_shift (both cross-attention directions in one launch)."""
+    lib = pkg.load()
+    g = torch.Generator(device=DEV).manual_seed(11)
+    b2, n = 96, 200
+    proj = torch.randn(b2, n, 3, 4, 64, device=DEV, generator=g).half()
+    q, k, v = (proj[:, :, i].permute(0, 2, 1, 3) for i in range(3))
+    outs = []
+    try:
+        for mode in (0, 1):
+            assert lib.lg_attn_debug_set_throughput_kernel(mode) == 0
+            o = torch.empty(b2, n, 4, 64, dtype=torch.float16, device=DEV)
+            pkg.attention_strided(q, k, v, out=o.permute(0, 2, 1, 3), kv_batch_shift=b2 // 2)
+            outs.append(o)
+    finally:
+        lib.lg_attn_debug_set_throughput_kernel(-1)
+    assert torch.equal(outs[0], outs[1])
+    ref = torch.nn.functional.scaled_dot_product_attention(q.float(), torch.roll(k, -b2 // 2, 0).float(), torch.roll(v, -b2 // 2, 0).float())
+    assert (outs[1].permute(0, 2, 1, 3).float() - ref).abs().max().item() <= orc.TOL_F16_MAX_ABS

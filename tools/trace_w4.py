@@ -39,3 +39,21 @@ for sm, cs in by_sm.items():
 print("co-resident CTA phase offset (fraction of tile period): ", np.round(np.percentile(offs, [10, 50, 90]), 2) if offs else "n/a")
 c0 = 300
 print("one CTA, tiles 3..6, stamps relative to tile start:", (buf[c0, 3:7, :7] - buf[c0, 3:7, :1]).tolist())
+
+# CTA-level stamps (slot 7 of tile rows 0..5)
+cta = buf[:, :6, 7].astype(np.float64)
+ok = cta[:, 0] > 0
+setup = cta[ok, 1] - cta[ok, 0]; loop = cta[ok, 2] - cta[ok, 1]; epi = cta[ok, 3] - cta[ok, 2]; life = cta[ok, 3] - cta[ok, 0]
+first = buf[ok, 0, 1] - cta[ok, 1]
+print(f"CTA clocks: set-up {np.median(setup):.0f}  first S wait {np.median(first):.0f}  tile loop {np.median(loop):.0f}  epilogue {np.median(epi):.0f}  lifetime {np.median(life):.0f}")
+for lo, hi, tag in ((0, 296, "wave 1"), (296, 592, "wave 2")):
+    l = (cta[lo:hi, 3] - cta[lo:hi, 0]); print(f"  {tag}: lifetime p50 {np.median(l):.0f} p10 {np.percentile(l,10):.0f} p90 {np.percentile(l,90):.0f}; loop p50 {np.median(cta[lo:hi,2]-cta[lo:hi,1]):.0f}; ns p50 {np.median(cta[lo:hi,5]-cta[lo:hi,4]):.0f}")
+# successor gap on the same SM: wave-2 CTA start minus the end of the wave-1 CTA it replaced (globaltimer ns)
+gaps = []
+for sm, cs in by_sm.items():
+    firsts = [c for c in range(296) if int(smid[c]) == sm]
+    if not firsts: continue
+    ends = sorted(buf[c, 5, 7] for c in firsts)
+    starts = sorted(buf[c, 4, 7] for c in cs)
+    for e, st in zip(ends, starts): gaps.append(st - e)
+if gaps: print("same-SM successor gap ns (p10/p50/p90):", np.percentile(gaps, [10, 50, 90]))
