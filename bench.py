@@ -503,7 +503,7 @@ def extra_shapes(pkg, torch, dev, peaks) -> dict:
     """Batched shapes (BASELINE configs[4] attention shapes) — TFLOP/s against the measured tensor peak."""
     out = {}
     for (b, n, out_dt, tag) in [(64, 2048, torch.float16, "B64_N2048_f16out"), (64, 2048, torch.float32, "B64_N2048_f32out"),
-                                (16, 4096, torch.float16, "B16_N4096_f16out")]:
+                                (16, 4096, torch.float16, "B16_N4096_f16out"), (128, 1024, torch.float16, "B128_N1024_f16out")]:
         q = torch.randn(b, H, n, D, device=dev).half()
         k = torch.randn(b, H, n, D, device=dev).half()
         v = torch.randn(b, H, n, D, device=dev).half()
@@ -520,7 +520,8 @@ def extra_shapes(pkg, torch, dev, peaks) -> dict:
         torch.cuda.synchronize()
         ms = e0.elapsed_time(e1) / iters
         tf = 4.0 * b * H * n * n * D / (ms * 1e-3) / 1e12
-        out[tag] = {"ms": ms, "tflops": tf, "frac_of_measured_burst": tf / peaks["bf16_tflops"],
+        out[tag] = {"ms": ms, "tflops": tf, "kernel": "lgattn::w4p (persistent CTAs)" if n <= 1024 else "lgattn::w4 (one Q tile per CTA)",
+                    "frac_of_measured_burst": tf / peaks["bf16_tflops"],
                     "frac_of_measured_sustained": tf / peaks["bf16_tflops_sustained"] if peaks["bf16_tflops_sustained"] else None,
                     "frac_of_nominal_2250": tf / 2250.0}
         del q, k, v, o

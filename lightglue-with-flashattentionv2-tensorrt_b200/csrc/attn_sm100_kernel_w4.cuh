@@ -85,6 +85,9 @@ constexpr int kRegsSoftmax = 216;
 #ifndef LG_ATTN_W4_MAXAHEAD
 #define LG_ATTN_W4_MAXAHEAD 0   // 1: next tile's row max scanned under the current tile's exponentials
 #endif
+#ifndef LG_ATTN_W4_MERGE_WAIT
+#define LG_ATTN_W4_MERGE_WAIT 0
+#endif
 struct TrueC { static constexpr bool value = true; };
 struct FalseC { static constexpr bool value = false; };
 constexpr int kRegsOther = 40;
@@ -362,8 +365,13 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
 #else
         for (int j = 0; j < num_kv_tiles; ++j) {
             W4_TRACE(j, 0);
-            mbar_wait(bar(kBarSFull), j & 1);
-            tc_fence_after();
+#if LG_ATTN_W4_MERGE_WAIT
+            if (j == 0)   // later tiles: s_full(j) was already awaited under tile j-1 (see below)
+#endif
+            {
+                mbar_wait(bar(kBarSFull), j & 1);
+                tc_fence_after();
+            }
             W4_TRACE(j, 1);
             uint32_t sr[kBlockN];
 #pragma unroll
@@ -382,7 +390,11 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
                     if (c >= valid) sr[c] = 0xff800000u;
             }
 
+#if defined(LG_ATTN_WHATIF) && (LG_ATTN_WHATIF == 1 || LG_ATTN_WHATIF == 3)
+            const float mx = 0.f;   // what-if build (WRONG results in general): no row-max pass
+#else
             const float mx = row_max<kBlockN>(sr);
+#endif
 
             // lazy rescale decision (warp-uniform so the tcgen05.ld/st below stay aligned)
             float alpha = 1.f;
@@ -403,13 +415,44 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
 
             // P = exp2(s*c - m*c) as packed FP16 pairs + the FP32 row sum (softmax_math.cuh)
             uint32_t pk[kBlockN / 2];
+#if defined(LG_ATTN_WHATIF) && LG_ATTN_WHATIF >= 2
+            // what-if builds (WRONG results): 2 = no exponentials (one FFMA2 + pack per pair), 3 = no arithmetic at all
+            float tile_sum = 0.f;
+#pragma unroll
+            for (int c = 0; c < kBlockN; c += 2) {
+#if LG_ATTN_WHATIF == 2
+                float x0, x1;
+                unpack_f32x2(fma_f32x2(pack_f32x2(__uint_as_float(sr[c]), __uint_as_float(sr[c + 1])),
+                                       pack_f32x2(kScaleLog2, kScaleLog2), pack_f32x2(neg_m, neg_m)), x0, x1);
+                pk[c / 2] = pack_half2(x0, x1);
+#else
+                pk[c / 2] = sr[c] ^ sr[c + 1];
+#endif
+            }
+            tile_sum = __uint_as_float(pk[0]) + neg_m;
+#else
             const float tile_sum = softmax_exp_pass<kBlockN>(sr, pk, neg_m);
+#endif
 
             W4_TRACE(j, 4);
+#if LG_ATTN_W4_MERGE_WAIT
+            // ONE barrier round trip per tile instead of two (each costs 50-180 clk of MIO latency while the co-resident
+            // CTA keeps the MUFU queue full): the MMA thread issues QK(j+1) after PV(j-1), and a tcgen05.commit covers every
+            // earlier MMA of that thread, so s_full(j+1) — needed at the top of the next tile anyway — also says that
+            // PV(j-1) has finished reading P and writing O.  Only the last tile still waits on pv_done itself.
+            if (j + 1 < num_kv_tiles) {
+                mbar_wait(bar(kBarSFull), (j + 1) & 1);
+                tc_fence_after();
+            } else if (j > 0) {
+                mbar_wait(bar(kBarPVDone), (j - 1) & 1);
+                tc_fence_after();
+            }
+#else
             if (j > 0) {
                 mbar_wait(bar(kBarPVDone), (j - 1) & 1);  // P buffer free, O(j-1) final
                 tc_fence_after();
             }
+#endif
             W4_TRACE(j, 5);
             tmem_st_x32(t_p, pk);
             tmem_st_x32(t_p + 32u, pk + 32);

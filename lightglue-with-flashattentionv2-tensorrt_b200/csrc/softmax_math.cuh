@@ -100,6 +100,10 @@ __device__ __forceinline__ float softmax_exp_pass(const uint32_t (&sr)[kCols], u
         pk[c / 2] = pack_half2(p[c], p[c + 1]);
     }
     float sum;
+#ifdef LG_ATTN_EXPERIMENT_NOSUM
+    // what-if build (WRONG results): drops the row-sum adds to bound what moving them to the tensor core could gain
+    sum = p[0] + p[kCols - 1];
+#else
     if (LG_ATTN_PACKED_SUM) {
         uint64_t acc[4] = {0ull, 0ull, 0ull, 0ull};
 #pragma unroll
@@ -118,6 +122,7 @@ __device__ __forceinline__ float softmax_exp_pass(const uint32_t (&sr)[kCols], u
         }
         sum = (a0 + a1) + (a2 + a3);
     }
+#endif
     return sum;
 }
 
