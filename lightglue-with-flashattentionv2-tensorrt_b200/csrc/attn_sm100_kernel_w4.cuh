@@ -82,14 +82,14 @@ constexpr uint32_t kColP = 192;
 
 constexpr int kRegsSoftmax = 216;
 
-#ifndef LG_ATTN_W4_MAXAHEAD
-#define LG_ATTN_W4_MAXAHEAD 0   // 1: next tile's row max scanned under the current tile's exponentials
-#endif
+// Tuning builds (profiles/r1_throughput_kernel_analysis.txt): LG_ATTN_W4_MERGE_WAIT=1 one barrier wait per tile;
+// LG_ATTN_WHATIF=1|2|3 drop the row max | the exponentials | all arithmetic (WRONG results, timing decomposition only).
+// A variant that scanned the next tile's row max out of TMEM under chunked exponentials measured 738 vs 805 TFLOP/s and
+// was removed (git history: "max-ahead").
 #ifndef LG_ATTN_W4_MERGE_WAIT
 #define LG_ATTN_W4_MERGE_WAIT 0
 #endif
-struct TrueC { static constexpr bool value = true; };
-struct FalseC { static constexpr bool value = false; };
+
 constexpr int kRegsOther = 40;
 
 // Optional per-tile phase tracing (tuning builds only, -DLG_ATTN_W4_TRACE): clock64 stamps of softmax
@@ -250,119 +250,6 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
             g_w4_smid[blockIdx.x] = smid;
         }
 #endif
-#if LG_ATTN_W4_MAXAHEAD
-        // Software-pipelined tile: the exponentials run in four 32-column chunks with P stored chunk-wise, and the
-        // NEXT tile's row max is scanned straight out of TMEM underneath them (S(j+1) is complete by mid-tile:
-        // QK(j+1) was issued when S(j) reached registers), so the FMNMX work fills the issue slots the MUFU-bound
-        // chunks leave free instead of being a serial phase of its own.  A ragged last tile is never scanned
-        // ahead (its mask is applied to the register copy) and takes the plain row_max.
-        float mx_ahead = -INFINITY;
-        auto tile = [&](const int j, auto scan_c, const bool mx_ready) {
-            constexpr bool kScan = decltype(scan_c)::value;
-            W4_TRACE(j, 0);
-            mbar_wait(bar(kBarSFull), j & 1);
-            tc_fence_after();
-            W4_TRACE(j, 1);
-            uint32_t sr[kBlockN];
-#pragma unroll
-            for (int c = 0; c < kBlockN / 32; ++c) tmem_ld_x32(t_s + 32u * c, sr + 32 * c);
-            tmem_wait_ld();
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(bar(kBarSEmpty));
-            W4_TRACE(j, 2);
-
-            float mx = mx_ahead;
-            if (!mx_ready) {
-                const int valid = n_kv - j * kBlockN;
-                if (valid < kBlockN) {
-#pragma unroll
-                    for (int c = 0; c < kBlockN; ++c)
-                        if (c >= valid) sr[c] = 0xff800000u;
-                }
-                mx = row_max<kBlockN>(sr);
-            }
-
-            float alpha = 1.f;
-            bool rescale = false;
-            if (j == 0) {
-                m_used = mx;
-            } else {
-                const bool need = (mx - m_used) * kScaleLog2 > kTau;
-                rescale = __any_sync(0xffffffffu, need);
-                if (rescale) {
-                    const float m_new = fmaxf(m_used, mx);
-                    alpha = ex2_approx((m_used - m_new) * kScaleLog2);
-                    m_used = m_new;
-                }
-            }
-            const float neg_m = -m_used * kScaleLog2;
-            const PolyConsts pc = make_poly_consts(neg_m);
-            uint64_t acc[4] = {0ull, 0ull, 0ull, 0ull};
-            W4_TRACE(j, 3);
-
-            uint32_t pk[32];
-            softmax_exp_chunk<32>(sr, pk, neg_m, pc, acc);
-            softmax_exp_chunk<32>(sr + 32, pk + 16, neg_m, pc, acc);
-            if (j > 0) {
-                mbar_wait(bar(kBarPVDone), (j - 1) & 1);  // P buffer free, O(j-1) final
-                tc_fence_after();
-            }
-            tmem_st_x32(t_p, pk);
-            if (rescale) {
-#pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    uint32_t orow[32];
-                    tmem_ld_x32(t_o + 32u * h, orow);
-                    tmem_wait_ld();
-#pragma unroll
-                    for (int c = 0; c < 32; ++c)
-                        orow[c] = __float_as_uint(__uint_as_float(orow[c]) * alpha);
-                    tmem_st_x32(t_o + 32u * h, orow);
-                }
-                l_sum *= alpha;
-            }
-
-            uint32_t nx[64];
-            float mxa[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-            if constexpr (kScan) {
-                mbar_wait(bar(kBarSFull), (j + 1) & 1);
-                tc_fence_after();
-                tmem_ld_x32(t_s, nx);
-                tmem_ld_x32(t_s + 32u, nx + 32);
-            }
-            uint32_t pk2[32];
-            softmax_exp_chunk<32>(sr + 64, pk2, neg_m, pc, acc);
-            if constexpr (kScan) {
-                tmem_wait_ld();
-                scan_max<64>(nx, mxa);
-                tmem_ld_x32(t_s + 64u, nx);
-                tmem_ld_x32(t_s + 96u, nx + 32);
-            }
-            softmax_exp_chunk<32>(sr + 96, pk2 + 16, neg_m, pc, acc);
-            W4_TRACE(j, 4);
-            W4_TRACE(j, 5);
-            tmem_st_x32(t_p + 32u, pk2);
-            if constexpr (kScan) {
-                tmem_wait_ld();
-                scan_max<64>(nx, mxa);
-                mx_ahead = fmaxf(fmaxf(mxa[0], mxa[1]), fmaxf(mxa[2], mxa[3]));
-            }
-            l_sum += reduce_sum_acc(acc);
-            tmem_wait_st();
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(bar(kBarPFull));
-            W4_TRACE(j, 6);
-        };
-        {
-            const bool ragged = (n_kv % kBlockN) != 0;
-            const int n_scan = max(ragged ? num_kv_tiles - 2 : num_kv_tiles - 1, 0);  // tiles [0, n_scan) scan tile j+1
-            int j = 0;
-            for (; j < n_scan; ++j) tile(j, TrueC{}, j > 0);
-            for (; j < num_kv_tiles; ++j) tile(j, FalseC{}, j > 0 && j == n_scan);
-        }
-#else
         for (int j = 0; j < num_kv_tiles; ++j) {
             W4_TRACE(j, 0);
 #if LG_ATTN_W4_MERGE_WAIT
@@ -477,7 +364,6 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
             W4_TRACE(j, 6);
         }
 
-#endif
         // ------------------------------------------------------------------------------- epilogue
         mbar_wait(bar(kBarPVDone), (num_kv_tiles - 1) & 1);
         tc_fence_after();

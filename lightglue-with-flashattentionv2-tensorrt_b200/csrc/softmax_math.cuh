@@ -127,55 +127,6 @@ __device__ __forceinline__ float softmax_exp_pass(const uint32_t (&sr)[kCols], u
 }
 
 
-// ---- chunked forms (the throughput kernel's software-pipelined loop) ------------------------------
-// One kCols-wide piece of a row: same arithmetic and poly/MUFU column pattern as softmax_exp_pass, row sums
-// carried in four packed accumulators across the pieces of a tile (reduce with reduce_sum_acc at the end).
-template <int kCols>
-__device__ __forceinline__ void softmax_exp_chunk(const uint32_t* __restrict__ sr, uint32_t* __restrict__ pk,
-                                                  float neg_m_scaled, const PolyConsts& pc, uint64_t (&acc)[4]) {
-    static_assert(kCols % 8 == 0, "chunk keeps the 8-column poly/MUFU pattern");
-    float p[kCols];
-#pragma unroll
-    for (int c = 0; c < kCols; c += 2) {
-        const bool poly0 = ((c % 8) < LG_ATTN_POLY_OF_8);
-        const bool poly1 = (((c + 1) % 8) < LG_ATTN_POLY_OF_8);
-        if (!poly0 && !poly1) {
-            float x0, x1;
-            unpack_f32x2(fma_f32x2(pack_f32x2(__uint_as_float(sr[c]), __uint_as_float(sr[c + 1])),
-                                   pack_f32x2(kScaleLog2, kScaleLog2), pack_f32x2(neg_m_scaled, neg_m_scaled)),
-                         x0, x1);
-            p[c] = ex2_approx(x0);
-            p[c + 1] = ex2_approx(x1);
-        } else {
-            p[c] = poly0 ? ex2_poly(__uint_as_float(sr[c]), pc)
-                         : ex2_approx(fmaf(__uint_as_float(sr[c]), kScaleLog2, neg_m_scaled));
-            p[c + 1] = poly1 ? ex2_poly(__uint_as_float(sr[c + 1]), pc)
-                             : ex2_approx(fmaf(__uint_as_float(sr[c + 1]), kScaleLog2, neg_m_scaled));
-        }
-        pk[c / 2] = pack_half2(p[c], p[c + 1]);
-    }
-#pragma unroll
-    for (int c = 0; c < kCols; c += 2) acc[(c / 2) % 4] = add_f32x2(acc[(c / 2) % 4], pack_f32x2(p[c], p[c + 1]));
-}
-
-__device__ __forceinline__ float reduce_sum_acc(const uint64_t (&acc)[4]) {
-    float s0, s1;
-    unpack_f32x2(add_f32x2(add_f32x2(acc[0], acc[1]), add_f32x2(acc[2], acc[3])), s0, s1);
-    return s0 + s1;
-}
-
-// running 4-chain max over one piece (folds into FMNMX3 pairs)
-template <int kCols>
-__device__ __forceinline__ void scan_max(const uint32_t* __restrict__ sr, float (&mx)[4]) {
-#pragma unroll
-    for (int c = 0; c < kCols; c += 4) {
-        mx[0] = fmaxf(mx[0], __uint_as_float(sr[c + 0]));
-        mx[1] = fmaxf(mx[1], __uint_as_float(sr[c + 1]));
-        mx[2] = fmaxf(mx[2], __uint_as_float(sr[c + 2]));
-        mx[3] = fmaxf(mx[3], __uint_as_float(sr[c + 3]));
-    }
-}
-
 // row max of a slice with 3-input FMNMX chains
 template <int kCols>
 __device__ __forceinline__ float row_max(const uint32_t (&sr)[kCols]) {
