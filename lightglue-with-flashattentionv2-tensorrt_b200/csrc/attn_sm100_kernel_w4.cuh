@@ -87,8 +87,10 @@ constexpr int kRegsSoftmax = 216;
 // A variant that scanned the next tile's row max out of TMEM under chunked exponentials measured 738 vs 805 TFLOP/s and
 // was removed (git history: "max-ahead").
 #ifndef LG_ATTN_W4_MERGE_WAIT
-#define LG_ATTN_W4_MERGE_WAIT 0
+#define LG_ATTN_W4_MERGE_WAIT 1
 #endif
+// (storing the epilogue straight from registers, one output row per thread, instead of through the swizzled staging
+// buffer measured 792 vs 804 TFLOP/s on the same box and was dropped.)
 
 constexpr int kRegsOther = 40;
 
@@ -155,6 +157,14 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
         mbar_init(bar(kBarPFull), 4);
         mbar_init(bar(kBarPVDone), 1);
         fence_mbar_init();
+        // first loads go out before the TMEM allocation / CTA barrier below: the 2.5 k clk until the first S is mostly
+        // their latency (CTA-level trace), and only this thread ever arms these barriers
+        mbar_arrive_expect_tx(bar(kBarQFull), kTileBytes);
+        tma_load_4d(smem + kSmemQ, &tm_q, bar(kBarQFull), 0, tile_m * kBlockM, hi, bi);
+        mbar_arrive_expect_tx(bar(kBarKFull), kTileBytes);
+        tma_load_4d(smem + kSmemK, &tm_k, bar(kBarKFull), 0, 0, hi, bk);
+        mbar_arrive_expect_tx(bar(kBarVFull), kTileBytes);
+        tma_load_4d(smem + kSmemV, &tm_v, bar(kBarVFull), 0, 0, hi, bk);
     }
     if (warp == 6) {
         tmem_alloc<kTmemCols>(smem + kSmemTmemSlot);
@@ -170,9 +180,7 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
         setmaxnreg_dec<kRegsOther>();
         if (warp == 4 && lane == 0) {
             // ===================================================================== TMA producer
-            mbar_arrive_expect_tx(bar(kBarQFull), kTileBytes);
-            tma_load_4d(smem + kSmemQ, &tm_q, bar(kBarQFull), 0, tile_m * kBlockM, hi, bi);
-            for (int j = 0; j < num_kv_tiles; ++j) {
+            for (int j = 1; j < num_kv_tiles; ++j) {   // tile 0 (and Q) were issued in the prologue
                 const int s = j % kStages;
                 const uint32_t par = ((j / kStages) - 1) & 1;
                 if (j >= kStages) mbar_wait_backoff(bar(kBarKEmpty + s), par, LG_ATTN_SPIN_NS);

@@ -73,9 +73,6 @@ constexpr uint32_t kColP = 192;
 
 constexpr int kRegsSoftmax = 216;
 constexpr int kRegsOther = 40;
-#ifndef LG_ATTN_W4P_PROBE
-#define LG_ATTN_W4P_PROBE 0
-#endif
 
 #ifdef LG_ATTN_W4_TRACE
 // same layout as w4's trace (tools/trace_w4.py): rows [0,296) = first Q tile of each CTA, [296,592) = second
@@ -258,16 +255,12 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
             float m_used = -INFINITY;  // row max the exponent is referenced to (raw score units)
             float l_sum = 0.f;
 
-#if LG_ATTN_W4P_PROBE
-            bool s_ok = false;  // S(g) already seen complete by the probe issued under the previous tile's P store
-#endif
             for (int j = 0; j < num_kv_tiles; ++j, ++g) {
                 W4P_TRACE(j, 0);
-#if LG_ATTN_W4P_PROBE
-                if (!s_ok)
-#endif
+                if (j == 0) {  // later tiles of this Q tile: s_full(g) was already awaited under tile g-1 (see below)
                     mbar_wait(bar(kBarSFull), g & 1);
-                tc_fence_after();
+                    tc_fence_after();
+                }
                 W4P_TRACE(j, 1);
                 uint32_t sr[kBlockN];
 #pragma unroll
@@ -307,24 +300,19 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
 
                 // one monolithic pass: splitting it into column chunks with the P stores / barrier probes in between
                 // (measured: 722-738 vs 797 TFLOP/s) costs ptxas the freedom to spread the MUFU issue over the tile
-#if LG_ATTN_W4P_PROBE
-                // non-blocking probes, issued where their 50-180 clk MIO latency hides under arithmetic
-                const bool pv_ok = j > 0 ? mbar_test_wait(bar(kBarPVDone), (g - 1) & 1) : true;
-#endif
                 uint32_t pk[kBlockN / 2];
                 const float tile_sum = softmax_exp_pass<kBlockN>(sr, pk, neg_m);
 
                 W4P_TRACE(j, 4);
-#if LG_ATTN_W4P_PROBE
-                s_ok = j + 1 < num_kv_tiles ? mbar_test_wait(bar(kBarSFull), (g + 1) & 1) : false;
-                if (!pv_ok) mbar_wait(bar(kBarPVDone), (g - 1) & 1);
-                tc_fence_after();
-#else
-                if (j > 0) {
-                    mbar_wait(bar(kBarPVDone), (g - 1) & 1);  // P buffer free, O(j-1) final
+                // one barrier round trip per tile: QK(g+1) is issued after PV(g-1) by the same thread and tcgen05.commit covers
+                // all of that thread's earlier MMAs, so s_full(g+1) also means the P buffer is free and O(g-1) final
+                if (j + 1 < num_kv_tiles) {
+                    mbar_wait(bar(kBarSFull), (g + 1) & 1);
+                    tc_fence_after();
+                } else if (j > 0) {
+                    mbar_wait(bar(kBarPVDone), (g - 1) & 1);
                     tc_fence_after();
                 }
-#endif
                 W4P_TRACE(j, 5);
                 tmem_st_x32(t_p, pk);
                 tmem_st_x32(t_p + 32u, pk + 32);
