@@ -511,16 +511,17 @@ def extra_shapes(pkg, torch, dev, peaks) -> dict:
         for _ in range(3):
             pkg.attention(q, k, v, out_dtype=out_dt, out=o)
         torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        iters = 20
-        e0.record()
-        for _ in range(iters):
-            pkg.attention(q, k, v, out_dtype=out_dt, out=o)
-        e1.record()
-        torch.cuda.synchronize()
-        ms = e0.elapsed_time(e1) / iters
+        iters, ms = 20, float("inf")
+        for _ in range(3):  # best of 3 bursts of 20 launches (CUDA events on the launching stream)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(iters):
+                pkg.attention(q, k, v, out_dtype=out_dt, out=o)
+            e1.record()
+            torch.cuda.synchronize()
+            ms = min(ms, e0.elapsed_time(e1) / iters)
         tf = 4.0 * b * H * n * n * D / (ms * 1e-3) / 1e12
-        out[tag] = {"ms": ms, "tflops": tf, "kernel": "lgattn::w4p (persistent CTAs)" if n <= 1024 else "lgattn::w4 (one Q tile per CTA)",
+        out[tag] = {"ms": ms, "tflops": tf, "timing": "best of 3 bursts x 20 launches", "kernel": "lgattn::w4p (persistent CTAs)" if n <= 1024 else "lgattn::w4 (one Q tile per CTA)",
                     "frac_of_measured_burst": tf / peaks["bf16_tflops"],
                     "frac_of_measured_sustained": tf / peaks["bf16_tflops_sustained"] if peaks["bf16_tflops_sustained"] else None,
                     "frac_of_nominal_2250": tf / 2250.0}

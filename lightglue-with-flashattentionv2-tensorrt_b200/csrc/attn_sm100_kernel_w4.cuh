@@ -86,6 +86,9 @@ constexpr int kRegsSoftmax = 216;
 // LG_ATTN_WHATIF=1|2|3 drop the row max | the exponentials | all arithmetic (WRONG results, timing decomposition only).
 // A variant that scanned the next tile's row max out of TMEM under chunked exponentials measured 738 vs 805 TFLOP/s and
 // was removed (git history: "max-ahead").
+#ifndef LG_ATTN_W4_PIN_SMEM
+#define LG_ATTN_W4_PIN_SMEM 1
+#endif
 #ifndef LG_ATTN_W4_MERGE_WAIT
 #define LG_ATTN_W4_MERGE_WAIT 1
 #endif
@@ -127,7 +130,14 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
                  const __grid_constant__ CUtensorMap tm_v, void* __restrict__ out, int n_q, int n_kv,
                  int tiles_m, const OutLayout ol) {
     extern __shared__ uint8_t smem_raw[];
+#if LG_ATTN_W4_PIN_SMEM
+    // keep the aligned base in a register: otherwise ptxas re-derives it (S2UR SR_CgaCtaId + ULEA + ...) in front of every
+    // mbarrier probe of the KV loop, ~1.5 % of the softmax warps' time in the ncu source view
+    uint32_t smem = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    asm volatile("mov.u32 %0, %0;" : "+r"(smem));
+#else
     const uint32_t smem = (smem_u32(smem_raw) + 1023u) & ~1023u;
+#endif
     const uint32_t bars = smem + kSmemBar;
     auto bar = [&](uint32_t i) { return bars + 8u * i; };
 

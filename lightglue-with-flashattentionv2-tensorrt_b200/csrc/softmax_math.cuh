@@ -128,18 +128,26 @@ __device__ __forceinline__ float softmax_exp_pass(const uint32_t (&sr)[kCols], u
 
 
 // row max of a slice with 3-input FMNMX chains
+#ifndef LG_ATTN_MAX_CHAINS
+#define LG_ATTN_MAX_CHAINS 4
+#endif
 template <int kCols>
 __device__ __forceinline__ float row_max(const uint32_t (&sr)[kCols]) {
-    float mx0 = __uint_as_float(sr[0]), mx1 = __uint_as_float(sr[1]);
-    float mx2 = __uint_as_float(sr[2]), mx3 = __uint_as_float(sr[3]);
+    constexpr int kCh = LG_ATTN_MAX_CHAINS;
+    float mx[kCh];
 #pragma unroll
-    for (int c = 4; c < kCols; c += 4) {
-        mx0 = fmaxf(mx0, __uint_as_float(sr[c + 0]));
-        mx1 = fmaxf(mx1, __uint_as_float(sr[c + 1]));
-        mx2 = fmaxf(mx2, __uint_as_float(sr[c + 2]));
-        mx3 = fmaxf(mx3, __uint_as_float(sr[c + 3]));
+    for (int i = 0; i < kCh; ++i) mx[i] = __uint_as_float(sr[i]);
+#pragma unroll
+    for (int c = kCh; c < kCols; c += kCh) {
+#pragma unroll
+        for (int i = 0; i < kCh; ++i) mx[i] = fmaxf(mx[i], __uint_as_float(sr[c + i]));
     }
-    return fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
+#pragma unroll
+    for (int w = kCh / 2; w > 0; w /= 2) {
+#pragma unroll
+        for (int i = 0; i < w; ++i) mx[i] = fmaxf(mx[i], mx[i + w]);
+    }
+    return mx[0];
 }
 
 }  // namespace lgattn
