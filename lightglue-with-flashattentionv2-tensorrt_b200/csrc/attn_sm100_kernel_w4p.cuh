@@ -256,7 +256,9 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
             }
 #endif
             float m_used = -INFINITY;  // row max the exponent is referenced to (raw score units)
+            float m_thr = INFINITY, neg_m = 0.f;  // rescale threshold m_used + tau/c, and -m_used*c
             float l_sum = 0.f;
+            int kv_left = n_kv;
 
             for (int j = 0; j < num_kv_tiles; ++j, ++g) {
                 W4P_TRACE(j, 0);
@@ -275,7 +277,8 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
                 W4P_TRACE(j, 2);
 
                 // ragged KV tail: columns past n_kv get -inf (TMA zero-filled K rows gave S = 0 there)
-                const int valid = n_kv - j * kBlockN;
+                const int valid = kv_left;  // running count instead of n_kv - j*128: no constant-bank reload on the critical path
+                kv_left -= kBlockN;
                 if (valid < kBlockN) {
 #pragma unroll
                     for (int c = 0; c < kBlockN; ++c)
@@ -284,21 +287,24 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
 
                 const float mx = row_max<kBlockN>(sr);
 
-                // lazy rescale decision (warp-uniform so the tcgen05.ld/st below stay aligned)
+                // lazy rescale decision (warp-uniform so the tcgen05.ld/st below stay aligned).  The threshold and the scaled
+                // reference are carried across tiles, so the common no-rescale step costs one compare + vote.
                 float alpha = 1.f;
                 bool rescale = false;
                 if (j == 0) {
                     m_used = mx;
+                    m_thr = mx + kTau / kScaleLog2;
+                    neg_m = -mx * kScaleLog2;
                 } else {
-                    const bool need = (mx - m_used) * kScaleLog2 > kTau;
-                    rescale = __any_sync(0xffffffffu, need);
+                    rescale = __any_sync(0xffffffffu, mx > m_thr);
                     if (rescale) {
                         const float m_new = fmaxf(m_used, mx);
                         alpha = ex2_approx((m_used - m_new) * kScaleLog2);
                         m_used = m_new;
+                        m_thr = m_new + kTau / kScaleLog2;
+                        neg_m = -m_new * kScaleLog2;
                     }
                 }
-                const float neg_m = -m_used * kScaleLog2;
                 W4P_TRACE(j, 3);
 
                 // one monolithic pass: splitting it into column chunks with the P stores / barrier probes in between
