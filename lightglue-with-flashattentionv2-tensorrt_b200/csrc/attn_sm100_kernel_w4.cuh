@@ -86,6 +86,9 @@ constexpr int kRegsSoftmax = 216;
 // LG_ATTN_WHATIF=1|2|3 drop the row max | the exponentials | all arithmetic (WRONG results, timing decomposition only).
 // A variant that scanned the next tile's row max out of TMEM under chunked exponentials measured 738 vs 805 TFLOP/s and
 // was removed (git history: "max-ahead").
+// Measured and dropped (same-box A/B against 832-835 TFLOP/s at B64 N2048): S read back in two halves with half the row max
+// under the second TMEM load 827; arriving lane from elect.sync instead of lane == 0 835 (no difference); S(j+1) read back
+// right behind the P(j) store (loop-carried S registers) spills 72 B at any softmax / service register split.
 #ifndef LG_ATTN_W4_PIN_SMEM
 #define LG_ATTN_W4_PIN_SMEM 1
 #endif
