@@ -16,3 +16,8 @@ for (b, n) in ((1, 1024), (64, 2048)):
         pkg.attention(q, k, v, out_dtype=out_dt)
     torch.cuda.synchronize()
 print("ok")
+# third shape: full grid with few KV tiles per Q tile -> persistent throughput kernel w4p
+q = torch.randn(128, 4, 1024, 64, device="cuda").half(); k = torch.randn_like(q); v = torch.randn_like(q)
+pkg.attention(q, k, v)
+torch.cuda.synchronize()
+print("ok w4p")
