@@ -103,7 +103,35 @@ class ClockSampler:
                 "samples": len(self.samples)}
 
 
+_FULL_AFFINITY = os.sched_getaffinity(0) if hasattr(os, "sched_getaffinity") else None
+
+
+class all_host_cores:
+    """CPU-baseline legs use every core this process was started with, whatever GPU-local binding the e2e legs run under."""
+
+    def __enter__(self):
+        self.prev = os.sched_getaffinity(0) if _FULL_AFFINITY is not None else None
+        if self.prev is not None and self.prev != _FULL_AFFINITY:
+            os.sched_setaffinity(0, _FULL_AFFINITY)
+        return self
+
+    def __exit__(self, *exc):
+        if self.prev is not None and self.prev != _FULL_AFFINITY:
+            os.sched_setaffinity(0, self.prev)
+        return False
+
+
 def cpu_baseline_sample(reps: int) -> dict:
+    with all_host_cores():
+        return _cpu_baseline_sample(reps)
+
+
+def cpu_pairs_sample(kpts: int, reps: int = 1) -> dict:
+    with all_host_cores():
+        return _cpu_pairs_sample(kpts, reps)
+
+
+def _cpu_baseline_sample(reps: int) -> dict:
     """The reference's CPU path (lightglue_pytorch_no_plugin Attention.forward, lightglue.py:82-85) restated by
     the oracle's torch-CPU port, timed on this host with all cores on a bounded sample of the workload."""
     import torch
@@ -152,7 +180,7 @@ def synth_features_host(torch, pairs: int, kpts: int, seed: int):
     return kp.pin_memory(), d.pin_memory()
 
 
-def cpu_pairs_sample(kpts: int, reps: int = 1) -> dict:
+def _cpu_pairs_sample(kpts: int, reps: int = 1) -> dict:
     """The reference's CPU path for a whole pair (lightglue_pytorch_no_plugin LightGlue.forward + filter_matches),
     restated by oracle/matcher_oracle.py (pinned on reference-generated fixtures), FP32 torch CPU, all cores."""
     import torch
@@ -347,6 +375,16 @@ def run_ours(args) -> None:
         raise SystemExit("bench.py: no CUDA device (the product path has no CPU fallback)")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    # one process per GPU: run on (and first-touch pinned staging buffers from) the CPUs local to that GPU, so that the
+    # host<->device copies of the e2e legs do not cross the socket interconnect when 8 ranks run at once
+    # (the CPU-baseline legs must keep every core: spawn torch's worker pool BEFORE narrowing this thread's mask — pool threads
+    # keep the mask they were created with — and widen the main thread again around those legs, `all_host_cores`)
+    torch.set_num_threads(os.cpu_count() or 1)
+    _w = torch.randn(512, 512)
+    (_w @ _w).sum().item()
+    props = torch.cuda.get_device_properties(local)
+    placement = {"bound": False, "why": "LG_BENCH_NO_BIND"} if os.environ.get("LG_BENCH_NO_BIND") else \
+        pkg.sharding.bind_host_to_gpu(f"{props.pci_domain_id:04x}:{props.pci_bus_id:02x}:{props.pci_device_id:02x}.0")
     if world > 1:
         if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
             os.environ["NCCL_DEBUG"] = "WARN"   # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
@@ -486,7 +524,7 @@ def run_ours(args) -> None:
                          "hbm_floor_us": BYTES_PER_CALL / (peaks["hbm_gbs"] * 1e9) * 1e6,
                          "note": "latency-bound shape: 32 Q tiles x 4 KV splits = 128 CTAs on 148 SMs; duration = timed region / launches (includes launch gaps)"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": CALLS * (qs + ks + vs), "d2h_bytes_per_step": CALLS * os_,
-                    "steps": e2e_steps, "timing": "host wall clock around submit+sync, pinned host buffers, 4 streams",
+                    "steps": e2e_steps, "timing": "host wall clock around submit+sync, pinned host buffers, 4 streams", "host_placement": placement,
                     "note": "PCIe-bound: 2 MiB cross the Gen5 x16 link per 1.07 GFLOP problem (tools/e2e_probe.py: host issue 13 us, total 45 us per problem = 46 GB/s)"},
             "clocks": clocks,
             "extra": extra,

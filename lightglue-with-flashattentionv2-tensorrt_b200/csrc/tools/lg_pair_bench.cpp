@@ -11,9 +11,11 @@
 // through lg_matcher_submit_host / lg_matcher_sync (inputs of sub-batch i+1 staged under forward i).  Pure C++ over the C-ABI (include/lg_matcher.h): no Python, torch or TensorRT.
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
+#include <sched.h>
 #include <sys/wait.h>
 #include <unistd.h>
 
+#include <cctype>
 #include <chrono>
 #include <cmath>
 #include <cstdio>
@@ -38,11 +40,42 @@ struct WorkerResult {
     int rc;
 };
 
+// Run this worker on the CPUs local to its GPU (/sys/bus/pci/devices/<pci>/local_cpulist), so that the pinned
+// host buffers it first-touches next sit on the GPU's own NUMA node.  Best effort; returns the number of CPUs
+// bound to, 0 when nothing was changed.
+static int bind_to_gpu_local_cpus(int device) {
+    char bus[32] = {0};
+    if (cudaDeviceGetPCIBusId(bus, sizeof(bus), device) != cudaSuccess) { (void)cudaGetLastError(); return 0; }
+    for (char* c = bus; *c; ++c) *c = static_cast<char>(tolower(*c));
+    const std::string path = std::string("/sys/bus/pci/devices/") + bus + "/local_cpulist";
+    FILE* f = fopen(path.c_str(), "r");
+    if (f == nullptr) return 0;
+    char line[4096] = {0};
+    const bool ok = fgets(line, sizeof(line), f) != nullptr;
+    fclose(f);
+    if (!ok) return 0;
+    cpu_set_t allowed, target;
+    if (sched_getaffinity(0, sizeof(allowed), &allowed) != 0) return 0;
+    CPU_ZERO(&target);
+    int n = 0;
+    for (char* tok = strtok(line, ",\n"); tok != nullptr; tok = strtok(nullptr, ",\n")) {
+        int lo = 0, hi = 0;
+        const int got = sscanf(tok, "%d-%d", &lo, &hi);
+        if (got < 1) continue;
+        if (got == 1) hi = lo;
+        for (int c = lo; c <= hi && c < CPU_SETSIZE; ++c)
+            if (c >= 0 && CPU_ISSET(c, &allowed)) { CPU_SET(c, &target); ++n; }
+    }
+    if (n == 0 || sched_setaffinity(0, sizeof(target), &target) != 0) return 0;
+    return n;
+}
+
 static int worker(const Args& a, int rank, const std::vector<char>& blob, WorkerResult* res) {
     res->rc = 0;
     lg_matcher* eng = nullptr;
     int rc = lg_matcher_create(&eng, rank, a.layers, blob.data(), blob.size(), 0.0f);
     if (rc != 0) { fprintf(stderr, "rank %d: lg_matcher_create: %s\n", rank, lg_attn_error_string(rc)); return rc; }
+    if (getenv("LG_BENCH_NO_BIND") == nullptr) (void)bind_to_gpu_local_cpus(rank);
     const int n = a.kpts, sub = a.sub < a.pairs ? a.sub : a.pairs;
     // pinned host features for this rank's pairs (global pair id p = rank + i * gpus seeds the generator)
     float *k0, *k1, *ms;

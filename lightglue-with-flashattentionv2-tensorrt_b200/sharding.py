@@ -51,3 +51,62 @@ def gather_to_host(dist, local: dict) -> dict | None:
                 raise RuntimeError(f"pair {k} was matched by two ranks")
             merged[k] = v
     return merged
+
+
+def parse_cpulist(text: str) -> set[int]:
+    """``"0-3,8,10-11"`` (the sysfs ``local_cpulist`` format) -> {0, 1, 2, 3, 8, 10, 11}."""
+    cpus: set[int] = set()
+    for part in text.strip().split(","):
+        part = part.strip()
+        if not part:
+            continue
+        lo, _, hi = part.partition("-")
+        a, b = int(lo), int(hi or lo)
+        if b < a:
+            raise ValueError(f"bad cpu range {part!r}")
+        cpus.update(range(a, b + 1))
+    return cpus
+
+
+def bind_host_to_gpu(pci_bus_id: str, sysfs_root: str = "/sys/bus/pci/devices") -> dict:
+    """Pin the calling process to the CPUs local to one GPU (``<sysfs>/<pci>/local_cpulist``).
+
+    One process drives one GPU; its pinned staging buffers are first-touched after this call and so
+    land on the GPU's own NUMA node — host<->device copies of 8 ranks then stay off the socket
+    interconnect.  Best effort: returns ``{"bound": False, "why": ...}`` when sysfs has no entry, the
+    list does not intersect the cpuset this process may use, or the kernel refuses.
+    """
+    import os
+
+    dev = pci_bus_id.lower()
+    if dev.count(":") == 1:
+        dev = "0000:" + dev
+    path = os.path.join(sysfs_root, dev, "local_cpulist")
+    try:
+        with open(path) as f:
+            local = parse_cpulist(f.read())
+    except (OSError, ValueError) as exc:
+        return {"bound": False, "why": f"{path}: {exc.__class__.__name__}"}
+    try:
+        allowed = os.sched_getaffinity(0)
+    except (AttributeError, OSError):
+        return {"bound": False, "why": "sched_getaffinity unavailable"}
+    target = local & allowed
+    if not target:
+        return {"bound": False, "why": "local cpus not in this process's cpuset"}
+    if target == allowed:
+        return {"bound": True, "cpus": len(target), "numa_node": _read_int(os.path.join(sysfs_root, dev, "numa_node")),
+                "note": "already local"}
+    try:
+        os.sched_setaffinity(0, target)
+    except OSError as exc:
+        return {"bound": False, "why": f"sched_setaffinity: {exc.__class__.__name__}"}
+    return {"bound": True, "cpus": len(target), "numa_node": _read_int(os.path.join(sysfs_root, dev, "numa_node"))}
+
+
+def _read_int(path: str):
+    try:
+        with open(path) as f:
+            return int(f.read().strip())
+    except (OSError, ValueError):
+        return None

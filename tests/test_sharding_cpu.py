@@ -71,3 +71,32 @@ def test_single_process_paths_need_no_process_group():
     sh = pkg.sharding
     assert sh.max_over_ranks(dist, 0.25) == 0.25
     assert sh.gather_to_host(dist, {0: 1}) == {0: 1}
+
+
+def test_cpulist_parsing_and_gpu_local_binding(tmp_path):
+    import os
+
+    from lgattn_pkg import pkg
+
+    sh = pkg.sharding
+    assert sh.parse_cpulist("0-3,8,10-11\n") == {0, 1, 2, 3, 8, 10, 11}
+    assert sh.parse_cpulist("") == set()
+    # no sysfs entry: reported, not raised
+    assert sh.bind_host_to_gpu("0000:ff:00.0", sysfs_root=str(tmp_path))["bound"] is False
+    # a fake device whose local CPUs are exactly one CPU this process may use
+    before = os.sched_getaffinity(0)
+    cpu = min(before)
+    d = tmp_path / "0000:1b:00.0"
+    d.mkdir()
+    (d / "local_cpulist").write_text(f"{cpu}\n")
+    (d / "numa_node").write_text("1\n")
+    try:
+        r = sh.bind_host_to_gpu("1B:00.0", sysfs_root=str(tmp_path))
+        assert r["bound"] is True and r["numa_node"] == 1
+        assert os.sched_getaffinity(0) == {cpu}
+    finally:
+        os.sched_setaffinity(0, before)
+    # local CPUs outside the cpuset: left alone
+    (d / "local_cpulist").write_text("100000\n")
+    assert sh.bind_host_to_gpu("0000:1b:00.0", sysfs_root=str(tmp_path))["bound"] is False
+    assert os.sched_getaffinity(0) == before
