@@ -123,6 +123,25 @@ class ClockSampler:
                 "samples": len(self.samples), "samples_in_timed_region": cut, "source": "NVML polled in-process under load"}
 
 
+_RESULT_OUT = None
+
+
+def claim_stdout() -> None:
+    """Rank 0 prints ONE JSON line on stdout: keep the real stdout for it and point fd 1 at stderr for everything else
+    (NCCL prints its version banner on stdout whenever NCCL_DEBUG >= VERSION, as this pool's boxes set it)."""
+    global _RESULT_OUT
+    if _RESULT_OUT is None:
+        sys.stdout.flush()
+        _RESULT_OUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
+def emit(line: dict) -> None:
+    out = _RESULT_OUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 _FULL_AFFINITY = os.sched_getaffinity(0) if hasattr(os, "sched_getaffinity") else None
 
 
@@ -402,7 +421,7 @@ def run_reference(args) -> None:
             "cpu_baseline": cb,
             "e2e": {"value": tf, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "pairs": pairs}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def run_ours(args) -> None:
@@ -429,8 +448,6 @@ def run_ours(args) -> None:
     placement = {"bound": False, "why": "LG_BENCH_NO_BIND"} if os.environ.get("LG_BENCH_NO_BIND") else \
         pkg.sharding.bind_host_to_gpu(f"{props.pci_domain_id:04x}:{props.pci_bus_id:02x}:{props.pci_device_id:02x}.0")
     if world > 1:
-        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"   # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
         dist.init_process_group("nccl", device_id=dev)
     lib = pkg.load()
     pkg._binding.check(lib.lg_attn_hd64_init_device(local), "init_device")
@@ -587,7 +604,7 @@ def run_ours(args) -> None:
         }
         if cpu is not None:
             line["cpu_baseline"] = cpu
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -634,12 +651,14 @@ def main() -> None:
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.impl == "reference":
+        claim_stdout()
         run_reference(args)
         return
     if args.gpus > 1 and "WORLD_SIZE" not in os.environ:
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}", "--master-addr",
                "127.0.0.1", "--master-port", "29533", __file__] + sys.argv[1:]
         raise SystemExit(subprocess.call(cmd))
+    claim_stdout()
     run_ours(args)
 
 
