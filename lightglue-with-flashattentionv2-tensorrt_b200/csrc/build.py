@@ -21,8 +21,7 @@ LIB = BUILD / "liblightglue_attention_plugin.so"
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 SOURCES = [CSRC / "lg_attn_api.cu", CSRC / "lg_match_kernels.cu", CSRC / "lg_matcher.cu", CSRC / "plugin" / "lightglue_attention_plugin.cpp",
            CSRC / "plugin" / "mock_trt_host.cpp"]
-HEADERS = [CSRC / "tools" / "lg_pair_bench.cpp", CSRC / "attn_sm100_kernel.cuh", CSRC / "attn_sm100_kernel_w4.cuh", CSRC / "attn_sm100_kernel_w4p.cuh", CSRC / "softmax_math.cuh",
-           CSRC / "cvt_f32_f16.cuh", CSRC / "attn_sm100.h", CSRC / "ptx_sm100.cuh",
+HEADERS = [CSRC / "tools" / "lg_pair_bench.cpp", *sorted(CSRC.glob("*.cuh")), CSRC / "attn_sm100.h",
            CSRC / "plugin" / "lightglue_attention_plugin.h", CSRC / "plugin" / "mock_nvinfer" / "NvInfer.h",
            CSRC.parent.parent / "include" / "lg_attn.h", CSRC.parent.parent / "include" / "lg_match.h", CSRC.parent.parent / "include" / "lg_matcher.h"]
 

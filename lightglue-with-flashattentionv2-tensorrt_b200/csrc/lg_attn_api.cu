@@ -11,6 +11,7 @@
 #include "attn_sm100_kernel.cuh"     // lgattn::w8 — latency shapes, split-KV clusters, PDL
 #include "attn_sm100_kernel_w4.cuh"  // lgattn::w4 — full grids, one Q tile per CTA (kept for A/B: LG_ATTN_PERSIST=0)
 #include "attn_sm100_kernel_w4p.cuh" // lgattn::w4p — full grids, persistent CTAs (throughput)
+#include "attn_sm100_kernel_mq.cuh"  // lgattn::mq — full grids, one persistent CTA per SM owning several Q tiles (throughput)
 #include "cvt_f32_f16.cuh"
 
 #include <cuda.h>
@@ -46,6 +47,24 @@ std::atomic<int> g_use_persist{-1};       // full grids: -1 = automatic (persist
                                           // 0 / 1 = force the one-tile-per-CTA / persistent kernel (LG_ATTN_PERSIST, tests)
 constexpr int kPersistMaxKvTiles = 8;     // measured crossover (B200): +4 % at 8 KV tiles, -1 % at 16 and 32
 
+// The multi-Q-tile kernel variants compiled into the library (lg_attn_debug_set_throughput_kernel modes 2, 3, ...).
+template <int T, int BN, bool A, bool L>
+struct MqVariant {
+    static constexpr int kT = T, kBN = BN;
+    static constexpr bool kAlias = A, kLazy = L;
+    using C = mq::Cfg<T, BN, A>;
+};
+constexpr int kMqModeBase = 2;
+template <typename F>
+void mq_for_each_variant(F&& f) {
+    f(MqVariant<2, 128, false, false>{});   // mode 2
+    f(MqVariant<4, 64, true, true>{});      // mode 3
+    f(MqVariant<4, 64, true, false>{});     // mode 4
+    f(MqVariant<3, 64, false, false>{});    // mode 5
+    f(MqVariant<3, 64, true, true>{});      // mode 6
+}
+constexpr int kMqVariants = 5;
+
 int resolve_encode() {
     if (g_encode.load(std::memory_order_acquire) != nullptr) return 0;
     void* fn = nullptr;
@@ -78,7 +97,8 @@ bool strides_ok(const RowStrides& st, int batch, int heads, int rows, int elem_b
     return ok(st.batch, batch) && ok(st.head, heads) && ok(st.row, rows) && (rows == 1 || st.row >= kHeadDim);
 }
 
-int encode_rows_map(CUtensorMap* map, const void* base, int rows, int heads, int batch, const RowStrides& st) {
+int encode_rows_map(CUtensorMap* map, const void* base, int rows, int heads, int batch, const RowStrides& st,
+                    int box_rows = kBlockN) {
     const cuuint64_t dims[4] = {static_cast<cuuint64_t>(kHeadDim), static_cast<cuuint64_t>(rows),
                                 static_cast<cuuint64_t>(heads), static_cast<cuuint64_t>(batch)};
     // extent-1 dimensions never advance; give them any legal stride
@@ -86,7 +106,7 @@ int encode_rows_map(CUtensorMap* map, const void* base, int rows, int heads, int
     const cuuint64_t shead = heads > 1 ? static_cast<cuuint64_t>(st.head) * 2 : srow;
     const cuuint64_t sbatch = batch > 1 ? static_cast<cuuint64_t>(st.batch) * 2 : srow;
     const cuuint64_t strides[3] = {srow, shead, sbatch};
-    const cuuint32_t box[4] = {static_cast<cuuint32_t>(kHeadDim), static_cast<cuuint32_t>(kBlockN), 1, 1};
+    const cuuint32_t box[4] = {static_cast<cuuint32_t>(kHeadDim), static_cast<cuuint32_t>(box_rows), 1, 1};
     const cuuint32_t estr[4] = {1, 1, 1, 1};
     CUresult r = g_encode.load(std::memory_order_acquire)(
         map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
@@ -106,7 +126,10 @@ int init_device_locked(int device) {
         if (v == 1 || v == 2 || v == 4 || v == 8) g_forced_splits.store(v, std::memory_order_relaxed);
     }
     if (const char* env = getenv("LG_ATTN_PDL")) g_use_pdl.store(atoi(env) != 0 ? 1 : 0, std::memory_order_relaxed);
-    if (const char* env = getenv("LG_ATTN_PERSIST")) g_use_persist.store(atoi(env) < 0 ? -1 : (atoi(env) != 0 ? 1 : 0), std::memory_order_relaxed);
+    if (const char* env = getenv("LG_ATTN_PERSIST")) {
+        const int v = atoi(env);
+        g_use_persist.store(v < 0 ? -1 : (v < kMqModeBase + kMqVariants ? v : 1), std::memory_order_relaxed);
+    }
     int rc = resolve_encode();
     if (rc != 0) return rc;
     int prev = -1;
@@ -125,6 +148,11 @@ int init_device_locked(int device) {
     opt_in(reinterpret_cast<const void*>(w4::lg_attn_hd64_fwd<true>), w4::kSmemBytes);
     opt_in(reinterpret_cast<const void*>(w4p::lg_attn_hd64_fwd<false>), w4p::kSmemBytes);
     opt_in(reinterpret_cast<const void*>(w4p::lg_attn_hd64_fwd<true>), w4p::kSmemBytes);
+    mq_for_each_variant([&](auto v) {
+        using V = decltype(v);
+        opt_in(reinterpret_cast<const void*>(mq::lg_attn_hd64_fwd<V::kT, V::kBN, V::kAlias, V::kLazy, false>), V::C::kSmemBytes);
+        opt_in(reinterpret_cast<const void*>(mq::lg_attn_hd64_fwd<V::kT, V::kBN, V::kAlias, V::kLazy, true>), V::C::kSmemBytes);
+    });
     opt_in(reinterpret_cast<const void*>(w8::lg_attn_hd64_fwd<false, false>), w8::kSmemBytes);
     opt_in(reinterpret_cast<const void*>(w8::lg_attn_hd64_fwd<true, false>), w8::kSmemBytes);
     opt_in(reinterpret_cast<const void*>(w8::lg_attn_hd64_fwd<false, true>), w8::kSmemBytes + w8::kSmemSplitExtra);
@@ -170,6 +198,11 @@ extern "C" int lg_attn_debug_read_w4_trace(long long* dst, unsigned* smid) {
         if (e == cudaSuccess) e = cudaMemcpyFromSymbol(smid, lgattn::w4::g_w4_smid, sizeof(lgattn::w4::g_w4_smid));
     }
     return static_cast<int>(e);
+}
+#endif
+#ifdef LG_ATTN_MQ_TRACE
+extern "C" int lg_attn_debug_read_mq_trace(long long* dst) {
+    return static_cast<int>(cudaMemcpyFromSymbol(dst, lgattn::mq::g_mq_trace, sizeof(lgattn::mq::g_mq_trace)));
 }
 #endif
 #ifdef LG_ATTN_TRACE
@@ -218,7 +251,30 @@ static int launch_core(const void* qh, const void* kh, const void* vh, void* o, 
     unsigned n_attrs = 0;
     const int persist_mode = g_use_persist.load(std::memory_order_relaxed);
     const bool persist = persist_mode < 0 ? kv_tiles <= kPersistMaxKvTiles : persist_mode != 0;
-    if (full_grid && persist) {
+    if (full_grid && persist_mode >= kMqModeBase) {
+        // one persistent CTA per SM, kT Q tiles per work item, K/V tiles of kBN rows shared by the kT tiles
+        int idx = kMqModeBase;
+        mq_for_each_variant([&](auto v) {
+            using V = decltype(v);
+            if (idx++ != persist_mode || e != cudaSuccess || rc != 0) return;
+            if (V::kBN != kBlockN) {
+                if ((rc = encode_rows_map(&tm_k, kh, n_kv, heads, batch, sk, V::kBN)) != 0) return;
+                if ((rc = encode_rows_map(&tm_v, vh, n_kv, heads, batch, sv, V::kBN)) != 0) return;
+            }
+            const long long groups = (tiles_m_ll + V::kT - 1) / V::kT;
+            const long long items = bh_ll * groups;
+            cfg.gridDim = dim3(static_cast<unsigned>(items < g_sm_count[device] ? items : g_sm_count[device]));
+            cfg.blockDim = dim3(V::C::kThreads);
+            cfg.dynamicSmemBytes = V::C::kSmemBytes;
+            cfg.attrs = attrs;
+            cfg.numAttrs = 0;
+            e = cudaLaunchKernelEx(&cfg,
+                                   !out_f32 ? mq::lg_attn_hd64_fwd<V::kT, V::kBN, V::kAlias, V::kLazy, false>
+                                            : mq::lg_attn_hd64_fwd<V::kT, V::kBN, V::kAlias, V::kLazy, true>,
+                                   tm_q, tm_k, tm_v, o, n_q, n_kv, static_cast<int>(groups), static_cast<int>(items), ol);
+        });
+        if (rc != 0) return rc;
+    } else if (full_grid && persist) {
         // persistent: 2 resident CTAs per SM walk the Q tiles blockIdx.x + i * gridDim.x
         cfg.gridDim = dim3(static_cast<unsigned>(2 * g_sm_count[device]));
         cfg.blockDim = dim3(w4p::kThreads);
@@ -284,7 +340,7 @@ extern "C" {
 int lg_attn_version(void) { return kAbiVersion; }
 
 int lg_attn_debug_set_throughput_kernel(int mode) {
-    if (mode < -1 || mode > 1) return LG_ATTN_EINVAL;
+    if (mode < -1 || mode >= kMqModeBase + kMqVariants) return LG_ATTN_EINVAL;
     g_use_persist.store(mode, std::memory_order_relaxed);
     return 0;
 }

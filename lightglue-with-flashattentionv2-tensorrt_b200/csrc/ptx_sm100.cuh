@@ -103,6 +103,20 @@ __device__ __forceinline__ void mbar_wait_backoff(uint32_t bar, uint32_t parity,
 #endif
 }
 
+// One lane of a converged warp (elect.sync): the issuing lane of TMA / tcgen05 instructions in the service warps.  Unlike a
+// `lane == 0` test, ptxas keeps the elected branch on the uniform datapath (no per-instruction R2UR / BRA.U.ANY waterfall).
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred px;\n\t"
+        "elect.sync _|px, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, px;\n\t"
+        "}\n"
+        : "=r"(pred));
+    return pred != 0;
+}
+
 // named barrier among `count` threads (ids 1..15; id 0 is __syncthreads)
 __device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t count) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");

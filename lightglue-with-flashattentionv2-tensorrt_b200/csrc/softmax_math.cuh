@@ -11,6 +11,7 @@
 //   LG_ATTN_POLY_OF_8    how many of every 8 columns take the polynomial path
 //   LG_ATTN_PACKED_SCALE 1: the s*c - m*c FFMA runs two columns per FFMA2 on the MUFU-path columns
 //   LG_ATTN_PACKED_SUM   1: row sums accumulate with FADD2
+//   LG_ATTN_PACKED_POLY  1: polynomial columns in pairs on FFMA2
 #pragma once
 #include "ptx_sm100.cuh"
 
@@ -19,6 +20,9 @@
 #endif
 #ifndef LG_ATTN_PACKED_SCALE
 #define LG_ATTN_PACKED_SCALE 1
+#endif
+#ifndef LG_ATTN_PACKED_POLY
+#define LG_ATTN_PACKED_POLY 0   // 1: polynomial columns are processed in pairs with FFMA2 (ex2_poly_pair)
 #endif
 #ifndef LG_ATTN_PACKED_SUM
 #define LG_ATTN_PACKED_SUM 1
@@ -35,6 +39,10 @@ constexpr float kScaleLog2 = 0.125f * 1.4426950408889634f;
 #define LG_ATTN_TAU 8.0f
 #endif
 constexpr float kTau = LG_ATTN_TAU;
+// lazy row max (attn_sm100_kernel_mq.cuh): a step whose row sum reaches this is redone with the true row max.  2^(tau-1): the
+// polynomial path saturates at 2^tau * 0.99993, so the trigger has to sit below that.
+constexpr float kLazyTrigger = 128.0f;
+static_assert(LG_ATTN_TAU == 8.0f, "kLazyTrigger assumes tau = 8");
 
 // ---- polynomial exp2 on the FMA pipes -----------------------------------------------------------
 // x = s*c - m*c lies in (-inf, kTau].  y = sat((x + 120) / 128) in [0, 1] comes out of ONE saturating
@@ -72,6 +80,27 @@ __device__ __forceinline__ float ex2_poly(float s, const PolyConsts& pc) {
     return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
 }
 
+// Two columns at once: the clamp stays scalar (fma.sat has no f32x2 form), range reduction and Horner steps run as FFMA2 / FADD2
+// (one issue slot for two columns; 5 instead of 8 issue slots per column).
+__device__ __forceinline__ void ex2_poly_pair(float s0, float s1, const PolyConsts& pc, float& p0, float& p1) {
+    float y0, y1;
+    asm("fma.rn.sat.f32 %0, %1, %2, %3;" : "=f"(y0) : "f"(s0), "f"(pc.scale), "f"(pc.bias));
+    asm("fma.rn.sat.f32 %0, %1, %2, %3;" : "=f"(y1) : "f"(s1), "f"(pc.scale), "f"(pc.bias));
+    const uint64_t y = pack_f32x2(y0, y1);
+    const uint64_t k128 = pack_f32x2(128.f, 128.f), magic = pack_f32x2(kMagic, kMagic);
+    const uint64_t t = fma_f32x2(y, k128, magic);   // integer part of x' in the low mantissa bits
+    const uint64_t nn = sub_f32x2(magic, t);        // -round(x')
+    const uint64_t f = fma_f32x2(y, k128, nn);      // x' - round(x') in [-0.5, 0.5]
+    uint64_t p = fma_f32x2(f, pack_f32x2(kC3, kC3), pack_f32x2(kC2, kC2));
+    p = fma_f32x2(p, f, pack_f32x2(kC1, kC1));
+    p = fma_f32x2(p, f, pack_f32x2(kC0, kC0));
+    float q0, q1, t0, t1;
+    unpack_f32x2(p, q0, q1);
+    unpack_f32x2(t, t0, t1);
+    p0 = __int_as_float(__float_as_int(q0) + (__float_as_int(t0) << 23));
+    p1 = __int_as_float(__float_as_int(q1) + (__float_as_int(t1) << 23));
+}
+
 // ---- one row slice ------------------------------------------------------------------------------
 // sr[kCols]: raw scores (bit patterns); pk[kCols/2]: FP16 pairs (column 2i in the low half).
 // Returns the FP32 sum of the (unrounded) probabilities.
@@ -84,7 +113,9 @@ __device__ __forceinline__ float softmax_exp_pass(const uint32_t (&sr)[kCols], u
     for (int c = 0; c < kCols; c += 2) {
         const bool poly0 = ((c % 8) < LG_ATTN_POLY_OF_8);
         const bool poly1 = (((c + 1) % 8) < LG_ATTN_POLY_OF_8);
-        if (!poly0 && !poly1 && LG_ATTN_PACKED_SCALE) {
+        if (poly0 && poly1 && LG_ATTN_PACKED_POLY) {
+            ex2_poly_pair(__uint_as_float(sr[c]), __uint_as_float(sr[c + 1]), pc, p[c], p[c + 1]);
+        } else if (!poly0 && !poly1 && LG_ATTN_PACKED_SCALE) {
             float x0, x1;
             unpack_f32x2(fma_f32x2(pack_f32x2(__uint_as_float(sr[c]), __uint_as_float(sr[c + 1])),
                                    pack_f32x2(kScaleLog2, kScaleLog2), pack_f32x2(neg_m_scaled, neg_m_scaled)),
