@@ -45,9 +45,10 @@ enum lg_attn_io_dtype {
 /* ABI version of this header (bumped on any signature change). */
 int lg_attn_version(void);
 
-/* Test / tuning hook (no reference counterpart): which of the two full-grid kernels lg_attn_hd64_launch* picks.
- * -1 automatic (default: persistent CTAs when a Q tile spans <= 8 KV tiles, else one Q tile per CTA),
- * 0 one Q tile per CTA, 1 persistent CTAs.  Same results either way; also settable as LG_ATTN_PERSIST. */
+/* Test / tuning hook (no reference counterpart): which full-grid (throughput) kernel lg_attn_hd64_launch* uses.
+ * -1 automatic (default: whichever packs the launch best, see choose_full_grid_kernel in lg_attn_api.cu),
+ * 0 one 128-row Q tile per CTA, 1 persistent CTAs owning four Q tiles (64-row KV steps), 2 persistent CTAs owning two Q
+ * tiles (128-row KV steps).  All meet the same tolerances; also settable as LG_ATTN_FULL_GRID_KERNEL. */
 int lg_attn_debug_set_throughput_kernel(int mode);
 
 /* Per-device one-time setup (shared-memory opt-in, driver entry point lookup). Idempotent and

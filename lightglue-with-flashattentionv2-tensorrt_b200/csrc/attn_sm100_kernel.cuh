@@ -177,44 +177,53 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
     const int kv_tile0 = split * kv_base + (split < kv_rem ? split : kv_rem);
     const int prologue_tiles = num_kv_tiles < kStages ? num_kv_tiles : kStages;
 
-    if (warp == kSoftmaxWarps && lane == 0) {
+    // Service warps run converged and issue through one elected lane (elect.sync): inside a `lane == 0` branch ptxas cannot prove
+    // that the operands of UTMALDG / UTCHMMA / UTCBAR are warp-uniform and wraps every one of them in an R2UR + BRA.U.ANY waterfall
+    // loop (~80 clk each; see attn_sm100_kernel_mq.cuh).  smem_u is the un-pinned (provably uniform) copy of the aligned base.
+    const uint32_t smem_u = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t bars_u = smem_u + kSmemBar;
+    auto ubar = [&](uint32_t i) { return bars_u + 8u * i; };
+    auto usmem_k = [&](int s) { return smem_u + kSmemRing + static_cast<uint32_t>(s) * kStageBytes; };
+    auto usmem_v = [&](int s) { return smem_u + kSmemRing + static_cast<uint32_t>(s) * kStageBytes + kTileBytes; };
+    if (warp == kSoftmaxWarps && elect_one()) {
         prefetch_tmap(&tm_q);
         prefetch_tmap(&tm_k);
         prefetch_tmap(&tm_v);
-        mbar_init(bar(kBarQFull), 1);
+        mbar_init(ubar(kBarQFull), 1);
         for (int s = 0; s < kStages; ++s) {
-            mbar_init(bar(kBarKFull + s), 1);
-            mbar_init(bar(kBarKEmpty + s), 1);
-            mbar_init(bar(kBarVFull + s), 1);
-            mbar_init(bar(kBarVEmpty + s), 1);
+            mbar_init(ubar(kBarKFull + s), 1);
+            mbar_init(ubar(kBarKEmpty + s), 1);
+            mbar_init(ubar(kBarVFull + s), 1);
+            mbar_init(ubar(kBarVEmpty + s), 1);
         }
-        mbar_init(bar(kBarSFull), 1);
-        mbar_init(bar(kBarSEmpty), kSoftmaxWarps);  // one arrival per softmax warp
-        mbar_init(bar(kBarPFull), kSoftmaxWarps);
-        mbar_init(bar(kBarPVDone), 1);
+        mbar_init(ubar(kBarSFull), 1);
+        mbar_init(ubar(kBarSEmpty), kSoftmaxWarps);  // one arrival per softmax warp
+        mbar_init(ubar(kBarPFull), kSoftmaxWarps);
+        mbar_init(ubar(kBarPVDone), 1);
 #if LG_ATTN_COMB_MBAR == 2
         {   // one arrival per (sender warp or half-warp) whose rows this CTA owns
             const int rp = num_splits > 1 ? kBlockM / num_splits : kBlockM;
-            mbar_init(bar(kBarComb), static_cast<uint32_t>(2 * rp / (rp < 32 ? rp : 32) * num_splits));
+            mbar_init(ubar(kBarComb), static_cast<uint32_t>(2 * rp / (rp < 32 ? rp : 32) * num_splits));
         }
 #else
-        mbar_init(bar(kBarComb), LG_ATTN_COMB_MBAR ? kSoftmaxWarps * 32 : 1);
+        mbar_init(ubar(kBarComb), LG_ATTN_COMB_MBAR ? kSoftmaxWarps * 32 : 1);
 #endif
         fence_mbar_init();
         // Everything above is independent of earlier kernels in the stream; the loads are not.
         pdl_wait_prior_grids();
         LG_TRACE(12);
         // First loads go out before the CTA-wide setup barrier (they only need this thread's inits).
-        mbar_arrive_expect_tx(bar(kBarQFull), kTileBytes);
-        tma_load_4d(smem + kSmemQ, &tm_q, bar(kBarQFull), 0, tile_m * kBlockM, hi, bi);
+        mbar_arrive_expect_tx(ubar(kBarQFull), kTileBytes);
+        tma_load_4d(smem_u + kSmemQ, &tm_q, ubar(kBarQFull), 0, tile_m * kBlockM, hi, bi);
         for (int j = 0; j < prologue_tiles; ++j) {
-            mbar_arrive_expect_tx(bar(kBarKFull + j), kTileBytes);
-            tma_load_4d(smem_k(j), &tm_k, bar(kBarKFull + j), 0, (kv_tile0 + j) * kBlockN, hi, bk);
-            mbar_arrive_expect_tx(bar(kBarVFull + j), kTileBytes);
-            tma_load_4d(smem_v(j), &tm_v, bar(kBarVFull + j), 0, (kv_tile0 + j) * kBlockN, hi, bk);
+            mbar_arrive_expect_tx(ubar(kBarKFull + j), kTileBytes);
+            tma_load_4d(usmem_k(j), &tm_k, ubar(kBarKFull + j), 0, (kv_tile0 + j) * kBlockN, hi, bk);
+            mbar_arrive_expect_tx(ubar(kBarVFull + j), kTileBytes);
+            tma_load_4d(usmem_v(j), &tm_v, ubar(kBarVFull + j), 0, (kv_tile0 + j) * kBlockN, hi, bk);
         }
         LG_TRACE(13);
     }
+    __syncwarp();
     if (warp == kSoftmaxWarps + 2) {
         tmem_alloc<kTmemCols>(smem + kSmemTmemSlot);
         tmem_relinquish();
@@ -236,63 +245,75 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
 
     if (warp >= kSoftmaxWarps) {
         setmaxnreg_dec<kRegsOther>();
-        if (warp == kSoftmaxWarps && lane == 0) {
+        const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
+        if (warp == kSoftmaxWarps) {
             // ===================================================================== TMA producer
             for (int j = prologue_tiles; j < num_kv_tiles; ++j) {
                 const int s = j % kStages;
                 const uint32_t par = ((j / kStages) - 1) & 1;
-                mbar_wait_backoff(bar(kBarKEmpty + s), par, LG_ATTN_SPIN_NS);
-                mbar_arrive_expect_tx(bar(kBarKFull + s), kTileBytes);
-                tma_load_4d(smem_k(s), &tm_k, bar(kBarKFull + s), 0, (kv_tile0 + j) * kBlockN, hi, bk);
-                mbar_wait_backoff(bar(kBarVEmpty + s), par, LG_ATTN_SPIN_NS);
-                mbar_arrive_expect_tx(bar(kBarVFull + s), kTileBytes);
-                tma_load_4d(smem_v(s), &tm_v, bar(kBarVFull + s), 0, (kv_tile0 + j) * kBlockN, hi, bk);
+                mbar_wait_backoff(ubar(kBarKEmpty + s), par, LG_ATTN_SPIN_NS);
+                if (elect_one()) {
+                    mbar_arrive_expect_tx(ubar(kBarKFull + s), kTileBytes);
+                    tma_load_4d(usmem_k(s), &tm_k, ubar(kBarKFull + s), 0, (kv_tile0 + j) * kBlockN, hi, bk);
+                }
+                __syncwarp();
+                mbar_wait_backoff(ubar(kBarVEmpty + s), par, LG_ATTN_SPIN_NS);
+                if (elect_one()) {
+                    mbar_arrive_expect_tx(ubar(kBarVFull + s), kTileBytes);
+                    tma_load_4d(usmem_v(s), &tm_v, ubar(kBarVFull + s), 0, (kv_tile0 + j) * kBlockN, hi, bk);
+                }
+                __syncwarp();
             }
-        } else if (warp == kSoftmaxWarps + 1 && lane == 0) {
+        } else if (warp == kSoftmaxWarps + 1) {
             // ===================================================================== MMA issuer
             constexpr uint32_t idesc_qk = make_idesc_f16_f32acc(kBlockM, kBlockN, false);
             constexpr uint32_t idesc_pv = make_idesc_f16_f32acc(kBlockM, kHeadDim, true);
-            const uint32_t t_s = tmem_base + kColS;
-            const uint32_t t_o = tmem_base + kColO;
-            const uint32_t t_p = tmem_base + kColP;
-            const uint64_t desc_q = make_smem_desc_sw128(smem + kSmemQ, 16, 1024);
+            const uint32_t t_s = tmem_u + kColS;
+            const uint32_t t_o = tmem_u + kColO;
+            const uint32_t t_p = tmem_u + kColP;
+            const uint64_t desc_q = make_smem_desc_sw128(smem_u + kSmemQ, 16, 1024);
 
             auto issue_qk = [&](int j) {
                 const int s = j % kStages;
-                mbar_wait_backoff(bar(kBarKFull + s), (j / kStages) & 1, LG_ATTN_SPIN_NS);
+                mbar_wait(ubar(kBarKFull + s), (j / kStages) & 1);
                 tc_fence_after();
-                const uint64_t desc_k = make_smem_desc_sw128(smem_k(s), 16, 1024);
+                if (elect_one()) {
+                    const uint64_t desc_k = make_smem_desc_sw128(usmem_k(s), 16, 1024);
 #pragma unroll
-                for (int kk = 0; kk < kHeadDim / 16; ++kk) {
-                    // K-major: advancing 16 halves along K = +32 B inside the 128-B swizzle row
-                    mma_f16_ss(t_s, desc_q + 2u * kk, desc_k + 2u * kk, idesc_qk, kk > 0 ? 1u : 0u);
+                    for (int kk = 0; kk < kHeadDim / 16; ++kk) {
+                        // K-major: advancing 16 halves along K = +32 B inside the 128-B swizzle row
+                        mma_f16_ss(t_s, desc_q + 2u * kk, desc_k + 2u * kk, idesc_qk, kk > 0 ? 1u : 0u);
+                    }
+                    mma_commit(ubar(kBarKEmpty + s));
+                    mma_commit(ubar(kBarSFull));
                 }
-                mma_commit(bar(kBarKEmpty + s));
-                mma_commit(bar(kBarSFull));
+                __syncwarp();
             };
 
-            mbar_wait(bar(kBarQFull), 0);
-            LG_TRACE(2);
+            mbar_wait(ubar(kBarQFull), 0);
+            if (lane == 0) LG_TRACE(2);
             issue_qk(0);
             for (int j = 0; j < num_kv_tiles; ++j) {
                 if (j + 1 < num_kv_tiles) {
-                    mbar_wait_backoff(bar(kBarSEmpty), j & 1, LG_ATTN_SPIN_NS);  // S(j) now lives in softmax registers
+                    mbar_wait(ubar(kBarSEmpty), j & 1);  // S(j) now lives in softmax registers
                     issue_qk(j + 1);
                 }
                 const int s = j % kStages;
-                mbar_wait_backoff(bar(kBarVFull + s), (j / kStages) & 1, LG_ATTN_SPIN_NS);
-                mbar_wait_backoff(bar(kBarPFull), j & 1, LG_ATTN_SPIN_NS);
+                mbar_wait(ubar(kBarVFull + s), (j / kStages) & 1);
+                mbar_wait(ubar(kBarPFull), j & 1);
                 tc_fence_after();
-                const uint64_t desc_v = make_smem_desc_sw128(smem_v(s), kTileBytes, 1024);
+                if (elect_one()) {
+                    const uint64_t desc_v = make_smem_desc_sw128(usmem_v(s), kTileBytes, 1024);
 #pragma unroll
-                for (int kk = 0; kk < kBlockN / 16; ++kk) {
-                    // A = P from TMEM: 16 halves = 8 columns per k-step.
-                    // B = V, MN-major: 16 kv rows = 2048 B per k-step.
-                    mma_f16_ts(t_o, t_p + 8u * kk, desc_v + 128u * kk, idesc_pv,
-                               (j > 0 || kk > 0) ? 1u : 0u);
+                    for (int kk = 0; kk < kBlockN / 16; ++kk) {
+                        // A = P from TMEM: 16 halves = 8 columns per k-step.
+                        // B = V, MN-major: 16 kv rows = 2048 B per k-step.
+                        mma_f16_ts(t_o, t_p + 8u * kk, desc_v + 128u * kk, idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
+                    }
+                    mma_commit(ubar(kBarVEmpty + s));
+                    mma_commit(ubar(kBarPVDone));
                 }
-                mma_commit(bar(kBarVEmpty + s));
-                mma_commit(bar(kBarPVDone));
+                __syncwarp();
             }
         }
         if (num_splits > 1) {  // service warps just take part in the cluster barrier(s)

@@ -154,31 +154,38 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
     W4_TRACE_CTA(0, clock64());
     W4_TRACE_CTA(4, w4_globaltimer());
 
-    if (warp == 4 && lane == 0) {
+    // Service warps run converged and issue through one elected lane (elect.sync): inside a `lane == 0` branch ptxas cannot prove
+    // that the operands of UTMALDG / UTCHMMA / UTCBAR are warp-uniform and wraps every one of them in an R2UR + BRA.U.ANY waterfall
+    // loop (~80 clk each; see attn_sm100_kernel_mq.cuh).  smem_u is the un-pinned (provably uniform) copy of the aligned base.
+    const uint32_t smem_u = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t bars_u = smem_u + kSmemBar;
+    auto ubar = [&](uint32_t i) { return bars_u + 8u * i; };
+    if (warp == 4 && elect_one()) {
         prefetch_tmap(&tm_q);
         prefetch_tmap(&tm_k);
         prefetch_tmap(&tm_v);
-        mbar_init(bar(kBarQFull), 1);
+        mbar_init(ubar(kBarQFull), 1);
         for (int s = 0; s < kStages; ++s) {
-            mbar_init(bar(kBarKFull + s), 1);
-            mbar_init(bar(kBarKEmpty + s), 1);
-            mbar_init(bar(kBarVFull + s), 1);
-            mbar_init(bar(kBarVEmpty + s), 1);
+            mbar_init(ubar(kBarKFull + s), 1);
+            mbar_init(ubar(kBarKEmpty + s), 1);
+            mbar_init(ubar(kBarVFull + s), 1);
+            mbar_init(ubar(kBarVEmpty + s), 1);
         }
-        mbar_init(bar(kBarSFull), 1);
-        mbar_init(bar(kBarSEmpty), 4);  // one arrival per softmax warp
-        mbar_init(bar(kBarPFull), 4);
-        mbar_init(bar(kBarPVDone), 1);
+        mbar_init(ubar(kBarSFull), 1);
+        mbar_init(ubar(kBarSEmpty), 4);  // one arrival per softmax warp
+        mbar_init(ubar(kBarPFull), 4);
+        mbar_init(ubar(kBarPVDone), 1);
         fence_mbar_init();
         // first loads go out before the TMEM allocation / CTA barrier below: the 2.5 k clk until the first S is mostly
         // their latency (CTA-level trace), and only this thread ever arms these barriers
-        mbar_arrive_expect_tx(bar(kBarQFull), kTileBytes);
-        tma_load_4d(smem + kSmemQ, &tm_q, bar(kBarQFull), 0, tile_m * kBlockM, hi, bi);
-        mbar_arrive_expect_tx(bar(kBarKFull), kTileBytes);
-        tma_load_4d(smem + kSmemK, &tm_k, bar(kBarKFull), 0, 0, hi, bk);
-        mbar_arrive_expect_tx(bar(kBarVFull), kTileBytes);
-        tma_load_4d(smem + kSmemV, &tm_v, bar(kBarVFull), 0, 0, hi, bk);
+        mbar_arrive_expect_tx(ubar(kBarQFull), kTileBytes);
+        tma_load_4d(smem_u + kSmemQ, &tm_q, ubar(kBarQFull), 0, tile_m * kBlockM, hi, bi);
+        mbar_arrive_expect_tx(ubar(kBarKFull), kTileBytes);
+        tma_load_4d(smem_u + kSmemK, &tm_k, ubar(kBarKFull), 0, 0, hi, bk);
+        mbar_arrive_expect_tx(ubar(kBarVFull), kTileBytes);
+        tma_load_4d(smem_u + kSmemV, &tm_v, ubar(kBarVFull), 0, 0, hi, bk);
     }
+    __syncwarp();
     if (warp == 6) {
         tmem_alloc<kTmemCols>(smem + kSmemTmemSlot);
         tmem_relinquish();
@@ -191,65 +198,74 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
 
     if (warp >= 4) {
         setmaxnreg_dec<kRegsOther>();
-        if (warp == 4 && lane == 0) {
+        const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
+        if (warp == 4) {
             // ===================================================================== TMA producer
             for (int j = 1; j < num_kv_tiles; ++j) {   // tile 0 (and Q) were issued in the prologue
                 const int s = j % kStages;
                 const uint32_t par = ((j / kStages) - 1) & 1;
-                if (j >= kStages) mbar_wait_backoff(bar(kBarKEmpty + s), par, LG_ATTN_SPIN_NS);
-                mbar_arrive_expect_tx(bar(kBarKFull + s), kTileBytes);
-                tma_load_4d(smem + kSmemK + s * kTileBytes, &tm_k, bar(kBarKFull + s), 0,
-                            j * kBlockN, hi, bk);
-                if (j >= kStages) mbar_wait_backoff(bar(kBarVEmpty + s), par, LG_ATTN_SPIN_NS);
-                mbar_arrive_expect_tx(bar(kBarVFull + s), kTileBytes);
-                tma_load_4d(smem + kSmemV + s * kTileBytes, &tm_v, bar(kBarVFull + s), 0,
-                            j * kBlockN, hi, bk);
+                if (j >= kStages) mbar_wait_backoff(ubar(kBarKEmpty + s), par, LG_ATTN_SPIN_NS);
+                if (elect_one()) {
+                    mbar_arrive_expect_tx(ubar(kBarKFull + s), kTileBytes);
+                    tma_load_4d(smem_u + kSmemK + s * kTileBytes, &tm_k, ubar(kBarKFull + s), 0, j * kBlockN, hi, bk);
+                }
+                __syncwarp();
+                if (j >= kStages) mbar_wait_backoff(ubar(kBarVEmpty + s), par, LG_ATTN_SPIN_NS);
+                if (elect_one()) {
+                    mbar_arrive_expect_tx(ubar(kBarVFull + s), kTileBytes);
+                    tma_load_4d(smem_u + kSmemV + s * kTileBytes, &tm_v, ubar(kBarVFull + s), 0, j * kBlockN, hi, bk);
+                }
+                __syncwarp();
             }
-        } else if (warp == 5 && lane == 0) {
+        } else if (warp == 5) {
             // ===================================================================== MMA issuer
             constexpr uint32_t idesc_qk = make_idesc_f16_f32acc(kBlockM, kBlockN, false);
             constexpr uint32_t idesc_pv = make_idesc_f16_f32acc(kBlockM, kHeadDim, true);
-            const uint32_t t_s = tmem_base + kColS;
-            const uint32_t t_o = tmem_base + kColO;
-            const uint32_t t_p = tmem_base + kColP;
-            const uint64_t desc_q = make_smem_desc_sw128(smem + kSmemQ, 16, 1024);
+            const uint32_t t_s = tmem_u + kColS;
+            const uint32_t t_o = tmem_u + kColO;
+            const uint32_t t_p = tmem_u + kColP;
+            const uint64_t desc_q = make_smem_desc_sw128(smem_u + kSmemQ, 16, 1024);
 
             auto issue_qk = [&](int j) {
                 const int s = j % kStages;
-                mbar_wait_backoff(bar(kBarKFull + s), (j / kStages) & 1, LG_ATTN_SPIN_NS);
+                mbar_wait_backoff(ubar(kBarKFull + s), (j / kStages) & 1, LG_ATTN_SPIN_NS);
                 tc_fence_after();
-                const uint64_t desc_k = make_smem_desc_sw128(smem + kSmemK + s * kTileBytes, 16, 1024);
+                if (elect_one()) {
+                    const uint64_t desc_k = make_smem_desc_sw128(smem_u + kSmemK + s * kTileBytes, 16, 1024);
 #pragma unroll
-                for (int kk = 0; kk < kHeadDim / 16; ++kk) {
-                    // K-major: advancing 16 halves along K = +32 B inside the 128-B swizzle row
-                    mma_f16_ss(t_s, desc_q + 2u * kk, desc_k + 2u * kk, idesc_qk, kk > 0 ? 1u : 0u);
+                    for (int kk = 0; kk < kHeadDim / 16; ++kk) {
+                        // K-major: advancing 16 halves along K = +32 B inside the 128-B swizzle row
+                        mma_f16_ss(t_s, desc_q + 2u * kk, desc_k + 2u * kk, idesc_qk, kk > 0 ? 1u : 0u);
+                    }
+                    mma_commit(ubar(kBarKEmpty + s));
+                    mma_commit(ubar(kBarSFull));
                 }
-                mma_commit(bar(kBarKEmpty + s));
-                mma_commit(bar(kBarSFull));
+                __syncwarp();
             };
 
-            mbar_wait(bar(kBarQFull), 0);
+            mbar_wait(ubar(kBarQFull), 0);
             issue_qk(0);
             for (int j = 0; j < num_kv_tiles; ++j) {
                 if (j + 1 < num_kv_tiles) {
-                    mbar_wait_backoff(bar(kBarSEmpty), j & 1, LG_ATTN_SPIN_NS);  // S(j) now lives in softmax registers
+                    mbar_wait_backoff(ubar(kBarSEmpty), j & 1, LG_ATTN_SPIN_NS);  // S(j) now lives in softmax registers
                     issue_qk(j + 1);
                 }
                 const int s = j % kStages;
-                mbar_wait_backoff(bar(kBarVFull + s), (j / kStages) & 1, LG_ATTN_SPIN_NS);
-                mbar_wait_backoff(bar(kBarPFull), j & 1, LG_ATTN_SPIN_NS);
+                mbar_wait_backoff(ubar(kBarVFull + s), (j / kStages) & 1, LG_ATTN_SPIN_NS);
+                mbar_wait_backoff(ubar(kBarPFull), j & 1, LG_ATTN_SPIN_NS);
                 tc_fence_after();
-                const uint64_t desc_v =
-                    make_smem_desc_sw128(smem + kSmemV + s * kTileBytes, kTileBytes, 1024);
+                if (elect_one()) {
+                    const uint64_t desc_v = make_smem_desc_sw128(smem_u + kSmemV + s * kTileBytes, kTileBytes, 1024);
 #pragma unroll
-                for (int kk = 0; kk < kBlockN / 16; ++kk) {
-                    // A = P from TMEM: 16 halves = 8 columns per k-step.
-                    // B = V, MN-major: 16 kv rows = 2048 B per k-step.
-                    mma_f16_ts(t_o, t_p + 8u * kk, desc_v + 128u * kk, idesc_pv,
-                               (j > 0 || kk > 0) ? 1u : 0u);
+                    for (int kk = 0; kk < kBlockN / 16; ++kk) {
+                        // A = P from TMEM: 16 halves = 8 columns per k-step.
+                        // B = V, MN-major: 16 kv rows = 2048 B per k-step.
+                        mma_f16_ts(t_o, t_p + 8u * kk, desc_v + 128u * kk, idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
+                    }
+                    mma_commit(ubar(kBarVEmpty + s));
+                    mma_commit(ubar(kBarPVDone));
                 }
-                mma_commit(bar(kBarVEmpty + s));
-                mma_commit(bar(kBarPVDone));
+                __syncwarp();
             }
         }
     } else {

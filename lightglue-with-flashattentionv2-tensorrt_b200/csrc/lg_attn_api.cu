@@ -9,9 +9,8 @@
 
 #include "attn_sm100.h"
 #include "attn_sm100_kernel.cuh"     // lgattn::w8 — latency shapes, split-KV clusters, PDL
-#include "attn_sm100_kernel_w4.cuh"  // lgattn::w4 — full grids, one Q tile per CTA (kept for A/B: LG_ATTN_PERSIST=0)
-#include "attn_sm100_kernel_w4p.cuh" // lgattn::w4p — full grids, persistent CTAs (throughput)
-#include "attn_sm100_kernel_mq.cuh"  // lgattn::mq — full grids, one persistent CTA per SM owning several Q tiles (throughput)
+#include "attn_sm100_kernel_w4.cuh"  // lgattn::w4 — full grids whose Q-tile count packs badly into 2- / 4-tile work items
+#include "attn_sm100_kernel_mq.cuh"  // lgattn::mq — full grids: one persistent CTA per SM owning several Q tiles (throughput)
 #include "cvt_f32_f16.cuh"
 
 #include <cuda.h>
@@ -43,9 +42,8 @@ int g_sm_count[kMaxDevices];              // written once per device under g_ini
 int g_max_clusters[kMaxDevices][4];       // co-resident clusters of 1 << i CTAs (same publication rule)
 std::atomic<int> g_forced_splits{0};      // tuning override (LG_ATTN_SPLITS), 0 = automatic
 std::atomic<int> g_use_pdl{1};            // LG_ATTN_PDL=0 disables programmatic dependent launch
-std::atomic<int> g_use_persist{-1};       // full grids: -1 = automatic (persistent CTAs when a Q tile has few KV tiles),
-                                          // 0 / 1 = force the one-tile-per-CTA / persistent kernel (LG_ATTN_PERSIST, tests)
-constexpr int kPersistMaxKvTiles = 8;     // measured crossover (B200): +4 % at 8 KV tiles, -1 % at 16 and 32
+std::atomic<int> g_full_grid_kernel{-1};  // full grids: -1 = automatic, 0 = w4, 1 = mq (4 Q tiles), 2 = mq (2 Q tiles)
+                                          // (LG_ATTN_FULL_GRID_KERNEL, lg_attn_debug_set_throughput_kernel: tests, A/B runs)
 
 // The multi-Q-tile kernel variants compiled into the library (lg_attn_debug_set_throughput_kernel modes 2, 3, ...).
 template <int T, int BN, bool A, bool L>
@@ -54,16 +52,39 @@ struct MqVariant {
     static constexpr bool kAlias = A, kLazy = L;
     using C = mq::Cfg<T, BN, A>;
 };
-constexpr int kMqModeBase = 2;
+constexpr int kMqModeBase = 1;
 template <typename F>
 void mq_for_each_variant(F&& f) {
-    f(MqVariant<2, 128, false, false>{});   // mode 2
-    f(MqVariant<4, 64, true, true>{});      // mode 3
-    f(MqVariant<4, 64, true, false>{});     // mode 4
-    f(MqVariant<3, 64, false, false>{});    // mode 5
-    f(MqVariant<3, 64, true, true>{});      // mode 6
+    f(MqVariant<4, 64, true, true>{});      // mode 1: 4 Q tiles, 64-row KV steps, P aliased onto S, lazy row max
+    f(MqVariant<2, 128, false, false>{});   // mode 2: 2 Q tiles, 128-row KV steps, S / P / O separate
+#ifdef LG_ATTN_MQ_EXTRA_VARIANTS            // tuning builds: more layouts to A/B
+    f(MqVariant<4, 64, true, false>{});     // mode 3
+    f(MqVariant<3, 64, false, false>{});    // mode 4
+    f(MqVariant<3, 64, true, true>{});      // mode 5
+#endif
 }
+#ifdef LG_ATTN_MQ_EXTRA_VARIANTS
 constexpr int kMqVariants = 5;
+#else
+constexpr int kMqVariants = 2;
+#endif
+
+// Which full-grid kernel is expected to finish first.  Relative speeds are same-box medians on square shapes (B200, round 2:
+// mq4 1.00, mq2 0.93, w4 0.85); each is discounted by how well the launch packs: Q tiles wasted inside partly filled work
+// items, and the last wave of the (persistent or not) grid.
+int choose_full_grid_kernel(long long bh, long long tiles_m, int sms) {
+    auto wave_eff = [&](long long units, long long slots) {
+        const long long waves = (units + slots - 1) / slots;
+        return static_cast<double>(units) / static_cast<double>(waves * slots);
+    };
+    auto mq_eff = [&](int t) {
+        const long long groups = (tiles_m + t - 1) / t;
+        return static_cast<double>(tiles_m) / static_cast<double>(groups * t) * wave_eff(bh * groups, sms);
+    };
+    const double s_w4 = 0.85 * wave_eff(bh * tiles_m, 2LL * sms), s_mq4 = 1.00 * mq_eff(4), s_mq2 = 0.93 * mq_eff(2);
+    if (s_mq4 >= s_mq2 && s_mq4 >= s_w4) return 1;
+    return s_mq2 >= s_w4 ? 2 : 0;
+}
 
 int resolve_encode() {
     if (g_encode.load(std::memory_order_acquire) != nullptr) return 0;
@@ -126,9 +147,9 @@ int init_device_locked(int device) {
         if (v == 1 || v == 2 || v == 4 || v == 8) g_forced_splits.store(v, std::memory_order_relaxed);
     }
     if (const char* env = getenv("LG_ATTN_PDL")) g_use_pdl.store(atoi(env) != 0 ? 1 : 0, std::memory_order_relaxed);
-    if (const char* env = getenv("LG_ATTN_PERSIST")) {
+    if (const char* env = getenv("LG_ATTN_FULL_GRID_KERNEL")) {
         const int v = atoi(env);
-        g_use_persist.store(v < 0 ? -1 : (v < kMqModeBase + kMqVariants ? v : 1), std::memory_order_relaxed);
+        g_full_grid_kernel.store(v < 0 || v >= kMqModeBase + kMqVariants ? -1 : v, std::memory_order_relaxed);
     }
     int rc = resolve_encode();
     if (rc != 0) return rc;
@@ -146,8 +167,6 @@ int init_device_locked(int device) {
     e = cudaSuccess;
     opt_in(reinterpret_cast<const void*>(w4::lg_attn_hd64_fwd<false>), w4::kSmemBytes);
     opt_in(reinterpret_cast<const void*>(w4::lg_attn_hd64_fwd<true>), w4::kSmemBytes);
-    opt_in(reinterpret_cast<const void*>(w4p::lg_attn_hd64_fwd<false>), w4p::kSmemBytes);
-    opt_in(reinterpret_cast<const void*>(w4p::lg_attn_hd64_fwd<true>), w4p::kSmemBytes);
     mq_for_each_variant([&](auto v) {
         using V = decltype(v);
         opt_in(reinterpret_cast<const void*>(mq::lg_attn_hd64_fwd<V::kT, V::kBN, V::kAlias, V::kLazy, false>), V::C::kSmemBytes);
@@ -189,14 +208,8 @@ bool valid_dtype(int d) { return d == LG_ATTN_F16_F16 || d == LG_ATTN_F32_F32 ||
 
 #ifdef LG_ATTN_W4_TRACE
 extern "C" int lg_attn_debug_read_w4_trace(long long* dst, unsigned* smid) {
-    cudaError_t e;
-    if (g_use_persist.load() != 0) {
-        e = cudaMemcpyFromSymbol(dst, lgattn::w4p::g_w4p_trace, sizeof(lgattn::w4p::g_w4p_trace));
-        if (e == cudaSuccess) e = cudaMemcpyFromSymbol(smid, lgattn::w4p::g_w4p_smid, sizeof(lgattn::w4p::g_w4p_smid));
-    } else {
-        e = cudaMemcpyFromSymbol(dst, lgattn::w4::g_w4_trace, sizeof(lgattn::w4::g_w4_trace));
-        if (e == cudaSuccess) e = cudaMemcpyFromSymbol(smid, lgattn::w4::g_w4_smid, sizeof(lgattn::w4::g_w4_smid));
-    }
+    cudaError_t e = cudaMemcpyFromSymbol(dst, lgattn::w4::g_w4_trace, sizeof(lgattn::w4::g_w4_trace));
+    if (e == cudaSuccess) e = cudaMemcpyFromSymbol(smid, lgattn::w4::g_w4_smid, sizeof(lgattn::w4::g_w4_smid));
     return static_cast<int>(e);
 }
 #endif
@@ -234,8 +247,9 @@ static int launch_core(const void* qh, const void* kh, const void* vh, void* o, 
     const int tiles_m = static_cast<int>(tiles_m_ll);
     cudaError_t e = cudaSuccess;
 
-    // Two kernels (see their headers): full grids take the 4-softmax-warp kernel (best sustained
-    // throughput); grids that cannot fill the GPU take the 8-softmax-warp kernel, which splits each
+    // Full grids (>= 2 Q tiles per SM) take a throughput kernel — the multi-Q-tile persistent kernel (mq) in its 4- or 2-tile
+    // layout, or the one-tile-per-CTA kernel (w4) when the Q-tile count packs badly into work items (choose_full_grid_kernel);
+    // grids that cannot fill the GPU take the 8-softmax-warp kernel (w8), which splits each
     // Q tile's KV range over a cluster of `splits` CTAs (DSMEM combine) and uses programmatic
     // dependent launch so its prologue overlaps the previous kernel's tail.  splits = the largest
     // power of two <= min(8, KV tiles) whose clusters are all co-resident (one wave), from
@@ -249,14 +263,14 @@ static int launch_core(const void* qh, const void* kh, const void* vh, void* o, 
     cfg.stream = stream;
     cudaLaunchAttribute attrs[2];
     unsigned n_attrs = 0;
-    const int persist_mode = g_use_persist.load(std::memory_order_relaxed);
-    const bool persist = persist_mode < 0 ? kv_tiles <= kPersistMaxKvTiles : persist_mode != 0;
-    if (full_grid && persist_mode >= kMqModeBase) {
+    int fg_kernel = g_full_grid_kernel.load(std::memory_order_relaxed);
+    if (full_grid && fg_kernel < 0) fg_kernel = choose_full_grid_kernel(bh_ll, tiles_m_ll, g_sm_count[device]);
+    if (full_grid && fg_kernel >= kMqModeBase) {
         // one persistent CTA per SM, kT Q tiles per work item, K/V tiles of kBN rows shared by the kT tiles
         int idx = kMqModeBase;
         mq_for_each_variant([&](auto v) {
             using V = decltype(v);
-            if (idx++ != persist_mode || e != cudaSuccess || rc != 0) return;
+            if (idx++ != fg_kernel || e != cudaSuccess || rc != 0) return;
             if (V::kBN != kBlockN) {
                 if ((rc = encode_rows_map(&tm_k, kh, n_kv, heads, batch, sk, V::kBN)) != 0) return;
                 if ((rc = encode_rows_map(&tm_v, vh, n_kv, heads, batch, sv, V::kBN)) != 0) return;
@@ -274,15 +288,6 @@ static int launch_core(const void* qh, const void* kh, const void* vh, void* o, 
                                    tm_q, tm_k, tm_v, o, n_q, n_kv, static_cast<int>(groups), static_cast<int>(items), ol);
         });
         if (rc != 0) return rc;
-    } else if (full_grid && persist) {
-        // persistent: 2 resident CTAs per SM walk the Q tiles blockIdx.x + i * gridDim.x
-        cfg.gridDim = dim3(static_cast<unsigned>(2 * g_sm_count[device]));
-        cfg.blockDim = dim3(w4p::kThreads);
-        cfg.dynamicSmemBytes = w4p::kSmemBytes;
-        cfg.attrs = attrs;
-        cfg.numAttrs = 0;
-        e = cudaLaunchKernelEx(&cfg, !out_f32 ? w4p::lg_attn_hd64_fwd<false> : w4p::lg_attn_hd64_fwd<true>, tm_q,
-                               tm_k, tm_v, o, n_q, n_kv, tiles_m, static_cast<int>(base), ol);
     } else if (full_grid) {
         cfg.gridDim = dim3(static_cast<unsigned>(base));
         cfg.blockDim = dim3(w4::kThreads);
@@ -341,7 +346,7 @@ int lg_attn_version(void) { return kAbiVersion; }
 
 int lg_attn_debug_set_throughput_kernel(int mode) {
     if (mode < -1 || mode >= kMqModeBase + kMqVariants) return LG_ATTN_EINVAL;
-    g_use_persist.store(mode, std::memory_order_relaxed);
+    g_full_grid_kernel.store(mode, std::memory_order_relaxed);
     return 0;
 }
 

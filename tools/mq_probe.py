@@ -1,5 +1,5 @@
 """GPU box: correctness + burst TFLOP/s of every full-grid kernel the library carries, selected through
-lg_attn_debug_set_throughput_kernel (0 = w4, 1 = w4p, >= 2 = multi-Q-tile variants, see lg_attn_api.cu).
+lg_attn_debug_set_throughput_kernel (0 = w4, 1 = mq 4 Q tiles, 2 = mq 2 Q tiles; -2 = torch SDPA for reference).
 Each mode runs in its own subprocess under a timeout so that a hung variant cannot take the call down.
 
     python tools/mq_probe.py [--modes 0,2,3] [--out gpurun_out/mq_probe.json] [--lib path/to/variant.so]
@@ -74,7 +74,7 @@ print("RESULT " + json.dumps(res))
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--modes", default="-2,0,1,2,3,4,5,6")
+    ap.add_argument("--modes", default="-2,0,1,2")
     ap.add_argument("--out", default="gpurun_out/mq_probe.json")
     ap.add_argument("--lib", default=None)
     ap.add_argument("--tag", default="")
