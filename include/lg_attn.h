@@ -45,11 +45,22 @@ enum lg_attn_io_dtype {
 /* ABI version of this header (bumped on any signature change). */
 int lg_attn_version(void);
 
+/* Bit mask of the tuning switches this library was compiled with; 0 for a product build.  bit 0 LG_ATTN_TUNING_BUILD,
+ * bit 1 LG_ATTN_WHATIF (wrong results by design), bit 2 LG_ATTN_EXPERIMENT_NOSUM (wrong results), bit 3 a phase-trace build
+ * (LG_ATTN_TRACE / LG_ATTN_W4_TRACE / LG_ATTN_MQ_TRACE).  tests/test_boundary_cpu.py requires 0 of the shipped .so. */
+int lg_attn_build_flags(void);
+
 /* Test / tuning hook (no reference counterpart): which full-grid (throughput) kernel lg_attn_hd64_launch* uses.
  * -1 automatic (default: whichever packs the launch best, see choose_full_grid_kernel in lg_attn_api.cu),
  * 0 one 128-row Q tile per CTA, 1 persistent CTAs owning four Q tiles (64-row KV steps), 2 persistent CTAs owning two Q
  * tiles (128-row KV steps).  All meet the same tolerances; also settable as LG_ATTN_FULL_GRID_KERNEL. */
 int lg_attn_debug_set_throughput_kernel(int mode);
+
+/* Measurement hooks (no reference counterpart).  set_pdl: programmatic dependent launch of the latency kernel on / off (also
+ * LG_ATTN_PDL) so that a bench can report a serialised single-call latency both ways.  describe_launch: writes which kernel,
+ * grid and split count lg_attn_hd64_launch would use for this shape on the current device into buf (NUL-terminated). */
+int lg_attn_debug_set_pdl(int enabled);
+int lg_attn_debug_describe_launch(int batch, int heads, int n_q, int n_kv, char* buf, size_t buf_bytes);
 
 /* Per-device one-time setup (shared-memory opt-in, driver entry point lookup). Idempotent and
  * thread-safe; lg_attn_hd64_launch() calls it lazily, but call it before stream capture.

@@ -64,6 +64,10 @@ int lg_matcher_sync(lg_matcher* m);
 /* Kernel launches inside one captured forward of the current plan (0 before planning). */
 int lg_matcher_launches(const lg_matcher* m);
 
+/* How many shape plans (device buffers + captured graph) the engine currently holds: the active one plus the parked ones
+ * (at most 4; the least recently used is evicted).  Shapes that alternate are swapped in without re-planning. */
+int lg_matcher_plans_resident(const lg_matcher* m);
+
 void lg_matcher_destroy(lg_matcher* m);
 
 #ifdef __cplusplus

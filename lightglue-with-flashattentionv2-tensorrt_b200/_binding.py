@@ -30,7 +30,10 @@ EARCH = 100004
 # every symbol include/lg_attn.h declares (tests check the .so exports exactly these)
 C_ABI_SYMBOLS = (
     "lg_attn_version",
+    "lg_attn_build_flags",
     "lg_attn_debug_set_throughput_kernel",
+    "lg_attn_debug_set_pdl",
+    "lg_attn_debug_describe_launch",
     "lg_attn_hd64_init_device",
     "lg_attn_hd64_workspace_bytes",
     "lg_attn_hd64_launch",
@@ -63,6 +66,7 @@ MATCHER_ABI_SYMBOLS = (
     "lg_matcher_submit_host",
     "lg_matcher_sync",
     "lg_matcher_launches",
+    "lg_matcher_plans_resident",
     "lg_matcher_destroy",
 )
 ECUBLAS = 100010
@@ -80,6 +84,13 @@ class LgAttnError(RuntimeError):
     def __init__(self, code: int, what: str):
         super().__init__(f"{what} failed: code {code} ({error_string(code)})")
         self.code = code
+
+
+def describe_launch(batch: int, heads: int, n_q: int, n_kv: int) -> str:
+    """Which kernel / grid ``lg_attn_hd64_launch`` uses for this shape on the current device."""
+    buf = ctypes.create_string_buffer(256)
+    check(load().lg_attn_debug_describe_launch(batch, heads, n_q, n_kv, buf, 256), "lg_attn_debug_describe_launch")
+    return buf.value.decode()
 
 
 def lib_path() -> Path:
@@ -101,8 +112,14 @@ def load() -> ctypes.CDLL:
     lib = ctypes.CDLL(str(path), mode=ctypes.RTLD_GLOBAL)
     lib.lg_attn_version.restype = ctypes.c_int
     lib.lg_attn_version.argtypes = []
+    lib.lg_attn_build_flags.restype = ctypes.c_int
+    lib.lg_attn_build_flags.argtypes = []
     lib.lg_attn_debug_set_throughput_kernel.restype = ctypes.c_int
     lib.lg_attn_debug_set_throughput_kernel.argtypes = [ctypes.c_int]
+    lib.lg_attn_debug_set_pdl.restype = ctypes.c_int
+    lib.lg_attn_debug_set_pdl.argtypes = [ctypes.c_int]
+    lib.lg_attn_debug_describe_launch.restype = ctypes.c_int
+    lib.lg_attn_debug_describe_launch.argtypes = [ctypes.c_int] * 4 + [ctypes.c_char_p, ctypes.c_size_t]
     lib.lg_attn_hd64_init_device.restype = ctypes.c_int
     lib.lg_attn_hd64_init_device.argtypes = [ctypes.c_int]
     lib.lg_attn_hd64_workspace_bytes.restype = ctypes.c_size_t
@@ -166,6 +183,8 @@ def load() -> ctypes.CDLL:
     lib.lg_matcher_sync.argtypes = [P]
     lib.lg_matcher_launches.restype = I
     lib.lg_matcher_launches.argtypes = [P]
+    lib.lg_matcher_plans_resident.restype = I
+    lib.lg_matcher_plans_resident.argtypes = [P]
     lib.lg_matcher_destroy.restype = None
     lib.lg_matcher_destroy.argtypes = [P]
     _lib = lib

@@ -54,6 +54,8 @@ def up_to_date() -> bool:
 
 def build(force: bool = False, verbose: bool = False, defs: list[str] | None = None, out: Path | None = None) -> Path:
     """Default: the product library.  `defs` / `out` build a tuning variant (extra -D flags) elsewhere."""
+    if out is None and defs:
+        raise ValueError("the product library is built without extra -D flags; pass out=... for a tuning variant")
     if out is None and not force and up_to_date():
         return LIB
     BUILD.mkdir(exist_ok=True)

@@ -344,9 +344,68 @@ extern "C" {
 
 int lg_attn_version(void) { return kAbiVersion; }
 
+int lg_attn_build_flags(void) {
+    int f = 0;
+#ifdef LG_ATTN_TUNING_BUILD
+    f |= 1;
+#endif
+#ifdef LG_ATTN_WHATIF
+    f |= 2;
+#endif
+#ifdef LG_ATTN_EXPERIMENT_NOSUM
+    f |= 4;
+#endif
+#if defined(LG_ATTN_TRACE) || defined(LG_ATTN_W4_TRACE) || defined(LG_ATTN_MQ_TRACE)
+    f |= 8;
+#endif
+    return f;
+}
+
 int lg_attn_debug_set_throughput_kernel(int mode) {
     if (mode < -1 || mode >= kMqModeBase + kMqVariants) return LG_ATTN_EINVAL;
     g_full_grid_kernel.store(mode, std::memory_order_relaxed);
+    return 0;
+}
+
+int lg_attn_debug_set_pdl(int enabled) {
+    g_use_pdl.store(enabled != 0 ? 1 : 0, std::memory_order_relaxed);
+    return 0;
+}
+
+int lg_attn_debug_describe_launch(int batch, int heads, int n_q, int n_kv, char* buf, size_t buf_bytes) {
+    if (buf == nullptr || buf_bytes == 0 || batch <= 0 || heads <= 0 || n_q <= 0 || n_kv <= 0) return LG_ATTN_EINVAL;
+    int device = 0;
+    cudaError_t e = cudaGetDevice(&device);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    int rc = lg_attn_hd64_init_device(device);
+    if (rc != 0) return rc;
+    const long long bh = static_cast<long long>(batch) * heads, tiles_m = (static_cast<long long>(n_q) + kBlockM - 1) / kBlockM;
+    const long long base = bh * tiles_m;
+    const int kv_tiles = (n_kv + kBlockN - 1) / kBlockN, sms = g_sm_count[device];
+    const int forced = g_forced_splits.load(std::memory_order_relaxed);
+    if (base >= 2LL * sms && forced == 0) {
+        int k = g_full_grid_kernel.load(std::memory_order_relaxed);
+        if (k < 0) k = choose_full_grid_kernel(bh, tiles_m, sms);
+        if (k == 0) {
+            snprintf(buf, buf_bytes, "lgattn::w4 (one 128-row Q tile per CTA, 2 CTAs/SM), grid %lld", base);
+        } else {
+            const int t = k == 1 ? 4 : 2;
+            const long long items = bh * ((tiles_m + t - 1) / t);
+            snprintf(buf, buf_bytes, "lgattn::mq<%d Q tiles, %d-row KV steps> (persistent, 1 CTA/SM), grid %lld over %lld work items",
+                     t, k == 1 ? 64 : 128, items < sms ? items : static_cast<long long>(sms), items);
+        }
+    } else {
+        int splits = 1;
+        if (forced > 0) {
+            splits = forced;
+        } else if (base < sms) {
+            for (int lg = 1; lg <= 3; ++lg)
+                if ((1 << lg) <= kv_tiles && base <= g_max_clusters[device][lg]) splits = 1 << lg;
+        }
+        while (splits > 1 && splits > kv_tiles) splits /= 2;
+        snprintf(buf, buf_bytes, "lgattn::w8 (latency kernel, %d-CTA split-KV cluster%s, PDL %s), grid %lld", splits, splits > 1 ? "s" : "",
+                 g_use_pdl.load(std::memory_order_relaxed) ? "on" : "off", base * splits);
+    }
     return 0;
 }
 
@@ -406,7 +465,8 @@ int lg_attn_hd64_launch(const void* q, const void* k, const void* v, void* o, in
         const size_t nkv8 = static_cast<size_t>(bh) * n_kv * (kHeadDim / 8);
         const size_t total = nq8 + 2 * nkv8;
         size_t blocks = (total + 255) / 256;
-        if (blocks > 148 * 16) blocks = 148 * 16;  // grid-stride; 16 resident-CTA waves over 148 SMs
+        const size_t cap = static_cast<size_t>(g_sm_count[device]) * 16;   // grid-stride beyond 16 CTAs per SM
+        if (blocks > cap) blocks = cap;
         cudaLaunchConfig_t ccfg = {};
         ccfg.gridDim = dim3(static_cast<unsigned>(blocks));
         ccfg.blockDim = dim3(256);

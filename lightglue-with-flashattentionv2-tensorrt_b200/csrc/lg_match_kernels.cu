@@ -19,7 +19,18 @@
 
 namespace lgmatch {
 
-constexpr int kSMs = 148;
+// SM count of the current device (queried once per device; the glue kernels size their grid-stride grids from it)
+static int sm_count() {
+    static int cached[64] = {0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    if (cached[dev] == 0) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        cached[dev] = n;
+    }
+    return cached[dev];
+}
 constexpr int kFfnCols = 512;   // 2 * embed_dim (lightglue.py:131)
 constexpr int kAngles = 32;     // head_dim / 2
 
@@ -151,7 +162,7 @@ __global__ void __launch_bounds__(256) layernorm_gelu_kernel(__half* __restrict_
 // Four streaming passes over sim [B, n0, n1] FP32 (row lse, column lse, row best, column best), each a
 // pure read at L2 / HBM speed: 128-bit loads when n1 % 4 == 0 (VEC = 4), rows unrolled for memory-level
 // parallelism, column passes split over row blocks (partials combined by a tiny second kernel) so the
-// grid fills 148 SMs at any batch size.
+// grid fills every SM at any batch size.
 __device__ __forceinline__ float log_sigmoid(float z) { return fminf(z, 0.f) - log1pf(expf(-fabsf(z))); }
 
 // (max, sum exp(x - max)) online merge
@@ -334,8 +345,11 @@ __global__ void __launch_bounds__(256) mutual_kernel(const int* __restrict__ m0,
     for (long long r = blockIdx.x * 256LL + threadIdx.x; r < rows; r += gridDim.x * 256LL) {
         const long long b = r / n0;
         const int i = static_cast<int>(r - b * n0);
+        // a row of NaN / -inf similarities (FP16 overflow upstream) has no argmax: its index stays at the INT_MAX sentinel,
+        // which must neither be dereferenced nor reported as a match
         const int j = m0[r];
-        const bool mutual = m1[b * n1 + j] == i;
+        const bool valid = static_cast<unsigned>(j) < static_cast<unsigned>(n1);
+        const bool mutual = valid && m1[b * n1 + j] == i;
         const float ms = mutual ? expf(score0[r]) : 0.f;
         mscores0[r] = ms;
         matches0[r] = ms > threshold ? j : -1;
@@ -373,7 +387,7 @@ __global__ void __launch_bounds__(256) scores_kernel_scalar(const float* __restr
 
 unsigned grid_for(long long work_items, int per_block, int waves = 8) {
     long long blocks = (work_items + per_block - 1) / per_block;
-    const long long cap = static_cast<long long>(kSMs) * waves;  // grid-stride beyond `waves` CTAs per SM
+    const long long cap = static_cast<long long>(sm_count()) * waves;  // grid-stride beyond `waves` CTAs per SM
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
     return static_cast<unsigned>(blocks);

@@ -19,6 +19,7 @@
 #include <cstdio>
 #include <cstring>
 #include <new>
+#include <utility>
 #include <vector>
 
 #include "../../include/lg_attn.h"
@@ -131,15 +132,8 @@ int run_gemm(cublasLtHandle_t lt, const Gemm& g, const void* act, const void* wt
 
 }  // namespace
 
-struct lg_matcher {
-    int device = 0, n_layers = 0;
-    float threshold = 0.1f;
-    cublasLtHandle_t lt = nullptr;
-    uint8_t* blob = nullptr;  // device copy of the weight blob
-    const float* wr = nullptr;
-    std::vector<BlockW> self_w, cross_w;
-    const __half *wf_t = nullptr, *bf = nullptr;
-    // ---- plan (one shape resident)
+// Everything that depends on the (pairs, n0, n1) shape: device buffers, cuBLASLt plans, the captured graph.
+struct ShapePlan {
     int pairs = 0, n0 = 0, n1 = 0;
     long long rows = 0;
     uint8_t* pool = nullptr;
@@ -149,21 +143,41 @@ struct lg_matcher {
     void *assign_ws = nullptr, *lt_ws = nullptr;
     size_t assign_ws_bytes = 0;
     Gemm g_qkv, g_cross_in, g_ffn1, g_ffn2, g_final, g_sim;
-    cudaStream_t stream = nullptr;  // capture / host-buffer stream
     cudaGraph_t graph = nullptr;
     cudaGraphExec_t exec = nullptr;
     int launches = 0;
-    // asynchronous host-buffer path: a copy stream fills one of two device staging slots while the
-    // compute stream runs the previous sub-batch (slot layout: kpts0 | kpts1 | desc0 | desc1)
-    cudaStream_t copy_stream = nullptr;
+    // asynchronous host-buffer path: device staging slots (slot layout: kpts0 | kpts1 | desc0 | desc1)
     uint8_t* stage[2] = {nullptr, nullptr};
+    unsigned long long last_use = 0;
+};
+
+// The reference engine is dynamic (1..2048 keypoints per image, a different count for every pair — steps.txt:152 profiles);
+// a shape change here costs cudaMalloc + a warm-up forward + graph capture, so the engine keeps the active plan plus a few
+// parked ones (least recently used is evicted) instead of re-planning every time two shapes alternate.
+constexpr size_t kMaxParkedPlans = 3;
+
+struct lg_matcher : ShapePlan {   // the inherited members are the ACTIVE plan
+    int device = 0, n_layers = 0;
+    float threshold = 0.1f;
+    cublasLtHandle_t lt = nullptr;
+    uint8_t* blob = nullptr;  // device copy of the weight blob
+    const float* wr = nullptr;
+    std::vector<BlockW> self_w, cross_w;
+    const __half *wf_t = nullptr, *bf = nullptr;
+    cudaStream_t stream = nullptr;  // capture / host-buffer stream
+    // asynchronous host-buffer path: a copy stream fills one of two staging slots while the compute stream runs the previous
+    // sub-batch
+    cudaStream_t copy_stream = nullptr;
     cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_free[2] = {nullptr, nullptr};
     unsigned long long submits = 0;
+    std::vector<ShapePlan> parked;
+    unsigned long long tick = 0;
+    ShapePlan& active() { return *this; }
 };
 
 namespace {
 
-void free_plan(lg_matcher* m) {
+void free_plan(ShapePlan* m) {
     if (m->exec) cudaGraphExecDestroy(m->exec);
     if (m->graph) cudaGraphDestroy(m->graph);
     m->exec = nullptr;
@@ -265,7 +279,10 @@ cudaError_t place_desc(const void* src, __half* xc, long long rows, cudaStream_t
     const long long n_vec = rows * 32;
     if (n_vec == 0) return cudaSuccess;
     const long long blocks = (n_vec + 255) / 256;
-    place_desc_kernel<<<static_cast<unsigned>(blocks < 148 * 16 ? blocks : 148 * 16), 256, 0, st>>>(
+    int dev = 0, sms = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) sms = 148;
+    const long long cap = 16LL * sms;   // grid-stride beyond 16 CTAs per SM
+    place_desc_kernel<<<static_cast<unsigned>(blocks < cap ? blocks : cap), 256, 0, st>>>(
         static_cast<const uint4*>(src), reinterpret_cast<uint4*>(xc), n_vec);
     return cudaGetLastError();
 }
@@ -410,15 +427,35 @@ static int build_plan(lg_matcher* m, int pairs, int n0, int n1) {
 
 int lg_matcher_plan(lg_matcher* m, int pairs, int n0, int n1) {
     if (m == nullptr || pairs <= 0 || n0 <= 0 || n1 <= 0) return LG_ATTN_EINVAL;
+    m->last_use = ++m->tick;
     if (m->exec != nullptr && m->pairs == pairs && m->n0 == n0 && m->n1 == n1) return 0;
     cudaError_t e = cudaSetDevice(m->device);
     if (e != cudaSuccess) return static_cast<int>(e);
-    if (m->pool != nullptr) {
-        // the old plan's buffers may still be in use by a forward enqueued on the caller's stream
-        e = cudaDeviceSynchronize();
-        if (e != cudaSuccess) return static_cast<int>(e);
+    // a parked plan of this shape: swap it in.  Nothing is freed, so forwards still in flight on the old plan's buffers are safe.
+    for (ShapePlan& q : m->parked) {
+        if (q.exec != nullptr && q.pairs == pairs && q.n0 == n0 && q.n1 == n1) {
+            std::swap(m->active(), q);
+            m->last_use = m->tick;
+            return 0;
+        }
     }
-    free_plan(m);
+    if (m->exec != nullptr) {   // park the active plan; evict the least recently used one if the shelf is full
+        if (m->parked.size() >= kMaxParkedPlans) {
+            size_t lru = 0;
+            for (size_t i = 1; i < m->parked.size(); ++i)
+                if (m->parked[i].last_use < m->parked[lru].last_use) lru = i;
+            // the evicted plan's buffers may still be in use by a forward enqueued on a caller's stream
+            e = cudaDeviceSynchronize();
+            if (e != cudaSuccess) return static_cast<int>(e);
+            free_plan(&m->parked[lru]);
+            m->parked.erase(m->parked.begin() + static_cast<long>(lru));
+        }
+        m->parked.push_back(m->active());
+        m->active() = ShapePlan{};
+    } else {
+        free_plan(m);   // a half-initialised active plan (previous build failed) holds nothing, but keep the invariant
+    }
+    m->last_use = m->tick;
     const int rc = build_plan(m, pairs, n0, n1);
     if (rc != 0) {          // never leave a half-built plan behind: the next call must re-plan, not launch it
         (void)cudaStreamSynchronize(m->stream);
@@ -426,6 +463,11 @@ int lg_matcher_plan(lg_matcher* m, int pairs, int n0, int n1) {
         (void)cudaGetLastError();   // a failed allocation must not surface later as a launch error
     }
     return rc;
+}
+
+int lg_matcher_plans_resident(const lg_matcher* m) {
+    if (m == nullptr) return 0;
+    return static_cast<int>(m->parked.size()) + (m->exec != nullptr ? 1 : 0);
 }
 
 int lg_matcher_launches(const lg_matcher* m) { return m ? m->launches : 0; }
@@ -481,7 +523,9 @@ int lg_matcher_submit_host(lg_matcher* m, const float* kpts0, const float* kpts1
         matches0 == nullptr || mscores0 == nullptr)
         return LG_ATTN_EINVAL;
     if (m->exec == nullptr || m->pairs != pairs || m->n0 != n0 || m->n1 != n1) {
-        int rc = lg_matcher_sync(m);      // a shape change drains the pipeline, then re-plans
+        bool parked = false;
+        for (const ShapePlan& q : m->parked) parked = parked || (q.exec != nullptr && q.pairs == pairs && q.n0 == n0 && q.n1 == n1);
+        int rc = parked ? 0 : lg_matcher_sync(m);   // building a plan drains the pipeline; swapping a parked one in does not
         if (rc == 0) rc = lg_matcher_plan(m, pairs, n0, n1);
         if (rc != 0) return rc;
     }
@@ -519,8 +563,10 @@ int lg_matcher_sync(lg_matcher* m) {
 void lg_matcher_destroy(lg_matcher* m) {
     if (m == nullptr) return;
     (void)cudaSetDevice(m->device);
-    if (m->stream) (void)cudaStreamSynchronize(m->stream);
+    (void)cudaDeviceSynchronize();   // parked plans may have forwards in flight on callers' streams
     free_plan(m);
+    for (ShapePlan& q : m->parked) free_plan(&q);
+    m->parked.clear();
     if (m->stream) (void)cudaStreamDestroy(m->stream);
     if (m->copy_stream) (void)cudaStreamDestroy(m->copy_stream);
     for (int i = 0; i < 2; ++i) {

@@ -15,6 +15,13 @@
 #pragma once
 #include "ptx_sm100.cuh"
 
+// Build switches that produce WRONG results by design (timing decompositions only) must be asked for twice, so that a stray -D
+// can never ship a kernel that fails parity: csrc/build.py's product build does not define LG_ATTN_TUNING_BUILD, and
+// tests/test_boundary_cpu.py checks the shipped library was built without any of them.
+#if (defined(LG_ATTN_WHATIF) || defined(LG_ATTN_EXPERIMENT_NOSUM)) && !defined(LG_ATTN_TUNING_BUILD)
+#error "LG_ATTN_WHATIF / LG_ATTN_EXPERIMENT_NOSUM give wrong results: tuning builds only (-DLG_ATTN_TUNING_BUILD)"
+#endif
+
 #ifndef LG_ATTN_POLY_OF_8
 #define LG_ATTN_POLY_OF_8 2
 #endif

@@ -82,8 +82,19 @@ static int worker(const Args& a, int rank, const std::vector<char>& blob, Worker
     __half *d0, *d1;
     int* m0;
     const size_t nk = static_cast<size_t>(a.pairs) * n * 2, nd = static_cast<size_t>(a.pairs) * n * 256, nm = static_cast<size_t>(a.pairs) * n;
-    cudaMallocHost(&k0, nk * 4); cudaMallocHost(&k1, nk * 4); cudaMallocHost(&d0, nd * 2); cudaMallocHost(&d1, nd * 2);
-    cudaMallocHost(&m0, nm * 4); cudaMallocHost(&ms, nm * 4);
+    {
+        cudaError_t me = cudaMallocHost(&k0, nk * 4);
+        if (me == cudaSuccess) me = cudaMallocHost(&k1, nk * 4);
+        if (me == cudaSuccess) me = cudaMallocHost(&d0, nd * 2);
+        if (me == cudaSuccess) me = cudaMallocHost(&d1, nd * 2);
+        if (me == cudaSuccess) me = cudaMallocHost(&m0, nm * 4);
+        if (me == cudaSuccess) me = cudaMallocHost(&ms, nm * 4);
+        if (me != cudaSuccess) {
+            fprintf(stderr, "rank %d: cudaMallocHost: %s\n", rank, cudaGetErrorString(me));
+            lg_matcher_destroy(eng);
+            return static_cast<int>(me);
+        }
+    }
     for (int i = 0; i < a.pairs; ++i) {
         std::mt19937 gen(1000u + static_cast<unsigned>(rank + i * a.gpus));
         std::uniform_real_distribution<float> u(-1.f, 1.f);
@@ -111,7 +122,7 @@ static int worker(const Args& a, int rank, const std::vector<char>& blob, Worker
         }
         if (rc == 0) rc = lg_matcher_sync(eng);   // one step = all of this rank's pairs matched and back on the host
     };
-    step();  // warm-up (also re-plans a short last sub-batch once)
+    step();  // warm-up (a short last sub-batch gets its own plan here; afterwards the two plans are swapped, not rebuilt)
     step();
     const auto t0 = std::chrono::steady_clock::now();
     for (int i = 0; i < a.steps && rc == 0; ++i) step();

@@ -29,6 +29,7 @@ There is no CPU path: tensors must be on a CUDA device and the C-ABI library mus
 from __future__ import annotations
 
 import math
+from collections import OrderedDict
 from dataclasses import dataclass
 
 import torch
@@ -395,7 +396,7 @@ class PairMatcher:
     """
 
     def __init__(self, state_dict: dict | None = None, n_layers: int = 9, device="cuda:0", threshold: float = 0.1,
-                 seed: int = 0, use_graph: bool = True):
+                 seed: int = 0, use_graph: bool = True, max_plans: int = 8):
         if not torch.cuda.is_available():
             raise RuntimeError("PairMatcher needs a CUDA device (there is no CPU path)")
         B.load()
@@ -404,7 +405,10 @@ class PairMatcher:
         self.use_graph = use_graph
         sd = state_dict if state_dict is not None else reference_init_state_dict(seed, n_layers)
         self.w = MatcherWeights(sd, n_layers, self.device)
-        self._plans: dict[tuple, _Plan] = {}
+        # shape plans, least recently used first.  The reference engine is dynamic (1..2048 keypoints per image, different for
+        # every pair): an unbounded cache would grow by ~35 MB of buffers + one CUDA graph per distinct shape until OOM.
+        self._plans: "OrderedDict[tuple, _Plan]" = OrderedDict()
+        self.max_plans = int(max_plans)
 
     # -- one forward on the current stream (eager or under capture) ---------------------------------
     def _forward(self, p: _Plan, want_scores: bool) -> int:
@@ -465,7 +469,15 @@ class PairMatcher:
     def plan(self, b: int, n0: int, n1: int, want_scores: bool = False) -> _Plan:
         key = (b, n0, n1, want_scores)
         p = self._plans.get(key)
+        if p is not None:
+            self._plans.move_to_end(key)
         if p is None:
+            while len(self._plans) >= self.max_plans:
+                # evicted buffers / graph may still be in use by a forward enqueued on some stream
+                torch.cuda.synchronize(self.device)
+                _, old = self._plans.popitem(last=False)
+                old.graph = None
+                del old
             with torch.cuda.device(self.device):
                 p = _Plan(b, n0, n1, self.device, want_scores)
                 B.check(B.load().lg_attn_hd64_init_device(self.device.index or 0), "lg_attn_hd64_init_device")

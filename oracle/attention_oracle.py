@@ -101,3 +101,14 @@ def max_abs_err(got, ref) -> float:
 def rel_err(got, ref) -> float:
     ref = np.asarray(ref, dtype=np.float64)
     return max_abs_err(got, ref) / float(np.max(np.abs(ref)))
+
+
+def row_rel_err(got, ref) -> float:
+    """The stricter reading of "relative" (reported beside rel_err, tests/test_attention_gpu.py): every output row's max-abs error
+    over THAT row's max-abs reference value, maximised over rows — one normaliser per (batch, head, row) instead of one per tensor."""
+    got = np.asarray(got, dtype=np.float64)
+    ref = np.asarray(ref, dtype=np.float64)
+    err = np.max(np.abs(got - ref), axis=-1)
+    den = np.max(np.abs(ref), axis=-1)
+    return float(np.max(err / np.maximum(den, np.finfo(np.float64).tiny)))
+

@@ -4,6 +4,7 @@ import ctypes
 import json
 import re
 import subprocess
+import sys
 from pathlib import Path
 
 import pytest
@@ -30,6 +31,8 @@ def test_header_symbols_are_exported(pkg, lib):
         assert sym in exported, sym
         assert getattr(lib, sym) is not None
     assert lib.lg_attn_version() == 1
+    # the shipped library carries no tuning switch (what-if arithmetic, phase traces): see include/lg_attn.h
+    assert lib.lg_attn_build_flags() == 0
 
 
 def test_glue_header_symbols_are_exported(pkg, lib):
@@ -84,6 +87,43 @@ def test_library_is_sm100a_native(pkg):
     for mnemonic in ("UTCHMMA", "UTMALDG", "LDTM", "STTM"):
         assert mnemonic in sass, mnemonic
     assert "HMMA." not in sass.replace("UTCHMMA", "")  # no legacy mma.sync path
+
+
+def test_cmake_build_drops_in(pkg, tmp_path):
+    """The CMake flow of the reference's steps.txt (`cmake .. && make` in lightglue_attention_plugin/, CMakeLists.txt:11-12,76-89):
+    csrc/CMakeLists.txt configures for sm_100a without CUTLASS / libtorch and yields the same library name exporting every C-ABI
+    symbol and the plugin registration, with tcgen05 / TMA SASS inside."""
+    import shutil
+
+    if shutil.which("cmake") is None or shutil.which("ninja") is None:
+        pytest.skip("cmake / ninja not installed")
+    src = ROOT / "lightglue-with-flashattentionv2-tensorrt_b200" / "csrc"
+    bld = tmp_path / "build"
+    subprocess.run(["cmake", "-S", str(src), "-B", str(bld), "-G", "Ninja"], check=True, capture_output=True, text=True)
+    subprocess.run(["cmake", "--build", str(bld), "-j", "8"], check=True, capture_output=True, text=True)
+    lib_path = bld / "liblightglue_attention_plugin.so"
+    assert lib_path.exists() and (bld / "lg_pair_bench").exists()
+    out = subprocess.run(["nm", "-D", "--defined-only", str(lib_path)], capture_output=True, text=True, check=True).stdout
+    exported = set(re.findall(r" T (\w+)", out))
+    B = pkg._binding
+    for sym in B.C_ABI_SYMBOLS + B.MATCH_ABI_SYMBOLS + B.MATCHER_ABI_SYMBOLS:
+        assert sym in exported, sym
+    elfs = subprocess.run(["cuobjdump", "-lelf", str(lib_path)], capture_output=True, text=True).stdout
+    assert "sm_100a" in elfs and "sm_8" not in elfs and "sm_9" not in elfs
+    # load it in a fresh process (this one already holds the in-tree build and its plugin registry): static registration
+    # happened at load, the creator answers to the reference's plugin name / version
+    child = (
+        "import ctypes, json, sys\n"
+        "lib = ctypes.CDLL(sys.argv[1])\n"
+        "assert lib.lg_attn_version() == 1 and lib.lg_attn_build_flags() == 0\n"
+        "lib.lg_mock_trt_describe.argtypes = [ctypes.c_char_p, ctypes.c_size_t]\n"
+        "buf = ctypes.create_string_buffer(4096)\n"
+        "assert lib.lg_mock_trt_describe(buf, 4096) > 0\n"
+        "d = json.loads(buf.value.decode())\n"
+        "assert (d['name'], d['version'], d['namespace'], d['n_creators']) == ('MHAHeadDim64', '1', '', 1), d\n"
+        "print('ok')\n")
+    r = subprocess.run([sys.executable, "-c", child, str(lib_path)], capture_output=True, text=True)
+    assert r.returncode == 0 and r.stdout.strip() == "ok", r.stderr[-800:]
 
 
 def test_workspace_and_launch_counts(pkg, lib):
@@ -142,3 +182,39 @@ def test_python_operator_mirror(pkg):
     q = torch.zeros(1, 4, 8, 64)
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         pkg.Attention()(q, q, q)
+
+
+@pytest.mark.skipif(not Path("/root/reference/lightglue_pytorch_with_plugin/lightglue.py").exists(),
+                    reason="the reference checkout only exists in the build container")
+def test_bind_reference_model_routes_the_reference_call_sites_to_the_kernel(pkg):
+    """bind_reference_model swaps the kernel in under the reference's own 36 call sites
+    (lightglue_pytorch_with_plugin/lightglue.py:102-115 -> :148, :194, :198).  Checked here on CPU: after binding, the reference
+    module's MHAHeadDim64.forward IS ours, its ONNX symbolic is untouched, and its Attention module no longer computes eagerly
+    on CPU tensors — it raises the launcher's "no CPU fallback" error, i.e. the call really goes to the CUDA path."""
+    import importlib
+    import torch
+
+    sys.path.insert(0, "/root/reference")
+    try:
+        ref_lg = importlib.import_module("lightglue_pytorch_with_plugin.lightglue")
+    finally:
+        sys.path.remove("/root/reference")
+    ref_symbolic = ref_lg.MHAHeadDim64.symbolic
+    eager_forward = ref_lg.MHAHeadDim64.forward
+    q = torch.randn(1, 4, 8, 64)
+    assert ref_lg.Attention()(q, q, q).shape == q.shape            # stock reference: eager SDPA on CPU
+    try:
+        pkg.bind_reference_model(ref_lg)
+        assert ref_lg.MHAHeadDim64.forward is pkg.MHAHeadDim64.forward
+        assert ref_lg.MHAHeadDim64.symbolic is ref_symbolic
+        with pytest.raises(RuntimeError, match="no CPU fallback"):
+            ref_lg.Attention()(q, q, q)
+        # the whole reference model now runs its attention through the binding as well
+        model = ref_lg.LightGlue(features=None, n_layers=1).eval()
+        data = {"keypoints0": torch.rand(1, 8, 2), "keypoints1": torch.rand(1, 6, 2),
+                "descriptors0": torch.randn(1, 8, 256), "descriptors1": torch.randn(1, 6, 256)}
+        with pytest.raises(RuntimeError, match="no CPU fallback"), torch.no_grad():
+            model(data["keypoints0"], data["keypoints1"], data["descriptors0"], data["descriptors1"])
+    finally:
+        ref_lg.MHAHeadDim64.forward = eager_forward
+

@@ -95,17 +95,22 @@ def test_assignment_kernels_match_oracle(pkg, b, n0, n1):
 
 # ------------------------------------------------------------------------------------------------ full matcher
 def _agreement(ref_scores: torch.Tensor, got_m0: torch.Tensor):
-    """share of the reference's mutual-NN matches reproduced + the largest reference score gap among
-    disagreements (a disagreement is benign when the reference itself was nearly tied)."""
+    """share of the reference's mutual-NN matches reproduced + the largest reference margin among disagreements.  A reference
+    match (i, j) needs j = argmax of row i AND i = argmax of column j; it can only be lost to score noise if one of those two
+    was nearly tied in the reference, so the margin of a disagreement is min(row margin, column margin) to the runner-up: a
+    disagreement is benign when that is small (scores agree to TOL_SCORES_MAX), a large one is a real error."""
     want_m0, _ = mo.filter_matches(ref_scores, 0.0)
     want, got = want_m0[0], got_m0[0].long().cpu()
     has = want >= 0
     agree = float((got[has] == want[has]).float().mean()) if has.any() else 1.0
     worst_gap = 0.0
+    sc = ref_scores[0]
     for i in torch.nonzero(has & (got != want))[:, 0].tolist():
-        row = ref_scores[0, i]
-        alt = got[i] if got[i] >= 0 else row.topk(2).indices[1] if row.numel() > 1 else want[i]
-        worst_gap = max(worst_gap, float(row[want[i]] - row[alt]))
+        j = int(want[i])
+        row, col = sc[i], sc[:, j]
+        row_margin = float(row[j] - row.topk(2).values[1]) if row.numel() > 1 else float("inf")
+        col_margin = float(col[i] - col.topk(2).values[1]) if col.numel() > 1 else float("inf")
+        worst_gap = max(worst_gap, min(row_margin, col_margin))
     return agree, worst_gap
 
 
@@ -197,6 +202,78 @@ def test_nine_layer_ragged_pair_matches_oracle(pkg):
     assert float(err.max()) <= TOL_SCORES_MAX and float(err.mean()) <= TOL_SCORES_MEAN
     agree, gap = _agreement(want["scores"], out["matches0"])
     assert agree >= MIN_MATCH_AGREEMENT and gap < 0.1
+
+
+@pytest.mark.parametrize("n", [1024, 2048])
+def test_config4_full_size_pair_matches_oracle(pkg, n, capsys):
+    """BASELINE.json configs[3] (the 1x1024x1024 engine shape) and the 2048-keypoint shape of configs[4]: the full 9-layer
+    matcher against the FP32 CPU oracle (oracle/matcher_oracle.py = lightglue_pytorch_no_plugin/lightglue.py:359-384 +
+    filter_matches :265-288) on freiburg-shaped synthetic SuperPoint features.  Prints the agreement figures DESIGN.md quotes."""
+    sd = pkg.reference_init_state_dict(0, 9)
+    f = mo.synth_pair(1000 + n, n, n) if n == 1024 else mo.synth_pair(1000 + n, n, n, width=1280, height=960)
+    out = pkg.PairMatcher(sd, n_layers=9, threshold=0.0, device=DEV).match(*(t.to(DEV) for t in f), want_scores=True)
+    want = mo.forward(sd, *f, n_layers=9, threshold=0.0)
+    err = (out["scores"].cpu() - want["scores"]).abs()
+    agree, gap = _agreement(want["scores"], out["matches0"])
+    n_ref = int((want["matches0"] >= 0).sum())
+    with capsys.disabled():
+        print(f"\n[config4 parity] {n}x{n} kpts, 9 layers: scores max-abs err {float(err.max()):.4f}, mean-abs {float(err.mean()):.5f}; "
+              f"mutual-NN matches in the reference {n_ref}, reproduced {agree * 100:.2f} % (largest reference score gap among "
+              f"disagreements {gap:.4f})")
+    assert float(err.max()) <= TOL_SCORES_MAX and float(err.mean()) <= TOL_SCORES_MEAN
+    assert agree >= MIN_MATCH_AGREEMENT and gap < 0.1
+
+
+def test_assignment_survives_nan_and_inf_rows(pkg):
+    """FP16 overflow upstream can hand the assignment a similarity row of NaN / -inf: such a row has no argmax (the index stays
+    at the INT_MAX sentinel), must not be dereferenced (illegal address) and must report 'no match'; other rows are unaffected."""
+    g = torch.Generator().manual_seed(5)
+    b, n0, n1 = 2, 130, 96
+    sim = torch.randn(b, n0, n1, generator=g) * 3
+    z0, z1 = torch.randn(b, n0, generator=g).half(), torch.randn(b, n1, generator=g).half()
+    clean = pkg.matcher.assign(sim.to(DEV), z0.to(DEV), z1.to(DEV), 0.0)
+    bad = sim.clone()
+    bad[0, 7] = float("nan")
+    bad[1, 100] = float("-inf")
+    m0, ms, _ = pkg.matcher.assign(bad.to(DEV), z0.to(DEV), z1.to(DEV), 0.0)
+    torch.cuda.synchronize()
+    assert int(m0[0, 7]) == -1 and int(m0[1, 100]) == -1
+    assert float(ms[1, 100]) == 0.0
+    assert ((m0.cpu() >= -1) & (m0.cpu() < n1)).all()
+    # a -inf row adds exp(-inf) = 0 to every column's log-sum-exp: rows of that pair that had a mutual match keep it, score included
+    had = clean[0][1].cpu() >= 0
+    had[100] = False
+    assert torch.equal(m0[1].cpu()[had], clean[0][1].cpu()[had])
+    torch.testing.assert_close(ms[1].cpu()[had], clean[1][1].cpu()[had], rtol=1e-5, atol=1e-30)
+
+
+def test_plan_caches_are_bounded_and_alternating_shapes_do_not_replan(pkg):
+    """The engine is dynamic (every pair has its own keypoint counts): shape plans are cached LRU with a bound, results do not
+    depend on what was evicted, and two alternating shapes are swapped instead of rebuilt (native engine: plans_resident)."""
+    sd = pkg.reference_init_state_dict(1, 2)
+    pm = pkg.PairMatcher(sd, n_layers=2, threshold=0.0, device=DEV, max_plans=3)
+    shapes = [(40, 33), (64, 64), (50, 70), (33, 40), (90, 10)]
+    feats = {s: tuple(t.to(DEV) for t in mo.synth_pair(7 + i, *s)) for i, s in enumerate(shapes)}
+    first = {s: pm.match(*feats[s])["matches0"].clone() for s in shapes}
+    assert len(pm._plans) == 3
+    for s in shapes:                     # every shape again, most of them after an eviction
+        assert torch.equal(pm.match(*feats[s])["matches0"], first[s])
+    assert len(pm._plans) == 3
+    # native engine: active + parked plans, LRU eviction at 4, alternation without re-planning
+    eng = pkg.NativeMatcher(sd, n_layers=2, device=0, threshold=0.0)
+    lib = pkg.load()
+    host = {s: mo.synth_pair(7 + i, *s) for i, s in enumerate(shapes)}
+    got = {}
+    for s in shapes:
+        k0, k1, d0, d1 = host[s]
+        got[s] = eng.match_host(k0.numpy(), k1.numpy(), d0.half().numpy(), d1.half().numpy())["matches0"].copy()
+        assert float((got[s] == first[s].cpu().numpy()).mean()) >= MIN_MATCH_AGREEMENT
+    assert lib.lg_matcher_plans_resident(eng._h) == 4
+    for _ in range(3):
+        for s in shapes[-2:]:
+            k0, k1, d0, d1 = host[s]
+            assert np.array_equal(eng.match_host(k0.numpy(), k1.numpy(), d0.half().numpy(), d1.half().numpy())["matches0"], got[s])
+    assert lib.lg_matcher_plans_resident(eng._h) == 4
 
 
 # ------------------------------------------------------------------------------------------------ native C++ engine

@@ -1,6 +1,6 @@
 """Condense an .ncu-rep (read here, no GPU) into the handful of numbers the kernel notes quote.
 
-    python tools/ncu_summary.py gpurun_out/prof.ncu-rep [--source N]    # N hottest SASS lines by stall samples
+    python tools/ncu_summary.py gpurun_out/prof.ncu-rep [--source N] [--json profiles/x.json]   # N hottest SASS lines by stall samples
 """
 import csv
 import io
@@ -20,12 +20,26 @@ KEYS = ["gpu__time_duration.sum", "sm__cycles_elapsed.max", "sm__cycles_elapsed.
         "l1tex__data_pipe_tc_wavefronts_mem_shared.sum.pct_of_peak_sustained_elapsed"]
 
 
-def raw(rep):
+def raw(rep, json_out=None):
     out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(out)))
-    hdr = rows[0]
-    for vals in rows[2:]:
+    hdr, units = rows[0], rows[1]
+    for n, vals in enumerate(rows[2:]):
         d = dict(zip(hdr, vals))
+        if json_out and n == 0:
+            import json
+            u = dict(zip(hdr, units))
+            scale = {"Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "byte": 1.0}
+            keep = {"kernel": d.get("Kernel Name"), "source_report": rep}
+            for k in KEYS:
+                if k in d and d[k] != "":
+                    keep[k] = float(d[k].replace(",", "")) * (scale.get(u.get(k, ""), 1.0) if k.startswith("dram__bytes") or k.startswith("lts__t_bytes") else 1.0)
+                    if not (k.startswith("dram__bytes") or k.startswith("lts__t_bytes")):
+                        keep[k + ".unit"] = u.get(k, "")
+            stalls_j = {k.replace("smsp__average_warps_issue_stalled_", "").replace("_per_issue_active.ratio", ""): float(v)
+                        for k, v in d.items() if k.startswith("smsp__average_warps_issue_stalled_") and k.endswith("_per_issue_active.ratio") and v}
+            keep["stalls_per_issue"] = dict(sorted(stalls_j.items(), key=lambda kv: -kv[1])[:8])
+            open(json_out, "w").write(json.dumps(keep, indent=1) + "\n")
         print("==", d.get("Kernel Name", "?")[:100])
         for k in KEYS:
             if k in d:
@@ -56,6 +70,6 @@ def source(rep, top):
 
 if __name__ == "__main__":
     rep = sys.argv[1]
-    raw(rep)
+    raw(rep, sys.argv[sys.argv.index("--json") + 1] if "--json" in sys.argv else None)
     if "--source" in sys.argv:
         source(rep, int(sys.argv[sys.argv.index("--source") + 1]))
