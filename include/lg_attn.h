@@ -67,8 +67,8 @@ int lg_attn_debug_describe_launch(int batch, int heads, int n_q, int n_kv, char*
  * Replaces the static-initialiser cudaFuncSetAttribute of the reference (…fp16out.cu:242-250). */
 int lg_attn_hd64_init_device(int device);
 
-/* Scratch bytes the launcher needs for this problem: 0 for the half-input modes, the FP16 copy of
- * Q,K,V for LG_ATTN_F32_F32.  Replaces the fixed 5 MiB of getWorkspaceSize (…plugin.cpp:96-112). */
+/* Scratch bytes the launcher needs for this problem: 0 in every mode (LG_ATTN_F32_F32 converts to FP16 on the way into shared
+ * memory).  Replaces the fixed 5 MiB of getWorkspaceSize (…plugin.cpp:96-112); kept so that callers keep asking. */
 size_t lg_attn_hd64_workspace_bytes(int batch, int heads, int n_q, int n_kv, int io_dtype);
 
 /* The hot path: enqueue one fused attention on `stream` (a cudaStream_t passed as void*).
@@ -115,7 +115,8 @@ int lg_attn_session_submit(lg_attn_session* s, const void* q_host, const void* k
 int lg_attn_session_sync(lg_attn_session* s);
 void lg_attn_session_destroy(lg_attn_session* s);
 
-/* Number of kernels lg_attn_hd64_launch() enqueues for a dtype (1, or 2 for LG_ATTN_F32_F32). */
+/* Number of kernels lg_attn_hd64_launch() enqueues for a dtype: 1 in every mode (the reference enqueues 2-3: pad / convert,
+ * attention, unpad — …plugin.cpp:177-267). */
 int lg_attn_hd64_launches_per_call(int io_dtype);
 
 /* Human-readable name of a return code (static storage). */

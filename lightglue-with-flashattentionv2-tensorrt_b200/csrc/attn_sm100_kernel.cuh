@@ -58,6 +58,15 @@ using namespace ptx;
 
 constexpr int kSoftmaxWarps = 8;                     // two column-half warpgroups over the same 128 rows
 constexpr int kThreads = 32 * (kSoftmaxWarps + 4);   // + TMA, MMA, TMEM-alloc, spare
+// FP32-input instantiation (the plugin's kFLOAT branch, one launch): warps 10..23 convert the FP32 tiles that TMA brings in
+// into the swizzled FP16 operand tiles (replaces QKV_convert_from_fp32_to_fp16, …fp32out.cu:706-804).  Q and K(0) are on the
+// critical path of the first S, hence the many converter warps: 128 row pairs / 14 warps = 9-10 short iterations each.
+#ifndef LG_ATTN_CVT_WARPS
+#define LG_ATTN_CVT_WARPS 14
+#endif
+constexpr int kCvtWarps = LG_ATTN_CVT_WARPS;
+constexpr int kThreadsF32 = 32 * (kSoftmaxWarps + 2 + kCvtWarps);
+static_assert((2 + kCvtWarps) % 4 == 0, "setmaxnreg wants whole warpgroups of service warps");
 // Q tile + 2 x (K, V) tiles (16 KiB each) + barriers / row statistics, + 1 KiB slack for 1024-B alignment
 constexpr uint32_t kSmemBytes = (1 + 2 * kStages) * 16384 + 5120 + 1024;
 
@@ -82,7 +91,10 @@ enum : uint32_t {
     kBarPFull,
     kBarPVDone,
     kBarComb,                         // split-KV: bytes pushed into this CTA's receive area
-    kNumBars
+    kBarRawQ,                         // FP32 input: the raw FP32 tile has landed in its buffer (TMA transaction barriers)
+    kBarRawK,                         // [kStages]
+    kBarRawV = kBarRawK + kStages,    // [kStages]
+    kNumBars = kBarRawV + kStages
 };
 constexpr uint32_t kSmemTmemSlot = kSmemBar + 8 * kNumBars;
 // row-max / row-sum exchange between the two column halves: [parity][half][row] floats
@@ -100,6 +112,15 @@ constexpr uint32_t kSmemCombO = (kSmemUsed + 127u) & ~127u;
 constexpr uint32_t kSmemSplitExtra = kBlockM * kHeadDim * 4 + 128;
 constexpr uint32_t kCombBytes = kBlockM * kHeadDim * 4 + kBlockM * 8;  // what each CTA receives in total
 constexpr int kMaxSplits = 8;  // portable cluster size
+// FP32 input: every operand tile gets a 32 KiB buffer.  TMA fills it with the FP32 tile as two boxes of 128 rows x 32 floats
+// (128-byte rows, no swizzle: [box][row][32 floats]); the converter warps then rewrite it IN PLACE — a warp owns whole rows, reads
+// both halves of a row pair into registers and writes the 128-byte-swizzled FP16 rows over the first 16 KiB (= box 0's rows of the
+// same row pair) — so there is no staging ring to wait for and all first loads are in flight at once, like the FP16 path.
+// Q at 0, stage s: K at 32K + s*64K, V at 64K + s*64K; the barrier / statistics / split-KV blocks sit kSmemShiftF32 further up.
+constexpr uint32_t kRawBytes = kBlockN * kHeadDim * 4;   // 32 KiB
+constexpr uint32_t kSmemShiftF32 = (1 + 2 * kStages) * (kRawBytes - kTileBytes);
+constexpr uint32_t kSmemBytesF32 = kSmemBytes + kSmemSplitExtra + kSmemShiftF32;
+static_assert(kSmemBytesF32 <= 227 * 1024, "shared memory budget (FP32 input)");
 
 // TMEM column map
 constexpr uint32_t kTmemCols = 256;
@@ -146,8 +167,8 @@ __device__ __forceinline__ void trace_event(int seq, int ev) {
 
 // kBigSmem only distinguishes the instantiation launched with the extra split-KV receive area, so that
 // its larger MaxDynamicSharedMemorySize attribute does not cap the occupancy of the regular launches.
-template <bool kOutF32, bool kBigSmem = false>
-__global__ void __launch_bounds__(kThreads, 2)
+template <bool kOutF32, bool kBigSmem = false, bool kInF32 = false>
+__global__ void __launch_bounds__(kInF32 ? kThreadsF32 : kThreads, kInF32 ? 1 : 2)
 lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
                  const __grid_constant__ CUtensorMap tm_v, void* __restrict__ out, int n_q, int n_kv,
                  int tiles_m, int num_splits, int flags, const OutLayout ol LG_TRACE_ARG) {
@@ -157,10 +178,9 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
     // mbarrier operation of the KV loop (+1.6 % on the throughput kernel, same-box A/B)
     uint32_t smem = (smem_u32(smem_raw) + 1023u) & ~1023u;
     asm volatile("mov.u32 %0, %0;" : "+r"(smem));
-    const uint32_t bars = smem + kSmemBar;
+    constexpr uint32_t kOff = kInF32 ? kSmemShiftF32 : 0u;   // FP32 input: everything behind the (larger) tile buffers moves up
+    const uint32_t bars = smem + kSmemBar + kOff;
     auto bar = [&](uint32_t i) { return bars + 8u * i; };
-    auto smem_k = [&](int s) { return smem + kSmemRing + static_cast<uint32_t>(s) * kStageBytes; };
-    auto smem_v = [&](int s) { return smem + kSmemRing + static_cast<uint32_t>(s) * kStageBytes + kTileBytes; };
 
     const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
     const int lane = threadIdx.x & 31;
@@ -181,20 +201,37 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
     // that the operands of UTMALDG / UTCHMMA / UTCBAR are warp-uniform and wraps every one of them in an R2UR + BRA.U.ANY waterfall
     // loop (~80 clk each; see attn_sm100_kernel_mq.cuh).  smem_u is the un-pinned (provably uniform) copy of the aligned base.
     const uint32_t smem_u = (smem_u32(smem_raw) + 1023u) & ~1023u;
-    const uint32_t bars_u = smem_u + kSmemBar;
+    const uint32_t bars_u = smem_u + kSmemBar + kOff;
     auto ubar = [&](uint32_t i) { return bars_u + 8u * i; };
-    auto usmem_k = [&](int s) { return smem_u + kSmemRing + static_cast<uint32_t>(s) * kStageBytes; };
-    auto usmem_v = [&](int s) { return smem_u + kSmemRing + static_cast<uint32_t>(s) * kStageBytes + kTileBytes; };
+    auto usmem_k = [&](int s) {
+        return kInF32 ? smem_u + kRawBytes + static_cast<uint32_t>(s) * 2u * kRawBytes : smem_u + kSmemRing + static_cast<uint32_t>(s) * kStageBytes;
+    };
+    auto usmem_v = [&](int s) { return usmem_k(s) + (kInF32 ? kRawBytes : kTileBytes); };
+    // FP32 input: a raw tile = two 128-row x 32-float boxes into the tile's 32 KiB buffer (elected lane of the producer warp)
+    auto load_raw = [&](uint32_t dst, const CUtensorMap* tm, uint32_t full, int row, int b) {
+        mbar_arrive_expect_tx(full, kRawBytes);
+        tma_load_4d(dst, tm, full, 0, row, hi, b);
+        tma_load_4d(dst + kRawBytes / 2, tm, full, 32, row, hi, b);
+    };
     if (warp == kSoftmaxWarps && elect_one()) {
         prefetch_tmap(&tm_q);
         prefetch_tmap(&tm_k);
         prefetch_tmap(&tm_v);
-        mbar_init(ubar(kBarQFull), 1);
+        // FP16 input: the operand tiles are filled by TMA (one arrive.expect_tx each); FP32 input: by the converter warps
+        constexpr uint32_t kFillers = kInF32 ? kCvtWarps : 1;
+        mbar_init(ubar(kBarQFull), kFillers);
         for (int s = 0; s < kStages; ++s) {
-            mbar_init(ubar(kBarKFull + s), 1);
+            mbar_init(ubar(kBarKFull + s), kFillers);
             mbar_init(ubar(kBarKEmpty + s), 1);
-            mbar_init(ubar(kBarVFull + s), 1);
+            mbar_init(ubar(kBarVFull + s), kFillers);
             mbar_init(ubar(kBarVEmpty + s), 1);
+        }
+        if constexpr (kInF32) {
+            mbar_init(ubar(kBarRawQ), 1);
+            for (int s = 0; s < kStages; ++s) {
+                mbar_init(ubar(kBarRawK + s), 1);
+                mbar_init(ubar(kBarRawV + s), 1);
+            }
         }
         mbar_init(ubar(kBarSFull), 1);
         mbar_init(ubar(kBarSEmpty), kSoftmaxWarps);  // one arrival per softmax warp
@@ -213,26 +250,34 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
         pdl_wait_prior_grids();
         LG_TRACE(12);
         // First loads go out before the CTA-wide setup barrier (they only need this thread's inits).
-        mbar_arrive_expect_tx(ubar(kBarQFull), kTileBytes);
-        tma_load_4d(smem_u + kSmemQ, &tm_q, ubar(kBarQFull), 0, tile_m * kBlockM, hi, bi);
-        for (int j = 0; j < prologue_tiles; ++j) {
-            mbar_arrive_expect_tx(ubar(kBarKFull + j), kTileBytes);
-            tma_load_4d(usmem_k(j), &tm_k, ubar(kBarKFull + j), 0, (kv_tile0 + j) * kBlockN, hi, bk);
-            mbar_arrive_expect_tx(ubar(kBarVFull + j), kTileBytes);
-            tma_load_4d(usmem_v(j), &tm_v, ubar(kBarVFull + j), 0, (kv_tile0 + j) * kBlockN, hi, bk);
+        if constexpr (kInF32) {
+            load_raw(smem_u + kSmemQ, &tm_q, ubar(kBarRawQ), tile_m * kBlockM, bi);
+            for (int j = 0; j < prologue_tiles; ++j) {
+                load_raw(usmem_k(j), &tm_k, ubar(kBarRawK + j), (kv_tile0 + j) * kBlockN, bk);
+                load_raw(usmem_v(j), &tm_v, ubar(kBarRawV + j), (kv_tile0 + j) * kBlockN, bk);
+            }
+        } else {
+            mbar_arrive_expect_tx(ubar(kBarQFull), kTileBytes);
+            tma_load_4d(smem_u + kSmemQ, &tm_q, ubar(kBarQFull), 0, tile_m * kBlockM, hi, bi);
+            for (int j = 0; j < prologue_tiles; ++j) {
+                mbar_arrive_expect_tx(ubar(kBarKFull + j), kTileBytes);
+                tma_load_4d(usmem_k(j), &tm_k, ubar(kBarKFull + j), 0, (kv_tile0 + j) * kBlockN, hi, bk);
+                mbar_arrive_expect_tx(ubar(kBarVFull + j), kTileBytes);
+                tma_load_4d(usmem_v(j), &tm_v, ubar(kBarVFull + j), 0, (kv_tile0 + j) * kBlockN, hi, bk);
+            }
         }
         LG_TRACE(13);
     }
     __syncwarp();
     if (warp == kSoftmaxWarps + 2) {
-        tmem_alloc<kTmemCols>(smem + kSmemTmemSlot);
+        tmem_alloc<kTmemCols>(smem + kOff + kSmemTmemSlot);
         tmem_relinquish();
     }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     uint32_t tmem_base;
-    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(smem + kSmemTmemSlot));
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(smem + kOff + kSmemTmemSlot));
     if (threadIdx.x == 0) {
         // Small (single-wave) grids let the next kernel in the stream start its prologue right away;
         // large grids trigger at their epilogue so the dependents do not take slots from their own tail.
@@ -246,7 +291,50 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
     if (warp >= kSoftmaxWarps) {
         setmaxnreg_dec<kRegsOther>();
         const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
-        if (warp == kSoftmaxWarps) {
+        if (kInF32 && warp == kSoftmaxWarps) {
+            // ===================================================================== TMA producer (raw FP32 tiles)
+            for (int j = prologue_tiles; j < num_kv_tiles; ++j) {
+                const int s = j % kStages;
+                const uint32_t par = ((j / kStages) - 1) & 1;
+                mbar_wait_backoff(ubar(kBarKEmpty + s), par, LG_ATTN_SPIN_NS);   // the MMAs that read this buffer's FP16 tile are done
+                if (elect_one()) load_raw(usmem_k(s), &tm_k, ubar(kBarRawK + s), (kv_tile0 + j) * kBlockN, bk);
+                __syncwarp();
+                mbar_wait_backoff(ubar(kBarVEmpty + s), par, LG_ATTN_SPIN_NS);
+                if (elect_one()) load_raw(usmem_v(s), &tm_v, ubar(kBarRawV + s), (kv_tile0 + j) * kBlockN, bk);
+                __syncwarp();
+            }
+        } else if (kInF32 && warp >= kSoftmaxWarps + 2) {
+            // ===================================================================== FP32 -> FP16 converters (warps 10..), in place
+            // One warp iteration = one row pair (2p, 2p+1): lane l reads the float4 q4 = l % 8 of box (l / 8) % 2 of row 2p + l / 16
+            // (consecutive lanes read consecutive 16 B), all 32 loads complete (__syncwarp), then every lane writes its four halves to
+            // columns 32 box + 4 q4 of the 128-byte-swizzled FP16 row (16-byte chunk index XOR row % 8, as TMA SWIZZLE_128B would
+            // have written it) — bytes that belong to box 0 of the SAME row pair, which this warp has just read.  Round to nearest
+            // even, like QKV_convert_from_fp32_to_fp16 (…fp32out.cu:706-768).
+            const int cw = warp - (kSoftmaxWarps + 2);
+            const int total_loads = 1 + 2 * num_kv_tiles;   // 0 = Q, 1 + 2j = K(j), 2 + 2j = V(j)
+            for (int i = 0; i < total_loads; ++i) {
+                const int j = (i - 1) / 2, s = j % kStages;
+                const uint32_t buf = i == 0 ? smem_u + kSmemQ : ((i & 1) ? usmem_k(s) : usmem_v(s));
+                const uint32_t raw = i == 0 ? ubar(kBarRawQ) : ((i & 1) ? ubar(kBarRawK + s) : ubar(kBarRawV + s));
+                const uint32_t full = i == 0 ? ubar(kBarQFull) : ((i & 1) ? ubar(kBarKFull + s) : ubar(kBarVFull + s));
+                mbar_wait(raw, i == 0 ? 0u : static_cast<uint32_t>(j / kStages) & 1u);
+                const int row_in_pair = lane >> 4, box = (lane >> 3) & 1, q4 = lane & 7;
+#pragma unroll 2
+                for (int p = cw; p < kBlockN / 2; p += kCvtWarps) {
+                    const int r = 2 * p + row_in_pair;
+                    const uint4 u = ld_shared_v4(buf + static_cast<uint32_t>(box) * (kRawBytes / 2) + static_cast<uint32_t>(r) * 128u +
+                                                 static_cast<uint32_t>(q4) * 16u);
+                    const uint32_t h0 = pack_half2(__uint_as_float(u.x), __uint_as_float(u.y));
+                    const uint32_t h1 = pack_half2(__uint_as_float(u.z), __uint_as_float(u.w));
+                    __syncwarp();   // every lane holds its part of the row pair before anything of it is overwritten
+                    const uint32_t chunk = static_cast<uint32_t>(box * 4 + (q4 >> 1)) ^ static_cast<uint32_t>(r & 7);
+                    st_shared_v2u(buf + static_cast<uint32_t>(r) * 128u + (chunk << 4) + static_cast<uint32_t>(q4 & 1) * 8u, h0, h1);
+                }
+                fence_proxy_async_smem();   // generic-proxy writes -> visible to the tensor core's async-proxy reads
+                __syncwarp();
+                if (lane == 0) mbar_arrive(full);
+            }
+        } else if (!kInF32 && warp == kSoftmaxWarps) {
             // ===================================================================== TMA producer
             for (int j = prologue_tiles; j < num_kv_tiles; ++j) {
                 const int s = j % kStages;
@@ -333,7 +421,7 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
         const uint32_t t_s = tmem_base + lane_sel + kColS + static_cast<uint32_t>(half * kHalfN);
         const uint32_t t_o = tmem_base + lane_sel + kColO + static_cast<uint32_t>(half * 32);
         const uint32_t t_p = tmem_base + lane_sel + kColP + static_cast<uint32_t>(half * 32);
-        const uint32_t exch = smem + kSmemExch;  // [parity][half][row] floats
+        const uint32_t exch = smem + kOff + kSmemExch;  // [parity][half][row] floats
         // named barrier shared with the other column half of the same rows: ids 1..4 (immediates, so
         // the CTA reserves 6 of the SM's 16 hardware barriers and two CTAs still fit on one SM)
         auto pair_sync = [&]() {
@@ -445,7 +533,7 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
             //    (st.shared::cluster, 16-B chunks XOR-swizzled by owned row).  Direct DSMEM stores replace a
             //    local staging pass + bulk copies + a transaction barrier (7.8 -> 7.55 us per B=1 launch).
             const int rows_per = kBlockM / num_splits;
-            const uint32_t recv_o = smem + kSmemCombO;
+            const uint32_t recv_o = smem + kOff + kSmemCombO;
             const int owner = row / rows_per, lr_mine = row - owner * rows_per;
             const int slot_mine = split * rows_per + lr_mine;
             cluster_wait();                                // barrier #1: every peer CTA is running
@@ -470,7 +558,7 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
                                 pack_half2(__uint_as_float(orow[8 * c + 4]) * inv_own, __uint_as_float(orow[8 * c + 5]) * inv_own),
                                 pack_half2(__uint_as_float(orow[8 * c + 6]) * inv_own, __uint_as_float(orow[8 * c + 7]) * inv_own));
             }
-            if (half == 0) st_dsmem_v2(dsmem_addr(smem + kSmemCombStat + slot_mine * 8, owner), m_used, l_row);
+            if (half == 0) st_dsmem_v2(dsmem_addr(smem + kOff + kSmemCombStat + slot_mine * 8, owner), m_used, l_row);
             if (threadIdx.x == 0) LG_TRACE(6);
             // 2. cluster barrier #2 (release / acquire): every split's slices for the rows this CTA owns have
             //    landed.  After it nobody touches a peer's shared memory, so CTAs may exit independently.
@@ -501,7 +589,7 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
                 for (int sp = 0; sp < kMaxSplits; ++sp) {
                     if (sp < num_splits) {
                         const int slot = sp * rows_per + lr;
-                        const float2 st = ld_shared_v2f(smem + kSmemCombStat + slot * 8);
+                        const float2 st = ld_shared_v2f(smem + kOff + kSmemCombStat + slot * 8);
                         ms[sp] = st.x;
                         ls[sp] = st.y;
                         m_glob = fmaxf(m_glob, st.x);

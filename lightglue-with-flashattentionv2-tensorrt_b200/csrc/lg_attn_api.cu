@@ -11,7 +11,6 @@
 #include "attn_sm100_kernel.cuh"     // lgattn::w8 — latency shapes, split-KV clusters, PDL
 #include "attn_sm100_kernel_w4.cuh"  // lgattn::w4 — full grids whose Q-tile count packs badly into 2- / 4-tile work items
 #include "attn_sm100_kernel_mq.cuh"  // lgattn::mq — full grids: one persistent CTA per SM owning several Q tiles (throughput)
-#include "cvt_f32_f16.cuh"
 
 #include <cuda.h>
 #include <cuda_runtime.h>
@@ -40,6 +39,7 @@ std::atomic<int> g_device_ready[kMaxDevices];  // 0 = not initialised, 1 = ready
 std::atomic<EncodeTiledFn> g_encode{nullptr};
 int g_sm_count[kMaxDevices];              // written once per device under g_init_mutex, before g_device_ready
 int g_max_clusters[kMaxDevices][4];       // co-resident clusters of 1 << i CTAs (same publication rule)
+int g_max_clusters_f32[kMaxDevices][4];   // same for the FP32-input instantiation (1 CTA per SM)
 std::atomic<int> g_forced_splits{0};      // tuning override (LG_ATTN_SPLITS), 0 = automatic
 std::atomic<int> g_use_pdl{1};            // LG_ATTN_PDL=0 disables programmatic dependent launch
 std::atomic<int> g_full_grid_kernel{-1};  // full grids: -1 = automatic, 0 = w4, 1 = mq (4 Q tiles), 2 = mq (2 Q tiles)
@@ -136,6 +136,24 @@ int encode_rows_map(CUtensorMap* map, const void* base, int rows, int heads, int
     return r == CUDA_SUCCESS ? 0 : LG_ATTN_EDRIVER;
 }
 
+// FP32 Q / K / V of the plugin's kFLOAT branch, read directly by the latency kernel's FP32-input instantiation: same dims,
+// box (32 floats = 128 B, 128 rows, 1, 1), no swizzle (the converter warps write the swizzled FP16 operand tile themselves).
+int encode_rows_map_f32(CUtensorMap* map, const void* base, int rows, int heads, int batch, const RowStrides& st) {
+    const cuuint64_t dims[4] = {static_cast<cuuint64_t>(kHeadDim), static_cast<cuuint64_t>(rows),
+                                static_cast<cuuint64_t>(heads), static_cast<cuuint64_t>(batch)};
+    const cuuint64_t srow = static_cast<cuuint64_t>(rows > 1 ? st.row : kHeadDim) * 4;
+    const cuuint64_t shead = heads > 1 ? static_cast<cuuint64_t>(st.head) * 4 : srow;
+    const cuuint64_t sbatch = batch > 1 ? static_cast<cuuint64_t>(st.batch) * 4 : srow;
+    const cuuint64_t strides[3] = {srow, shead, sbatch};
+    const cuuint32_t box[4] = {32, static_cast<cuuint32_t>(kBlockN), 1, 1};
+    const cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = g_encode.load(std::memory_order_acquire)(
+        map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<void*>(base), dims, strides, box, estr,
+        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? 0 : LG_ATTN_EDRIVER;
+}
+
 int init_device_locked(int device) {
     cudaDeviceProp prop;
     cudaError_t e = cudaGetDeviceProperties(&prop, device);
@@ -176,6 +194,7 @@ int init_device_locked(int device) {
     opt_in(reinterpret_cast<const void*>(w8::lg_attn_hd64_fwd<true, false>), w8::kSmemBytes);
     opt_in(reinterpret_cast<const void*>(w8::lg_attn_hd64_fwd<false, true>), w8::kSmemBytes + w8::kSmemSplitExtra);
     opt_in(reinterpret_cast<const void*>(w8::lg_attn_hd64_fwd<true, true>), w8::kSmemBytes + w8::kSmemSplitExtra);
+    opt_in(reinterpret_cast<const void*>(w8::lg_attn_hd64_fwd<true, true, true>), w8::kSmemBytesF32);
     // how many clusters of 2 / 4 / 8 split-KV CTAs are co-resident on this device
     for (int lg = 1; lg <= 3 && e == cudaSuccess; ++lg) {
         cudaLaunchConfig_t cfg = {};
@@ -195,6 +214,14 @@ int init_device_locked(int device) {
             n = 0;  // no split launches on this device
         }
         g_max_clusters[device][lg] = n;
+        cfg.blockDim = dim3(w8::kThreadsF32);
+        cfg.dynamicSmemBytes = w8::kSmemBytesF32;
+        n = 0;
+        if (cudaOccupancyMaxActiveClusters(&n, w8::lg_attn_hd64_fwd<true, true, true>, &cfg) != cudaSuccess) {
+            (void)cudaGetLastError();
+            n = 0;
+        }
+        g_max_clusters_f32[device][lg] = n;
     }
     if (prev != device && prev >= 0) (void)cudaSetDevice(prev);
     return static_cast<int>(e);
@@ -235,12 +262,18 @@ extern "C" int lg_attn_debug_read_trace(unsigned long long* dst, int reset_seq) 
 // Shared tail of both public launchers: tensor maps + kernel choice + launch.  FP16 Q/K/V only.
 static int launch_core(const void* qh, const void* kh, const void* vh, void* o, int batch, int heads, int n_q,
                        int n_kv, bool out_f32, const RowStrides& sq, const RowStrides& sk, const RowStrides& sv,
-                       const RowStrides& so, int kv_shift, int device, cudaStream_t stream) {
+                       const RowStrides& so, int kv_shift, int device, cudaStream_t stream, bool in_f32 = false) {
     CUtensorMap tm_q, tm_k, tm_v;
     int rc;
-    if ((rc = encode_rows_map(&tm_q, qh, n_q, heads, batch, sq)) != 0) return rc;
-    if ((rc = encode_rows_map(&tm_k, kh, n_kv, heads, batch, sk)) != 0) return rc;
-    if ((rc = encode_rows_map(&tm_v, vh, n_kv, heads, batch, sv)) != 0) return rc;
+    if (in_f32) {
+        if ((rc = encode_rows_map_f32(&tm_q, qh, n_q, heads, batch, sq)) != 0) return rc;
+        if ((rc = encode_rows_map_f32(&tm_k, kh, n_kv, heads, batch, sk)) != 0) return rc;
+        if ((rc = encode_rows_map_f32(&tm_v, vh, n_kv, heads, batch, sv)) != 0) return rc;
+    } else {
+        if ((rc = encode_rows_map(&tm_q, qh, n_q, heads, batch, sq)) != 0) return rc;
+        if ((rc = encode_rows_map(&tm_k, kh, n_kv, heads, batch, sk)) != 0) return rc;
+        if ((rc = encode_rows_map(&tm_v, vh, n_kv, heads, batch, sv)) != 0) return rc;
+    }
     const OutLayout ol{so.batch, so.head, so.row, heads, batch, kv_shift};
     const long long bh_ll = static_cast<long long>(batch) * heads;
     const long long tiles_m_ll = (static_cast<long long>(n_q) + kBlockM - 1) / kBlockM;
@@ -257,7 +290,9 @@ static int launch_core(const void* qh, const void* kh, const void* vh, void* o, 
     const int kv_tiles = (n_kv + kBlockN - 1) / kBlockN;
     const long long base = bh_ll * tiles_m_ll;
     const int forced = g_forced_splits.load(std::memory_order_relaxed);
-    const bool full_grid = base >= 2LL * g_sm_count[device] && forced == 0;
+    // FP32 inputs (the plugin's kFLOAT branch: B = 1 engines) always take the latency kernel, whose FP32-input instantiation
+    // converts on the way into shared memory: one launch, no workspace, at the price of one CTA per SM on large grids
+    const bool full_grid = base >= 2LL * g_sm_count[device] && forced == 0 && !in_f32;
 
     cudaLaunchConfig_t cfg = {};
     cfg.stream = stream;
@@ -301,16 +336,17 @@ static int launch_core(const void* qh, const void* kh, const void* vh, void* o, 
         if (forced > 0) {
             splits = forced;
         } else if (base < g_sm_count[device]) {
+            const int* max_clusters = in_f32 ? g_max_clusters_f32[device] : g_max_clusters[device];
             for (int lg = 1; lg <= 3; ++lg)
-                if ((1 << lg) <= kv_tiles && base <= g_max_clusters[device][lg]) splits = 1 << lg;
+                if ((1 << lg) <= kv_tiles && base <= max_clusters[lg]) splits = 1 << lg;
         }
         while (splits > 1 && splits > kv_tiles) splits /= 2;
         if (base * splits > 2147483647LL) return LG_ATTN_EINVAL;
         int flags = 0;
         if (base * splits <= 2LL * g_sm_count[device]) flags |= w8::kFlagEarlyTrigger;
         cfg.gridDim = dim3(static_cast<unsigned>(base) * static_cast<unsigned>(splits));
-        cfg.blockDim = dim3(w8::kThreads);
-        cfg.dynamicSmemBytes = w8::kSmemBytes + (splits > 1 ? w8::kSmemSplitExtra : 0);
+        cfg.blockDim = dim3(in_f32 ? w8::kThreadsF32 : w8::kThreads);
+        cfg.dynamicSmemBytes = in_f32 ? w8::kSmemBytesF32 : w8::kSmemBytes + (splits > 1 ? w8::kSmemSplitExtra : 0);
         if (splits > 1) {
             attrs[n_attrs].id = cudaLaunchAttributeClusterDimension;
             attrs[n_attrs].val.clusterDim.x = static_cast<unsigned>(splits);
@@ -328,7 +364,10 @@ static int launch_core(const void* qh, const void* kh, const void* vh, void* o, 
         cfg.attrs = attrs;
         cfg.numAttrs = n_attrs;
         const bool f32 = out_f32;
-        if (splits > 1) {
+        if (in_f32) {
+            e = cudaLaunchKernelEx(&cfg, w8::lg_attn_hd64_fwd<true, true, true>, tm_q, tm_k, tm_v, o, n_q, n_kv, tiles_m, splits, flags,
+                                   ol LG_TRACE_SEQ);
+        } else if (splits > 1) {
             e = cudaLaunchKernelEx(&cfg, f32 ? w8::lg_attn_hd64_fwd<true, true> : w8::lg_attn_hd64_fwd<false, true>, tm_q, tm_k,
                                    tm_v, o, n_q, n_kv, tiles_m, splits, flags, ol LG_TRACE_SEQ);
         } else {
@@ -420,15 +459,13 @@ int lg_attn_hd64_init_device(int device) {
 }
 
 size_t lg_attn_hd64_workspace_bytes(int batch, int heads, int n_q, int n_kv, int io_dtype) {
-    if (batch <= 0 || heads <= 0 || n_q <= 0 || n_kv <= 0 || !valid_dtype(io_dtype)) return 0;
-    if (io_dtype != LG_ATTN_F32_F32) return 0;
-    const size_t bh = static_cast<size_t>(batch) * heads;
-    return align256(bh * n_q * kHeadDim * 2) + 2 * align256(bh * n_kv * kHeadDim * 2);
+    (void)batch; (void)heads; (void)n_q; (void)n_kv; (void)io_dtype;
+    return 0;   // every mode is one launch without scratch (the kFLOAT conversion happens on the way into shared memory)
 }
 
 int lg_attn_hd64_launches_per_call(int io_dtype) {
     if (!valid_dtype(io_dtype)) return 0;
-    return io_dtype == LG_ATTN_F32_F32 ? 2 : 1;
+    return 1;
 }
 
 int lg_attn_hd64_launch(const void* q, const void* k, const void* v, void* o, int batch, int heads,
@@ -452,43 +489,12 @@ int lg_attn_hd64_launch(const void* q, const void* k, const void* v, void* o, in
     const void* kh = k;
     const void* vh = v;
 
-    if (io_dtype == LG_ATTN_F32_F32) {
-        const size_t need = lg_attn_hd64_workspace_bytes(batch, heads, n_q, n_kv, io_dtype);
-        if (workspace == nullptr || workspace_bytes < need) return LG_ATTN_EWORKSPACE;
-        const size_t q_bytes = align256(static_cast<size_t>(bh) * n_q * kHeadDim * 2);
-        const size_t kv_bytes = align256(static_cast<size_t>(bh) * n_kv * kHeadDim * 2);
-        uint8_t* ws = static_cast<uint8_t*>(workspace);
-        uint4* qd = reinterpret_cast<uint4*>(ws);
-        uint4* kd = reinterpret_cast<uint4*>(ws + q_bytes);
-        uint4* vd = reinterpret_cast<uint4*>(ws + q_bytes + kv_bytes);
-        const size_t nq8 = static_cast<size_t>(bh) * n_q * (kHeadDim / 8);
-        const size_t nkv8 = static_cast<size_t>(bh) * n_kv * (kHeadDim / 8);
-        const size_t total = nq8 + 2 * nkv8;
-        size_t blocks = (total + 255) / 256;
-        const size_t cap = static_cast<size_t>(g_sm_count[device]) * 16;   // grid-stride beyond 16 CTAs per SM
-        if (blocks > cap) blocks = cap;
-        cudaLaunchConfig_t ccfg = {};
-        ccfg.gridDim = dim3(static_cast<unsigned>(blocks));
-        ccfg.blockDim = dim3(256);
-        ccfg.stream = stream;
-        cudaLaunchAttribute cattr[1];
-        cattr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-        cattr[0].val.programmaticStreamSerializationAllowed = 1;
-        ccfg.attrs = cattr;
-        ccfg.numAttrs = g_use_pdl.load(std::memory_order_relaxed) ? 1 : 0;
-        e = cudaLaunchKernelEx(&ccfg, lg_attn_cvt_f32_f16, static_cast<const float4*>(q), static_cast<const float4*>(k),
-                               static_cast<const float4*>(v), qd, kd, vd, nq8, nkv8);
-        if (e != cudaSuccess) return static_cast<int>(e);
-        e = cudaGetLastError();
-        if (e != cudaSuccess) return static_cast<int>(e);
-        qh = qd;
-        kh = kd;
-        vh = vd;
-    }
-
+    (void)workspace;        // kept in the signature for ABI stability; no mode needs scratch any more
+    (void)workspace_bytes;
+    (void)bh;
     const RowStrides cq = contiguous_strides(heads, n_q), ckv = contiguous_strides(heads, n_kv);
     return launch_core(qh, kh, vh, o, batch, heads, n_q, n_kv, io_dtype != LG_ATTN_F16_F16, cq, ckv, ckv, cq, 0, device,
-                       stream);
+                       stream, io_dtype == LG_ATTN_F32_F32);
 }
 
 int lg_attn_hd64_launch_strided(const void* q, const void* k, const void* v, void* o, int batch, int heads,

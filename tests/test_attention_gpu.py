@@ -239,13 +239,46 @@ def test_host_buffer_entry(pkg):
     assert orc.rel_err(of, orc.attention_np(q, k, v)) <= orc.TOL_F32_REL
 
 
-def test_workspace_error_is_reported_not_fatal(pkg):
+def test_kfloat_branch_is_one_launch_without_workspace(pkg):
+    """Row a6: the plugin's kFLOAT branch (FP32 tensors at the boundary) runs as ONE launch with no scratch — the FP32 -> FP16
+    conversion (round to nearest, like QKV_convert_from_fp32_to_fp16, …fp32out.cu:706-768) happens on the way into shared memory.
+    A null workspace is fine, and the result equals the FP16-in / FP32-out launch on the pre-rounded inputs bit for bit."""
     lib = pkg.load()
-    q = torch.zeros(1, 4, 64, 64, device=DEV)
-    o = torch.empty_like(q)
-    rc = lib.lg_attn_hd64_launch(q.data_ptr(), q.data_ptr(), q.data_ptr(), o.data_ptr(), 1, 4, 64, 64, pkg.F32_F32,
-                                 None, 0, None)
-    assert rc == pkg._binding.EWORKSPACE
+    assert lib.lg_attn_hd64_workspace_bytes(1, 4, 1024, 1024, pkg.F32_F32) == 0
+    assert lib.lg_attn_hd64_launches_per_call(pkg.F32_F32) == 1
+    g = torch.Generator(device=DEV).manual_seed(3)
+    for (b, n, m) in [(1, 1024, 1024), (1, 777, 1000), (1, 64, 1), (2, 300, 513), (1, 2048, 2048), (3, 130, 700)]:
+        q = torch.randn(b, 4, n, 64, device=DEV, generator=g) * 1.7
+        k = torch.randn(b, 4, m, 64, device=DEV, generator=g)
+        v = torch.randn(b, 4, m, 64, device=DEV, generator=g)
+        pad = 1024
+        buf = torch.full((b * 4 * n * 64 + pad,), -77.0, device=DEV)
+        o = buf[: b * 4 * n * 64].view(b, 4, n, 64)
+        rc = lib.lg_attn_hd64_launch(q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), b, 4, n, m, pkg.F32_F32, None, 0,
+                                     torch.cuda.current_stream().cuda_stream)
+        assert rc == 0
+        assert (buf[b * 4 * n * 64:] == -77.0).all()
+        want = pkg.attention(q.half(), k.half(), v.half(), out_dtype=torch.float32)
+        assert torch.equal(o, want), (b, n, m)
+        ref = orc.attention_np(q.half().cpu().numpy(), k.half().cpu().numpy(), v.half().cpu().numpy())
+        assert orc.rel_err(o.cpu().numpy(), ref) <= orc.TOL_F32_REL
+
+
+def test_kfloat_branch_on_a_full_grid_and_with_overflowing_inputs(pkg):
+    """FP32 inputs on a grid that fills the GPU (the latency kernel's FP32-input instantiation takes every kFLOAT shape), and
+    values beyond the FP16 range: they become +-inf like __float2half_rn in the reference's converter, not garbage."""
+    g = torch.Generator(device=DEV).manual_seed(4)
+    b, n, m = 90, 300, 260
+    q, k, v = (torch.randn(b, 4, r, 64, device=DEV, generator=g) for r in (n, m, m))
+    o = pkg.attention(q, k, v)
+    assert o.dtype == torch.float32
+    for bi in (0, 44, b - 1):
+        ref = orc.attention_np(*(t[bi:bi + 1].half().cpu().numpy() for t in (q, k, v)))
+        assert orc.rel_err(o[bi:bi + 1].cpu().numpy(), ref) <= orc.TOL_F32_REL
+    v2 = v[:1].clone()
+    v2[0, 0, 5, 7] = 1e6          # > 65504: +inf in FP16
+    o2 = pkg.attention(q[:1], k[:1], v2)
+    assert torch.isinf(o2[0, 0, :, 7]).all() and torch.isfinite(o2[0, 1]).all()
 
 
 def test_against_recompiled_reference_kernels(pkg):
