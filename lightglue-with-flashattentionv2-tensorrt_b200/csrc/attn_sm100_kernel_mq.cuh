@@ -55,6 +55,9 @@
 #ifndef LG_ATTN_MQ_MMA_SPIN_NS
 #define LG_ATTN_MQ_MMA_SPIN_NS 0   // poll interval of the MMA issuer (0: tight try_wait loop; its waits are on every tile's critical chain)
 #endif
+#ifndef LG_ATTN_MQ_FIRST_READY
+#define LG_ATTN_MQ_FIRST_READY 0   // 1: MMA warps with two tiles serve the tile whose P is ready first (measured slower: 869 vs 899 TFLOP/s)
+#endif
 #ifndef LG_ATTN_MQ_STAGGER_NS
 #define LG_ATTN_MQ_STAGGER_NS 0
 #endif
@@ -315,8 +318,21 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
                     if (!kAlias && more) qk_all(g + 1, it, false, j + 2 == nkv);
                     mma_wait(ubar(C::kBarVFull + g % C::kStages), (g / C::kStages) & 1);
                     if (kAlias && more) wait_k(g + 1);
+                    // Service order inside a step: with two tiles per MMA warp, whichever tile's P arrives first is served first
+                    // (a fixed order makes the earlier tile queue behind the later one: ~230 clk per step in the phase trace)
+                    int swap = 0;
+                    if (LG_ATTN_MQ_FIRST_READY && kTilesPerWarp == 2) {
+                        const uint32_t par = static_cast<uint32_t>(g & 1);
+                        while (true) {
+                            if (mbar_test_wait(ubar(C::kBarPFull + t_begin), par)) break;
+                            if (mbar_test_wait(ubar(C::kBarPFull + t_begin + 1), par)) { swap = 1; break; }
+                        }
+                        swap = __shfl_sync(0xffffffffu, swap, 0);   // one decision for the warp (probes of different lanes may differ)
+                    }
 #pragma unroll 1
-                    for (int t = t_begin; t < t_end; ++t) {
+                    for (int ti = 0; ti < kTilesPerWarp; ++ti) {
+                        const int t = t_begin + (swap ? kTilesPerWarp - 1 - ti : ti);
+                        const bool last_tile = ti == kTilesPerWarp - 1;
                         mma_wait(ubar(C::kBarPFull + t), g & 1);
                         MQ_TRACE(lane == 0, g, t, 5);
                         if (j == 0 && it > 0) mma_wait(ubar(C::kBarOEmpty + t), (it - 1) & 1);  // epilogue has read O
@@ -325,7 +341,7 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
                         if (elect_one()) {
                             issue_pv(t, g, j > 0);
                             mma_commit(ubar(C::kBarPVDone + t));
-                            if (t == t_end - 1) mma_commit(ubar(C::kBarVEmpty + g % C::kStages));
+                            if (last_tile) mma_commit(ubar(C::kBarVEmpty + g % C::kStages));
                         }
                         __syncwarp();
                         if (kAlias && more) {
@@ -335,7 +351,7 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
                                 issue_qk(t, g + 1);
                                 if (j + 2 == nkv) mma_commit(ubar(C::kBarQEmpty + t));
                                 mma_commit(ubar(C::kBarSFull + t));
-                                if (t == t_end - 1) mma_commit(ubar(C::kBarKEmpty + (g + 1) % C::kStages));
+                                if (last_tile) mma_commit(ubar(C::kBarKEmpty + (g + 1) % C::kStages));
                             }
                             __syncwarp();
                         }
@@ -343,12 +359,12 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
                         if (elect_one()) {
                             issue_pv(t, g, j > 0);
                             if (!kAlias || !more) mma_commit(ubar(C::kBarPVDone + t));   // alias: only the epilogue waits for it
-                            if (t == t_end - 1) mma_commit(ubar(C::kBarVEmpty + g % C::kStages));
+                            if (last_tile) mma_commit(ubar(C::kBarVEmpty + g % C::kStages));
                             if (kAlias && more) {
                                 issue_qk(t, g + 1);   // after PV_t(g) in the pipe: may overwrite P_t(g)
                                 if (j + 2 == nkv) mma_commit(ubar(C::kBarQEmpty + t));
                                 mma_commit(ubar(C::kBarSFull + t));
-                                if (t == t_end - 1) mma_commit(ubar(C::kBarKEmpty + (g + 1) % C::kStages));
+                                if (last_tile) mma_commit(ubar(C::kBarKEmpty + (g + 1) % C::kStages));
                             }
                         }
                         __syncwarp();
