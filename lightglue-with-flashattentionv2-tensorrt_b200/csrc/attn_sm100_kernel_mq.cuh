@@ -265,8 +265,10 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
             if (warp > kWarpMMA) __nanosleep(LG_ATTN_MQ_STAGGER_NS * (warp - kWarpMMA));
 #endif
 
+            bool skip_qk = false;
             // (elected lane) S_t = Q_t K(g)^T.  The caller has made sure K(g) has landed and S_t may be overwritten.
             auto issue_qk = [&](int t, int g) {
+                if (skip_qk) return;
                 const int s = g % C::kStages;
                 const uint64_t desc_q = make_smem_desc_sw128(smem_u + C::kSmemQ + t * C::kQBytes, 16, 1024);
                 const uint64_t desc_k = make_smem_desc_sw128(smem_u + C::kSmemK + s * C::kKVBytes, 16, 1024);
@@ -312,6 +314,12 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
 
             int g = 0;
             for (int it = 0; it < n_work; ++it) {
+#ifdef LG_ATTN_WHATIF_F3
+                // what-if build (WRONG results, timing only; tools/f3_whatif.py): row f3 of SURVEY section 8 — with both cross-attention
+                // directions in one launch (kv_shift), the second direction could reuse S(0->1)^T instead of computing its own
+                // Q K^T.  This drops the second direction's QK MMAs (commits stay) to bound what that could gain.
+                skip_qk = ol.kv_shift > 0 && item_coord(first + it * stride, groups, kT, ol).bi >= ol.batch / 2;
+#endif
                 qk_all(g, it, true, nkv == 1);
                 for (int j = 0; j < nkv; ++j, ++g) {
                     const bool more = j + 1 < nkv;

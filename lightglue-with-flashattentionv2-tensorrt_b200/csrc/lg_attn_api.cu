@@ -388,7 +388,7 @@ int lg_attn_build_flags(void) {
 #ifdef LG_ATTN_TUNING_BUILD
     f |= 1;
 #endif
-#ifdef LG_ATTN_WHATIF
+#if defined(LG_ATTN_WHATIF) || defined(LG_ATTN_WHATIF_F3)
     f |= 2;
 #endif
 #ifdef LG_ATTN_EXPERIMENT_NOSUM

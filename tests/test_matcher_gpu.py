@@ -240,11 +240,15 @@ def test_assignment_survives_nan_and_inf_rows(pkg):
     assert int(m0[0, 7]) == -1 and int(m0[1, 100]) == -1
     assert float(ms[1, 100]) == 0.0
     assert ((m0.cpu() >= -1) & (m0.cpu() < n1)).all()
-    # a -inf row adds exp(-inf) = 0 to every column's log-sum-exp: rows of that pair that had a mutual match keep it, score included
-    had = clean[0][1].cpu() >= 0
-    had[100] = False
-    assert torch.equal(m0[1].cpu()[had], clean[0][1].cpu()[had])
-    torch.testing.assert_close(ms[1].cpu()[had], clean[1][1].cpu()[had], rtol=1e-5, atol=1e-30)
+    # a -inf row adds exp(-inf) = 0 to every column's log-sum-exp and can win no column: the other rows of that pair must come
+    # out exactly as if the row did not exist
+    keep = torch.ones(n0, dtype=torch.bool)
+    keep[100] = False
+    w0, ws, _ = pkg.matcher.assign(bad[1:2, keep].contiguous().to(DEV), z0[1:2, keep].contiguous().to(DEV), z1[1:2].to(DEV), 0.0)
+    assert torch.equal(m0[1].cpu()[keep], w0[0].cpu())
+    torch.testing.assert_close(ms[1].cpu()[keep], ws[0].cpu(), rtol=1e-5, atol=1e-30)
+    assert torch.isfinite(ms[1]).all()
+    del clean
 
 
 def test_plan_caches_are_bounded_and_alternating_shapes_do_not_replan(pkg):
