@@ -127,14 +127,38 @@ struct Cfg {
     static constexpr int kRegsSoftmax = kRegsSoftmaxMax > 232 ? 232 : kRegsSoftmaxMax;
 };
 
-struct Item {
-    int tile_m0, hi, bi, bk;
+// Work items.  A full item = kT consecutive Q tiles of one (batch, head) ("group").  The persistent grid walks the items
+// blockIdx.x + i * gridDim.x, so when the number of groups is not a multiple of the grid the last wave would leave most SMs idle
+// for a whole item time (B16 N4096: 512 groups on 148 SMs = 3.46 waves).  The host therefore cuts the groups of that last partial
+// wave into `parts` smaller items (kT / parts tiles each): more CTAs busy, each for a shorter time.  Tiles of an item past its
+// n_active (split items, and groups that stick out past the last Q tile) take part in every barrier handshake but issue no
+// loads, MMAs, arithmetic or stores.
+struct Sched {
+    int groups;       // groups per (batch, head) = ceil(tiles_m / kT)
+    int tiles_m;      // Q tiles per (batch, head)
+    int n_full;       // items [0, n_full) are whole groups
+    int parts;        // items >= n_full: group n_full + (w - n_full) / parts, part (w - n_full) % parts
+    int total_items;
 };
 
-__device__ __forceinline__ Item item_coord(int w, int groups, int tiles_per_item, const OutLayout& ol) {
+struct Item {
+    int tile_m0, n_active, hi, bi, bk;
+};
+
+template <int kT>
+__device__ __forceinline__ Item item_coord(int w, const Sched& sc, const OutLayout& ol) {
     Item c;
-    c.tile_m0 = (w % groups) * tiles_per_item;
-    const int bh = w / groups;
+    int grp = w, off = 0, cnt = kT;
+    if (w >= sc.n_full) {
+        const int idx = w - sc.n_full;
+        grp = sc.n_full + idx / sc.parts;
+        cnt = kT / sc.parts;
+        off = (idx % sc.parts) * cnt;
+    }
+    c.tile_m0 = (grp % sc.groups) * kT + off;
+    const int left = sc.tiles_m - c.tile_m0;
+    c.n_active = left < cnt ? (left < 0 ? 0 : left) : cnt;
+    const int bh = grp / sc.groups;
     c.hi = bh % ol.heads;
     c.bi = bh / ol.heads;
     c.bk = c.bi + ol.kv_shift >= ol.batch ? c.bi + ol.kv_shift - ol.batch : c.bi + ol.kv_shift;
@@ -144,8 +168,8 @@ __device__ __forceinline__ Item item_coord(int w, int groups, int tiles_per_item
 template <int kT, int kBN, bool kAlias, bool kLazyMax, bool kOutF32>
 __global__ void __launch_bounds__(Cfg<kT, kBN, kAlias>::kThreads, 1)
 lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
-                 const __grid_constant__ CUtensorMap tm_v, void* __restrict__ out, int n_q, int n_kv, int groups,
-                 int total_items, const OutLayout ol) {
+                 const __grid_constant__ CUtensorMap tm_v, void* __restrict__ out, int n_q, int n_kv, const Sched sc,
+                 const OutLayout ol) {
     using C = Cfg<kT, kBN, kAlias>;
     static_assert(!kLazyMax || kAlias, "the lazy row max re-reads S from TMEM: S must survive until P is stored");
     extern __shared__ uint8_t smem_raw[];
@@ -158,6 +182,7 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
     const int lane = threadIdx.x & 31;
     const int nkv = (n_kv + kBN - 1) / kBN;
     const int first = blockIdx.x, stride = gridDim.x;
+    const int total_items = sc.total_items;
     constexpr int kWarpKV = C::kSoftmaxWarps, kWarpQ = kWarpKV + 1, kWarpAlloc = kWarpQ, kWarpMMA = kWarpKV + 2;
 
     if (warp == kWarpKV && lane == 0) {
@@ -208,13 +233,17 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
             // ===================================================================== Q producer
             int it = 0;
             for (int w = first; w < total_items; w += stride, ++it) {
-                const Item c = item_coord(w, groups, kT, ol);
+                const Item c = item_coord<kT>(w, sc, ol);
 #pragma unroll 1
                 for (int t = 0; t < kT; ++t) {
                     if (it > 0) mbar_wait_backoff(ubar(C::kBarQEmpty + t), (it - 1) & 1, LG_ATTN_SPIN_NS);  // last QK of the previous item done
                     if (elect_one()) {
-                        mbar_arrive_expect_tx(ubar(C::kBarQFull + t), C::kQBytes);
-                        tma_load_4d(smem_u + C::kSmemQ + t * C::kQBytes, &tm_q, ubar(C::kBarQFull + t), 0, (c.tile_m0 + t) * kBlockM, c.hi, c.bi);
+                        if (t < c.n_active) {
+                            mbar_arrive_expect_tx(ubar(C::kBarQFull + t), C::kQBytes);
+                            tma_load_4d(smem_u + C::kSmemQ + t * C::kQBytes, &tm_q, ubar(C::kBarQFull + t), 0, (c.tile_m0 + t) * kBlockM, c.hi, c.bi);
+                        } else {
+                            mbar_arrive(ubar(C::kBarQFull + t));   // idle tile of this item: nothing to load, the phase still turns
+                        }
                     }
                     __syncwarp();
                 }
@@ -241,7 +270,7 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
                 __syncwarp();
             };
             for (int w = first; w < total_items; w += stride) {
-                const Item c = item_coord(w, groups, kT, ol);
+                const Item c = item_coord<kT>(w, sc, ol);
                 for (int j = 0; j < nkv; ++j, ++g) {
                     if (j == 0) load_k(g, 0, c);
                     if (j + 1 < nkv) load_k(g + 1, j + 1, c);
@@ -266,9 +295,10 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
 #endif
 
             bool skip_qk = false;
+            int n_active = kT;   // of the item being issued (tiles >= n_active only exchange barrier arrivals)
             // (elected lane) S_t = Q_t K(g)^T.  The caller has made sure K(g) has landed and S_t may be overwritten.
             auto issue_qk = [&](int t, int g) {
-                if (skip_qk) return;
+                if (skip_qk || t >= n_active) return;
                 const int s = g % C::kStages;
                 const uint64_t desc_q = make_smem_desc_sw128(smem_u + C::kSmemQ + t * C::kQBytes, 16, 1024);
                 const uint64_t desc_k = make_smem_desc_sw128(smem_u + C::kSmemK + s * C::kKVBytes, 16, 1024);
@@ -279,6 +309,7 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
             };
             // (elected lane) O_t (+)= P_t V(g): A = P from TMEM (8 columns per 16 kv rows), B = V MN-major (16 kv rows = 2048 B per k-step)
             auto issue_pv = [&](int t, int g, bool accumulate) {
+                if (t >= n_active) return;
                 const int s = g % C::kStages;
                 const uint64_t desc_v = make_smem_desc_sw128(smem_u + C::kSmemV + s * C::kKVBytes, C::kKVBytes, 1024);
                 const uint32_t t_o = tmem_u + t * C::kTileCols + C::kColO;
@@ -314,11 +345,12 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
 
             int g = 0;
             for (int it = 0; it < n_work; ++it) {
+                n_active = item_coord<kT>(first + it * stride, sc, ol).n_active;
 #ifdef LG_ATTN_WHATIF_F3
                 // what-if build (WRONG results, timing only; tools/f3_whatif.py): row f3 of SURVEY section 8 — with both cross-attention
                 // directions in one launch (kv_shift), the second direction could reuse S(0->1)^T instead of computing its own
                 // Q K^T.  This drops the second direction's QK MMAs (commits stay) to bound what that could gain.
-                skip_qk = ol.kv_shift > 0 && item_coord(first + it * stride, groups, kT, ol).bi >= ol.batch / 2;
+                skip_qk = ol.kv_shift > 0 && item_coord<kT>(first + it * stride, sc, ol).bi >= ol.batch / 2;
 #endif
                 qk_all(g, it, true, nkv == 1);
                 for (int j = 0; j < nkv; ++j, ++g) {
@@ -396,7 +428,7 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
 
         int g = 0, it = 0;
         for (int w = first; w < total_items; w += stride, ++it) {
-            const Item c = item_coord(w, groups, kT, ol);
+            const Item c = item_coord<kT>(w, sc, ol);
             float m_used = -INFINITY;            // row max the exponent is referenced to (raw score units)
             float m_thr = INFINITY, neg_m = 0.f; // rescale threshold m_used + tau/c, and -m_used*c
             float l_sum = 0.f;
@@ -409,6 +441,17 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
                     tc_fence_after();
                 }
                 MQ_TRACE((warp & 3) == 0 && lane == 0, g, tile, 1);
+                if (tile >= c.n_active) {
+                    // idle tile of this item: keep every barrier phase turning (the MMA warp commits without issuing), nothing else
+                    __syncwarp();
+                    if (!kAlias) {
+                        if (lane == 0) mbar_arrive(bar_s_empty);
+                        if (j + 1 < nkv) mbar_wait(bar_s_full, (g + 1) & 1);
+                        else if (j > 0) mbar_wait(bar_pv_done, (g - 1) & 1);
+                    }
+                    if (lane == 0) mbar_arrive(bar_p_full);
+                    continue;
+                }
                 const int valid = kv_left;
                 kv_left -= kBN;
 
@@ -501,6 +544,11 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
             // --------------------------------------------------------------------------- epilogue
             mbar_wait(bar_pv_done, (kAlias && !LG_ATTN_MQ_STRICT_ORDER ? it : g - 1) & 1);
             tc_fence_after();
+            if (tile >= c.n_active) {
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar_o_empty);
+                continue;
+            }
             uint32_t orow[kHeadDim];
             tmem_ld_x32(t_o, orow);
             tmem_ld_x32(t_o + 32u, orow + 32);

@@ -69,21 +69,48 @@ constexpr int kMqVariants = 5;
 constexpr int kMqVariants = 2;
 #endif
 
+// How the multi-Q-tile kernel cuts a launch into work items (mq::Sched): whole groups of t Q tiles for every full wave of the
+// persistent grid; the groups of a last partial wave that fills <= 1/2 (1/4) of the SMs are cut into 2 (4) smaller items.
+mq::Sched mq_schedule(long long bh, long long tiles_m, int t, int sms) {
+    mq::Sched sc;
+    sc.groups = static_cast<int>((tiles_m + t - 1) / t);
+    sc.tiles_m = static_cast<int>(tiles_m);
+    const long long g = bh * sc.groups;
+    const long long rem = g % sms;
+    int parts = 1;
+    if (g > sms && rem > 0) {
+        if (4 * rem <= sms && t % 4 == 0) parts = 4;
+        else if (2 * rem <= sms && t % 2 == 0) parts = 2;
+    }
+    sc.parts = parts;
+    sc.n_full = static_cast<int>(parts > 1 ? g - rem : g);
+    sc.total_items = static_cast<int>(parts > 1 ? g - rem + rem * parts : g);
+    return sc;
+}
+
+// Relative time of a launch under that schedule, in units of one full item: full waves + the last (possibly split) wave.  An item
+// of t / parts tiles is cheaper than a full one, but not proportionally (fewer tiles hide less latency): measured about 0.65 / 0.50 of a
+// full item for 1/2 and 1/4 of the tiles (B16 N4096: 818 -> 930 TFLOP/s with the last wave cut in two).
+double mq_cost(long long bh, long long tiles_m, int t, int sms) {
+    const mq::Sched sc = mq_schedule(bh, tiles_m, t, sms);
+    const long long g = bh * sc.groups;
+    const double tail = sc.parts == 4 ? 0.50 : (sc.parts == 2 ? 0.65 : 1.0);
+    const long long full_waves = sc.parts > 1 ? sc.n_full / sms : (g + sms - 1) / sms;
+    return static_cast<double>(full_waves) + (sc.parts > 1 ? tail : 0.0);
+}
+
 // Which full-grid kernel is expected to finish first.  Relative speeds are same-box medians on square shapes (B200, round 2:
-// mq4 1.00, mq2 0.93, w4 0.85); each is discounted by how well the launch packs: Q tiles wasted inside partly filled work
-// items, and the last wave of the (persistent or not) grid.
+// mq4 1.00, mq2 0.90, w4 0.85 per unit of work); each is charged for how the launch packs: idle Q-tile slots inside partly filled
+// groups, and the last wave of the (persistent or not) grid.
 int choose_full_grid_kernel(long long bh, long long tiles_m, int sms) {
-    auto wave_eff = [&](long long units, long long slots) {
-        const long long waves = (units + slots - 1) / slots;
-        return static_cast<double>(units) / static_cast<double>(waves * slots);
-    };
-    auto mq_eff = [&](int t) {
-        const long long groups = (tiles_m + t - 1) / t;
-        return static_cast<double>(tiles_m) / static_cast<double>(groups * t) * wave_eff(bh * groups, sms);
-    };
-    const double s_w4 = 0.85 * wave_eff(bh * tiles_m, 2LL * sms), s_mq4 = 1.00 * mq_eff(4), s_mq2 = 0.93 * mq_eff(2);
-    if (s_mq4 >= s_mq2 && s_mq4 >= s_w4) return 1;
-    return s_mq2 >= s_w4 ? 2 : 0;
+    const double work = static_cast<double>(bh * tiles_m);                       // Q tiles
+    const long long waves_w4 = (bh * tiles_m + 2LL * sms - 1) / (2LL * sms);
+    const double t_w4 = static_cast<double>(waves_w4) * 2.0 * sms / 0.85;      // tile-times on the whole chip
+    const double t_mq4 = mq_cost(bh, tiles_m, 4, sms) * 4.0 * sms / 1.00;
+    const double t_mq2 = mq_cost(bh, tiles_m, 2, sms) * 2.0 * sms / 0.90;
+    (void)work;
+    if (t_mq4 <= t_mq2 && t_mq4 <= t_w4) return 1;
+    return t_mq2 <= t_w4 ? 2 : 0;
 }
 
 int resolve_encode() {
@@ -310,8 +337,8 @@ static int launch_core(const void* qh, const void* kh, const void* vh, void* o, 
                 if ((rc = encode_rows_map(&tm_k, kh, n_kv, heads, batch, sk, V::kBN)) != 0) return;
                 if ((rc = encode_rows_map(&tm_v, vh, n_kv, heads, batch, sv, V::kBN)) != 0) return;
             }
-            const long long groups = (tiles_m_ll + V::kT - 1) / V::kT;
-            const long long items = bh_ll * groups;
+            const mq::Sched sc = mq_schedule(bh_ll, tiles_m_ll, V::kT, g_sm_count[device]);
+            const long long items = sc.total_items;
             cfg.gridDim = dim3(static_cast<unsigned>(items < g_sm_count[device] ? items : g_sm_count[device]));
             cfg.blockDim = dim3(V::C::kThreads);
             cfg.dynamicSmemBytes = V::C::kSmemBytes;
@@ -320,7 +347,7 @@ static int launch_core(const void* qh, const void* kh, const void* vh, void* o, 
             e = cudaLaunchKernelEx(&cfg,
                                    !out_f32 ? mq::lg_attn_hd64_fwd<V::kT, V::kBN, V::kAlias, V::kLazy, false>
                                             : mq::lg_attn_hd64_fwd<V::kT, V::kBN, V::kAlias, V::kLazy, true>,
-                                   tm_q, tm_k, tm_v, o, n_q, n_kv, static_cast<int>(groups), static_cast<int>(items), ol);
+                                   tm_q, tm_k, tm_v, o, n_q, n_kv, sc, ol);
         });
         if (rc != 0) return rc;
     } else if (full_grid) {
@@ -429,9 +456,11 @@ int lg_attn_debug_describe_launch(int batch, int heads, int n_q, int n_kv, char*
             snprintf(buf, buf_bytes, "lgattn::w4 (one 128-row Q tile per CTA, 2 CTAs/SM), grid %lld", base);
         } else {
             const int t = k == 1 ? 4 : 2;
-            const long long items = bh * ((tiles_m + t - 1) / t);
-            snprintf(buf, buf_bytes, "lgattn::mq<%d Q tiles, %d-row KV steps> (persistent, 1 CTA/SM), grid %lld over %lld work items",
-                     t, k == 1 ? 64 : 128, items < sms ? items : static_cast<long long>(sms), items);
+            const mq::Sched sc = mq_schedule(bh, tiles_m, t, sms);
+            const long long items = sc.total_items;
+            snprintf(buf, buf_bytes,
+                     "lgattn::mq<%d Q tiles, %d-row KV steps> (persistent, 1 CTA/SM), grid %lld over %lld work items (last wave cut in %d)",
+                     t, k == 1 ? 64 : 128, items < sms ? items : static_cast<long long>(sms), items, sc.parts);
         }
     } else {
         int splits = 1;

@@ -376,7 +376,9 @@ def test_strided_kv_batch_shift_is_cross_attention_in_one_launch(pkg, b2, n):
 # step per Q tile (first QK is also the last), ragged N and M, partly filled work items (Q-tile counts that are no multiple of
 # 2 / 4: the spare tiles compute on TMA zero fill and must not store), items of different (batch, head) in one CTA.
 FULL_GRID = [(100, 100, 1), (80, 128, 128), (75, 129, 129), (40, 256, 250), (80, 777, 1000), (40, 300, 2047), (10, 1024, 1153),
-             (90, 513, 64), (30, 640, 65), (24, 1100, 300)]
+             (90, 513, 64), (30, 640, 65), (24, 1100, 300),
+             # 160 / 216 four-tile groups on 148 SMs: the last partial wave is cut into quarter / half items (mq::Sched)
+             (10, 2048, 300), (27, 1000, 200)]
 FULL_GRID_KERNELS = [0, 1, 2]
 
 
