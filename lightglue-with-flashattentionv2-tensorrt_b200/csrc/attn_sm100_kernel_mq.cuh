@@ -495,7 +495,24 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
                         }
                     }
                     // P = exp2(s*c - m*c) as packed FP16 pairs + the FP32 row sum (softmax_math.cuh)
+#if defined(LG_ATTN_WHATIF) && LG_ATTN_WHATIF >= 2
+                    // what-if builds (WRONG results, timing decomposition only; LG_ATTN_TUNING_BUILD): 2 = no exponentials (one FFMA2 +
+                    // pack per pair), 3 = no arithmetic at all ("skeleton": S load, P store, barriers, MMAs)
+#pragma unroll
+                    for (int cc = 0; cc < kBN; cc += 2) {
+#if LG_ATTN_WHATIF == 2
+                        float x0, x1;
+                        unpack_f32x2(fma_f32x2(pack_f32x2(__uint_as_float(sr[cc]), __uint_as_float(sr[cc + 1])),
+                                               pack_f32x2(kScaleLog2, kScaleLog2), pack_f32x2(neg_m, neg_m)), x0, x1);
+                        pk[cc / 2] = pack_half2(x0, x1);
+#else
+                        pk[cc / 2] = sr[cc] ^ sr[cc + 1];
+#endif
+                    }
+                    tile_sum = 1.0f;
+#else
                     tile_sum = softmax_exp_pass<kBN>(sr, pk, neg_m);
+#endif
                     if (kLazyMax && !need_max) {
                         // a probability >= 2^tau (the polynomial path saturates exactly there) shows in the row sum: the stale
                         // reference is too small for this step -> redo it with the true row max (S is intact: P not stored yet)
