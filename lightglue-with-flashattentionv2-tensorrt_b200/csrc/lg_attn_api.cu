@@ -88,27 +88,50 @@ mq::Sched mq_schedule(long long bh, long long tiles_m, int t, int sms) {
     return sc;
 }
 
-// Relative time of a launch under that schedule, in units of one full item: full waves + the last (possibly split) wave.  An item
-// of t / parts tiles is cheaper than a full one, but not proportionally (fewer tiles hide less latency): measured about 0.65 / 0.50 of a
-// full item for 1/2 and 1/4 of the tiles (B16 N4096: 818 -> 930 TFLOP/s with the last wave cut in two).
-double mq_cost(long long bh, long long tiles_m, int t, int sms) {
+// Relative time of an mq launch under that schedule, in units of one full 4-tile item of the 4-tile layout.  An item with fewer
+// active tiles is cheaper, but not proportionally (fewer tiles hide less of each other's latency): about 0.85 / 0.65 / 0.50 of a
+// full item for 3 / 2 / 1 of 4 tiles (B16 N4096: 818 -> 930 TFLOP/s with the last wave cut in two); the 2-tile layout's full
+// item costs 2/4 / 0.90.  The grid walks items blockIdx.x + i * gridDim.x, so the launch takes as long as its busiest CTA: summed
+// per CTA here exactly as the device decodes the items (a few thousand additions; beyond 64 items per CTA the average is exact
+// enough).
+double mq_time(long long bh, long long tiles_m, int t, int sms) {
+    static const double kCost4[5] = {0.10, 0.50, 0.65, 0.85, 1.00};   // by active tiles, 4-tile layout
+    static const double kCost2[3] = {0.06, 0.36, 0.556};              // 2-tile layout, same unit
     const mq::Sched sc = mq_schedule(bh, tiles_m, t, sms);
-    const long long g = bh * sc.groups;
-    const double tail = sc.parts == 4 ? 0.50 : (sc.parts == 2 ? 0.65 : 1.0);
-    const long long full_waves = sc.parts > 1 ? sc.n_full / sms : (g + sms - 1) / sms;
-    return static_cast<double>(full_waves) + (sc.parts > 1 ? tail : 0.0);
+    auto item_cost = [&](long long w) {
+        long long grp = w;
+        int off = 0, cnt = t;
+        if (w >= sc.n_full) {
+            const long long idx = w - sc.n_full;
+            grp = sc.n_full + idx / sc.parts;
+            cnt = t / sc.parts;
+            off = static_cast<int>(idx % sc.parts) * cnt;
+        }
+        const long long left = tiles_m - ((grp % sc.groups) * t + off);
+        const int act = static_cast<int>(left < cnt ? (left < 0 ? 0 : left) : cnt);
+        return t == 4 ? kCost4[act] : kCost2[act];
+    };
+    const long long items = sc.total_items;
+    if (items > 64LL * sms) {   // long launches: per-(batch, head) average times items per CTA
+        double per_bh = 0.0;
+        for (int g = 0; g < sc.groups; ++g) per_bh += item_cost(g);
+        return per_bh * static_cast<double>(bh) / sms;
+    }
+    double busy[256] = {0.0};
+    const int n = sms < 256 ? sms : 256;
+    for (long long w = 0; w < items; ++w) busy[w % n] += item_cost(w);
+    double worst = 0.0;
+    for (int i = 0; i < n; ++i) worst = busy[i] > worst ? busy[i] : worst;
+    return worst;
 }
 
-// Which full-grid kernel is expected to finish first.  Relative speeds are same-box medians on square shapes (B200, round 2:
-// mq4 1.00, mq2 0.90, w4 0.85 per unit of work); each is charged for how the launch packs: idle Q-tile slots inside partly filled
-// groups, and the last wave of the (persistent or not) grid.
+// Which full-grid kernel is expected to finish first (same unit: one full item of the 4-tile layout = 4 Q tiles at relative speed
+// 1.00; w4 runs two one-tile CTAs per SM at relative speed 0.85).  Relative speeds are same-box medians on square shapes, B200.
 int choose_full_grid_kernel(long long bh, long long tiles_m, int sms) {
-    const double work = static_cast<double>(bh * tiles_m);                       // Q tiles
     const long long waves_w4 = (bh * tiles_m + 2LL * sms - 1) / (2LL * sms);
-    const double t_w4 = static_cast<double>(waves_w4) * 2.0 * sms / 0.85;      // tile-times on the whole chip
-    const double t_mq4 = mq_cost(bh, tiles_m, 4, sms) * 4.0 * sms / 1.00;
-    const double t_mq2 = mq_cost(bh, tiles_m, 2, sms) * 2.0 * sms / 0.90;
-    (void)work;
+    const double t_w4 = static_cast<double>(waves_w4) * 2.0 * 0.25 / 0.85;
+    const double t_mq4 = mq_time(bh, tiles_m, 4, sms);
+    const double t_mq2 = mq_time(bh, tiles_m, 2, sms);
     if (t_mq4 <= t_mq2 && t_mq4 <= t_w4) return 1;
     return t_mq2 <= t_w4 ? 2 : 0;
 }
