@@ -774,6 +774,7 @@ def batched_section(pkg, torch, dev, peaks, props) -> dict:
               (16, 4096, torch.float16, "B16_N4096"), (128, 1024, torch.float16, "B128_N1024")]
 
     def bursts(fn, iters=20, n=5):
+        time.sleep(1.0)   # burst figures: every candidate (ours and SDPA alike) starts from an idle chip, not from its predecessor's heat
         for _ in range(3):
             fn()
         torch.cuda.synchronize()
