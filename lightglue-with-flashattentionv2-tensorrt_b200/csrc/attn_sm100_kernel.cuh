@@ -44,6 +44,7 @@
 #include <stdint.h>
 
 #include "attn_sm100.h"
+#include "attn_sm100_common.cuh"
 #include "softmax_math.cuh"
 
 // poll interval of the single-thread service warps (TMA producer, MMA issuer)
@@ -357,24 +358,16 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
             }
         } else if (warp == kSoftmaxWarps + 1) {
             // ===================================================================== MMA issuer
-            constexpr uint32_t idesc_qk = make_idesc_f16_f32acc(kBlockM, kBlockN, false);
-            constexpr uint32_t idesc_pv = make_idesc_f16_f32acc(kBlockM, kHeadDim, true);
             const uint32_t t_s = tmem_u + kColS;
             const uint32_t t_o = tmem_u + kColO;
             const uint32_t t_p = tmem_u + kColP;
-            const uint64_t desc_q = make_smem_desc_sw128(smem_u + kSmemQ, 16, 1024);
 
             auto issue_qk = [&](int j) {
                 const int s = j % kStages;
                 mbar_wait(ubar(kBarKFull + s), (j / kStages) & 1);
                 tc_fence_after();
                 if (elect_one()) {
-                    const uint64_t desc_k = make_smem_desc_sw128(usmem_k(s), 16, 1024);
-#pragma unroll
-                    for (int kk = 0; kk < kHeadDim / 16; ++kk) {
-                        // K-major: advancing 16 halves along K = +32 B inside the 128-B swizzle row
-                        mma_f16_ss(t_s, desc_q + 2u * kk, desc_k + 2u * kk, idesc_qk, kk > 0 ? 1u : 0u);
-                    }
+                    umma_qk<kBlockN>(t_s, smem_u + kSmemQ, usmem_k(s));
                     mma_commit(ubar(kBarKEmpty + s));
                     mma_commit(ubar(kBarSFull));
                 }
@@ -394,13 +387,7 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
                 mbar_wait(ubar(kBarPFull), j & 1);
                 tc_fence_after();
                 if (elect_one()) {
-                    const uint64_t desc_v = make_smem_desc_sw128(usmem_v(s), kTileBytes, 1024);
-#pragma unroll
-                    for (int kk = 0; kk < kBlockN / 16; ++kk) {
-                        // A = P from TMEM: 16 halves = 8 columns per k-step.
-                        // B = V, MN-major: 16 kv rows = 2048 B per k-step.
-                        mma_f16_ts(t_o, t_p + 8u * kk, desc_v + 128u * kk, idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
-                    }
+                    umma_pv<kBlockN>(t_o, t_p, usmem_v(s), kTileBytes, j > 0);
                     mma_commit(ubar(kBarVEmpty + s));
                     mma_commit(ubar(kBarPVDone));
                 }
@@ -456,11 +443,7 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
 
             // ragged KV tail: columns past n_kv get -inf (TMA zero-filled K rows gave S = 0 there)
             const int valid = n_kv - (kv_tile0 + j) * kBlockN - half * kHalfN;
-            if (valid < kHalfN) {
-#pragma unroll
-                for (int c = 0; c < kHalfN; ++c)
-                    if (c >= valid) sr[c] = 0xff800000u;
-            }
+            mask_kv_tail<kHalfN>(sr, valid);
 
             float mx = row_max<kHalfN>(sr);
             // combine with the other column half of the same rows
@@ -495,12 +478,7 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
             }
             tmem_st_x32(t_p, pk);
             if (rescale) {
-                uint32_t orow[32];
-                tmem_ld_x32(t_o, orow);
-                tmem_wait_ld();
-#pragma unroll
-                for (int c = 0; c < 32; ++c) orow[c] = __float_as_uint(__uint_as_float(orow[c]) * alpha);
-                tmem_st_x32(t_o, orow);
+                rescale_o_tmem<32>(t_o, alpha);   // this warp's 32 of the 64 O columns
                 l_sum *= alpha;
             }
             l_sum += tile_sum;

@@ -41,6 +41,7 @@
 #include <stdint.h>
 
 #include "attn_sm100.h"
+#include "attn_sm100_common.cuh"
 #include "softmax_math.cuh"
 
 #ifndef LG_ATTN_SPIN_NS
@@ -281,8 +282,6 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
             // ===================================================================== MMA issuers (each: its tiles in a fixed round-robin order)
             constexpr int kTilesPerWarp = kT / C::kMmaWarps;
             const int t_begin = (warp - kWarpMMA) * kTilesPerWarp, t_end = t_begin + kTilesPerWarp;
-            constexpr uint32_t idesc_qk = make_idesc_f16_f32acc(kBlockM, kBN, false);
-            constexpr uint32_t idesc_pv = make_idesc_f16_f32acc(kBlockM, kHeadDim, true);
             auto mma_wait = [&](uint32_t b, uint32_t parity) {
                 if (LG_ATTN_MQ_MMA_SPIN_NS > 0) mbar_wait_backoff(b, parity, LG_ATTN_MQ_MMA_SPIN_NS);
                 else mbar_wait(b, parity);
@@ -299,24 +298,14 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
             // (elected lane) S_t = Q_t K(g)^T.  The caller has made sure K(g) has landed and S_t may be overwritten.
             auto issue_qk = [&](int t, int g) {
                 if (skip_qk || t >= n_active) return;
-                const int s = g % C::kStages;
-                const uint64_t desc_q = make_smem_desc_sw128(smem_u + C::kSmemQ + t * C::kQBytes, 16, 1024);
-                const uint64_t desc_k = make_smem_desc_sw128(smem_u + C::kSmemK + s * C::kKVBytes, 16, 1024);
-                const uint32_t t_s = tmem_u + t * C::kTileCols + C::kColS;
-#pragma unroll
-                for (int kk = 0; kk < kHeadDim / 16; ++kk)   // K-major: 16 halves along K = +32 B inside the 128-B swizzle row
-                    mma_f16_ss(t_s, desc_q + 2u * kk, desc_k + 2u * kk, idesc_qk, kk > 0 ? 1u : 0u);
+                umma_qk<kBN>(tmem_u + t * C::kTileCols + C::kColS, smem_u + C::kSmemQ + t * C::kQBytes,
+                             smem_u + C::kSmemK + (g % C::kStages) * C::kKVBytes);
             };
-            // (elected lane) O_t (+)= P_t V(g): A = P from TMEM (8 columns per 16 kv rows), B = V MN-major (16 kv rows = 2048 B per k-step)
+            // (elected lane) O_t (+)= P_t V(g)
             auto issue_pv = [&](int t, int g, bool accumulate) {
                 if (t >= n_active) return;
-                const int s = g % C::kStages;
-                const uint64_t desc_v = make_smem_desc_sw128(smem_u + C::kSmemV + s * C::kKVBytes, C::kKVBytes, 1024);
-                const uint32_t t_o = tmem_u + t * C::kTileCols + C::kColO;
-                const uint32_t t_p = tmem_u + t * C::kTileCols + C::kColP;
-#pragma unroll
-                for (int kk = 0; kk < kBN / 16; ++kk)
-                    mma_f16_ts(t_o, t_p + 8u * kk, desc_v + 128u * kk, idesc_pv, (accumulate || kk > 0) ? 1u : 0u);
+                umma_pv<kBN>(tmem_u + t * C::kTileCols + C::kColO, tmem_u + t * C::kTileCols + C::kColP,
+                             smem_u + C::kSmemV + (g % C::kStages) * C::kKVBytes, C::kKVBytes, accumulate);
             };
             auto wait_k = [&](int g) {
                 mma_wait(ubar(C::kBarKFull + g % C::kStages), (g / C::kStages) & 1);
@@ -470,12 +459,7 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
                         __syncwarp();
                         if (lane == 0) mbar_arrive(bar_s_empty);
                     }
-                    // ragged KV tail: columns past n_kv get -inf (TMA zero-filled K rows gave S = 0 there)
-                    if (valid < kBN) {
-#pragma unroll
-                        for (int cc = 0; cc < kBN; ++cc)
-                            if (cc >= valid) sr[cc] = 0xff800000u;
-                    }
+                    mask_kv_tail<kBN>(sr, valid);   // ragged KV tail: columns past n_kv get -inf
                     if (need_max) {
                         const float mx = row_max<kBN>(sr);
                         // lazy rescale decision (warp-uniform so the tcgen05.ld/st below stay aligned)
@@ -539,15 +523,7 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
 #pragma unroll
                 for (int cc = 0; cc < kBN / 64; ++cc) tmem_st_x32(t_p + 32u * cc, pk + 32 * cc);
                 if (rescale) {
-#pragma unroll
-                    for (int h = 0; h < 2; ++h) {
-                        uint32_t orow[32];
-                        tmem_ld_x32(t_o + 32u * h, orow);
-                        tmem_wait_ld();
-#pragma unroll
-                        for (int cc = 0; cc < 32; ++cc) orow[cc] = __float_as_uint(__uint_as_float(orow[cc]) * alpha);
-                        tmem_st_x32(t_o + 32u * h, orow);
-                    }
+                    rescale_o_tmem<kHeadDim>(t_o, alpha);
                     l_sum *= alpha;
                 }
                 l_sum += tile_sum;
@@ -576,29 +552,9 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
             const float inv_l = 1.0f / l_sum;
             const int row = (c.tile_m0 + tile) * kBlockM + (warp & 3) * 32 + lane;
             if (row < n_q) {
-                if constexpr (!kOutF32) {
-                    __half* o = reinterpret_cast<__half*>(out) + (c.bi * ol.sb + c.hi * ol.sh + row * ol.sr);
-#pragma unroll
-                    for (int cc = 0; cc < 8; ++cc) {
-                        uint4 v;
-                        v.x = pack_half2(__uint_as_float(orow[8 * cc + 0]) * inv_l, __uint_as_float(orow[8 * cc + 1]) * inv_l);
-                        v.y = pack_half2(__uint_as_float(orow[8 * cc + 2]) * inv_l, __uint_as_float(orow[8 * cc + 3]) * inv_l);
-                        v.z = pack_half2(__uint_as_float(orow[8 * cc + 4]) * inv_l, __uint_as_float(orow[8 * cc + 5]) * inv_l);
-                        v.w = pack_half2(__uint_as_float(orow[8 * cc + 6]) * inv_l, __uint_as_float(orow[8 * cc + 7]) * inv_l);
-                        st_global_v4(o + cc * 8, v);
-                    }
-                } else {
-                    float* o = reinterpret_cast<float*>(out) + (c.bi * ol.sb + c.hi * ol.sh + row * ol.sr);
-#pragma unroll
-                    for (int cc = 0; cc < 16; ++cc) {
-                        uint4 v;
-                        v.x = __float_as_uint(__uint_as_float(orow[4 * cc + 0]) * inv_l);
-                        v.y = __float_as_uint(__uint_as_float(orow[4 * cc + 1]) * inv_l);
-                        v.z = __float_as_uint(__uint_as_float(orow[4 * cc + 2]) * inv_l);
-                        v.w = __float_as_uint(__uint_as_float(orow[4 * cc + 3]) * inv_l);
-                        st_global_v4(o + cc * 4, v);
-                    }
-                }
+                const long long off = c.bi * ol.sb + c.hi * ol.sh + row * ol.sr;
+                if constexpr (!kOutF32) store_o_row<false>(reinterpret_cast<__half*>(out) + off, orow, inv_l);
+                else store_o_row<true>(reinterpret_cast<float*>(out) + off, orow, inv_l);
             }
         }
     }

@@ -29,6 +29,7 @@
 #include <stdint.h>
 
 #include "attn_sm100.h"
+#include "attn_sm100_common.cuh"
 #include "softmax_math.cuh"
 
 // poll interval of the single-thread service warps (TMA producer, MMA issuer)
@@ -219,24 +220,16 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
             }
         } else if (warp == 5) {
             // ===================================================================== MMA issuer
-            constexpr uint32_t idesc_qk = make_idesc_f16_f32acc(kBlockM, kBlockN, false);
-            constexpr uint32_t idesc_pv = make_idesc_f16_f32acc(kBlockM, kHeadDim, true);
             const uint32_t t_s = tmem_u + kColS;
             const uint32_t t_o = tmem_u + kColO;
             const uint32_t t_p = tmem_u + kColP;
-            const uint64_t desc_q = make_smem_desc_sw128(smem_u + kSmemQ, 16, 1024);
 
             auto issue_qk = [&](int j) {
                 const int s = j % kStages;
                 mbar_wait_backoff(ubar(kBarKFull + s), (j / kStages) & 1, LG_ATTN_SPIN_NS);
                 tc_fence_after();
                 if (elect_one()) {
-                    const uint64_t desc_k = make_smem_desc_sw128(smem_u + kSmemK + s * kTileBytes, 16, 1024);
-#pragma unroll
-                    for (int kk = 0; kk < kHeadDim / 16; ++kk) {
-                        // K-major: advancing 16 halves along K = +32 B inside the 128-B swizzle row
-                        mma_f16_ss(t_s, desc_q + 2u * kk, desc_k + 2u * kk, idesc_qk, kk > 0 ? 1u : 0u);
-                    }
+                    umma_qk<kBlockN>(t_s, smem_u + kSmemQ, smem_u + kSmemK + s * kTileBytes);
                     mma_commit(ubar(kBarKEmpty + s));
                     mma_commit(ubar(kBarSFull));
                 }
@@ -255,13 +248,7 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
                 mbar_wait_backoff(ubar(kBarPFull), j & 1, LG_ATTN_SPIN_NS);
                 tc_fence_after();
                 if (elect_one()) {
-                    const uint64_t desc_v = make_smem_desc_sw128(smem_u + kSmemV + s * kTileBytes, kTileBytes, 1024);
-#pragma unroll
-                    for (int kk = 0; kk < kBlockN / 16; ++kk) {
-                        // A = P from TMEM: 16 halves = 8 columns per k-step.
-                        // B = V, MN-major: 16 kv rows = 2048 B per k-step.
-                        mma_f16_ts(t_o, t_p + 8u * kk, desc_v + 128u * kk, idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
-                    }
+                    umma_pv<kBlockN>(t_o, t_p, smem_u + kSmemV + s * kTileBytes, kTileBytes, j > 0);
                     mma_commit(ubar(kBarVEmpty + s));
                     mma_commit(ubar(kBarPVDone));
                 }
@@ -311,11 +298,7 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
             // ragged KV tail: columns past n_kv get -inf (TMA zero-filled K rows gave S = 0 there)
             const int valid = kv_left;  // running count instead of n_kv - j*128: no constant-bank reload on the critical path
             kv_left -= kBlockN;
-            if (valid < kBlockN) {
-#pragma unroll
-                for (int c = 0; c < kBlockN; ++c)
-                    if (c >= valid) sr[c] = 0xff800000u;
-            }
+            mask_kv_tail<kBlockN>(sr, valid);
 
 #if defined(LG_ATTN_WHATIF) && (LG_ATTN_WHATIF == 1 || LG_ATTN_WHATIF == 3)
             const float mx = 0.f;   // what-if build (WRONG results in general): no row-max pass
@@ -387,16 +370,7 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
             tmem_st_x32(t_p, pk);
             tmem_st_x32(t_p + 32u, pk + 32);
             if (rescale) {
-#pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    uint32_t orow[32];
-                    tmem_ld_x32(t_o + 32u * h, orow);
-                    tmem_wait_ld();
-#pragma unroll
-                    for (int c = 0; c < 32; ++c)
-                        orow[c] = __float_as_uint(__uint_as_float(orow[c]) * alpha);
-                    tmem_st_x32(t_o + 32u * h, orow);
-                }
+                rescale_o_tmem<kHeadDim>(t_o, alpha);
                 l_sum *= alpha;
             }
             l_sum += tile_sum;
