@@ -479,3 +479,39 @@ def test_full_grid_kernels_agree_through_strided_entry(pkg):
         lib.lg_attn_debug_set_throughput_kernel(-1)
     for o in outs[1:]:
         assert (o.float() - outs[0].float()).abs().max().item() <= 2 * orc.TOL_F16_MAX_ABS
+
+
+def test_random_shapes_all_kernels_fuzz(pkg):
+    """Seeded fuzz over batch / N / M / kernel / output type, including launches with work items of every fill level (1-4 active
+    tiles), single-step KV loops and grids just above and below the full-grid threshold; checked against an FP32 torch reference
+    on sampled (batch, head) slices, with a sentinel canary behind the output."""
+    import random
+
+    rng = random.Random(20260411)
+    lib = pkg.load()
+    g = torch.Generator(device=DEV).manual_seed(99)
+    try:
+        for case in range(48):
+            b = rng.choice([1, 2, 3, 5, 9, 17, 33, 40, 75, 80, 148, 150])
+            n = rng.choice([1, 31, 64, 127, 128, 129, 255, 300, 385, 512, 640, 777, 1000, 1025, 1500, 2048])
+            m = rng.choice([1, 2, 63, 64, 65, 127, 128, 129, 200, 511, 513, 1000, 1024, 2047])
+            mode = rng.choice([-1, 0, 1, 2])
+            out_dt = rng.choice([torch.float16, torch.float32])
+            assert lib.lg_attn_debug_set_throughput_kernel(mode) == 0
+            q = torch.randn(b, 4, n, 64, device=DEV, generator=g).half()
+            k = torch.randn(b, 4, m, 64, device=DEV, generator=g).half()
+            v = torch.randn(b, 4, m, 64, device=DEV, generator=g).half()
+            buf = torch.full((b * 4 * n * 64 + 512,), -77.0, dtype=out_dt, device=DEV)
+            out = buf[: b * 4 * n * 64].view(b, 4, n, 64)
+            pkg.attention(q, k, v, out_dtype=out_dt, out=out)
+            assert (buf[b * 4 * n * 64:] == -77.0).all(), (case, b, n, m, mode)
+            for bi in {0, b // 2, b - 1}:
+                ref = torch.nn.functional.scaled_dot_product_attention(q[bi].float(), k[bi].float(), v[bi].float())
+                err = (out[bi].float() - ref).abs().max().item()
+                # FP16 out: the north-star bar, or 1.5 FP16 ulps of the largest output where few keys make |O| reach |V| (M = 1, 2)
+                tol = max(orc.TOL_F16_MAX_ABS, 1.5e-3 * ref.abs().max().item()) if out_dt == torch.float16 \
+                    else orc.TOL_F32_REL * ref.abs().max().item()
+                assert err <= tol, (case, b, n, m, mode, out_dt, bi, err)
+    finally:
+        lib.lg_attn_debug_set_throughput_kernel(-1)
+
