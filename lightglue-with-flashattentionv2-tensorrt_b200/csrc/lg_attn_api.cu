@@ -614,11 +614,18 @@ int lg_attn_hd64_run_host(const void* q_host, const void* k_host, const void* v_
     return static_cast<int>(e);
 }
 
+// Host-buffer session.  Three streams — H2D copies, launches, D2H copies — tied together per slot by events, so that each copy
+// engine and the SMs each see one back-to-back queue: the input copy of problem k+1.. runs under the kernel of problem k and the
+// output copy of problem k-1 (one stream per slot, round 1, left the H2D engine idle whenever a slot's own D2H had not finished:
+// 25 of the 30 TFLOP/s-equivalent a copy-only loop reaches on the same box, tools/copy_only_probe.py).
 struct lg_attn_session {
     int device = 0, max_batch = 0, heads = 0, max_n_q = 0, max_n_kv = 0, io_dtype = 0, n_slots = 0;
-    size_t q_bytes = 0, kv_bytes = 0, o_bytes = 0, ws_bytes = 0;
+    size_t q_bytes = 0, kv_bytes = 0, o_bytes = 0;
     uint8_t* pool = nullptr;
-    cudaStream_t* streams = nullptr;
+    cudaStream_t s_in = nullptr, s_run = nullptr, s_out = nullptr;
+    cudaEvent_t* ev_in = nullptr;    // [slot] inputs have landed
+    cudaEvent_t* ev_run = nullptr;   // [slot] kernel done: inputs consumed, output written
+    cudaEvent_t* ev_out = nullptr;   // [slot] output copied out: the slot's output buffer may be rewritten
     unsigned long long next = 0;
 };
 
@@ -641,15 +648,21 @@ int lg_attn_session_create(lg_attn_session** out, int device, int max_batch, int
     s->q_bytes = align256(bh * max_n_q * kHeadDim * in_es);
     s->kv_bytes = align256(bh * max_n_kv * kHeadDim * in_es);
     s->o_bytes = align256(bh * max_n_q * kHeadDim * out_es);
-    s->ws_bytes = align256(lg_attn_hd64_workspace_bytes(max_batch, heads, max_n_q, max_n_kv, io_dtype));
-    const size_t slot = s->q_bytes + 2 * s->kv_bytes + s->o_bytes + s->ws_bytes;
+    const size_t slot = s->q_bytes + 2 * s->kv_bytes + s->o_bytes;
     e = cudaMalloc(&s->pool, slot * n_slots);
     if (e != cudaSuccess) { delete s; return static_cast<int>(e); }
-    s->streams = new cudaStream_t[n_slots]();
-    for (int i = 0; i < n_slots; ++i) {
-        e = cudaStreamCreateWithFlags(&s->streams[i], cudaStreamNonBlocking);
-        if (e != cudaSuccess) { lg_attn_session_destroy(s); return static_cast<int>(e); }
+    s->ev_in = new cudaEvent_t[n_slots]();
+    s->ev_run = new cudaEvent_t[n_slots]();
+    s->ev_out = new cudaEvent_t[n_slots]();
+    e = cudaStreamCreateWithFlags(&s->s_in, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&s->s_run, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&s->s_out, cudaStreamNonBlocking);
+    for (int i = 0; i < n_slots && e == cudaSuccess; ++i) {
+        e = cudaEventCreateWithFlags(&s->ev_in[i], cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&s->ev_run[i], cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&s->ev_out[i], cudaEventDisableTiming);
     }
+    if (e != cudaSuccess) { lg_attn_session_destroy(s); return static_cast<int>(e); }
     *out = s;
     return 0;
 }
@@ -662,53 +675,65 @@ int lg_attn_session_submit(lg_attn_session* s, const void* q_host, const void* k
         return LG_ATTN_EINVAL;
     cudaError_t e = cudaSetDevice(s->device);
     if (e != cudaSuccess) return static_cast<int>(e);
-    const int i = static_cast<int>(s->next++ % static_cast<unsigned long long>(s->n_slots));
-    const size_t slot = s->q_bytes + 2 * s->kv_bytes + s->o_bytes + s->ws_bytes;
+    const unsigned long long k = s->next++;
+    const int i = static_cast<int>(k % static_cast<unsigned long long>(s->n_slots));
+    const bool reused = k >= static_cast<unsigned long long>(s->n_slots);
+    const size_t slot = s->q_bytes + 2 * s->kv_bytes + s->o_bytes;
     uint8_t* dq = s->pool + slot * i;
     uint8_t* dk = dq + s->q_bytes;
     uint8_t* dv = dk + s->kv_bytes;
     uint8_t* dout = dv + s->kv_bytes;
-    uint8_t* dws = dout + s->o_bytes;
     const size_t in_es = (s->io_dtype == LG_ATTN_F32_F32) ? 4 : 2;
     const size_t out_es = (s->io_dtype == LG_ATTN_F16_F16) ? 2 : 4;
     const size_t bh = static_cast<size_t>(batch) * s->heads;
-    cudaStream_t st = s->streams[i];
     const size_t qb = bh * n_q * kHeadDim * in_es, kvb = bh * n_kv * kHeadDim * in_es;
     const uint8_t* qh8 = static_cast<const uint8_t*>(q_host);
+    // ---- input copies: the slot's previous kernel must have consumed its inputs
+    if (reused) e = cudaStreamWaitEvent(s->s_in, s->ev_run[i], 0);
+    if (e != cudaSuccess) return static_cast<int>(e);
     if (static_cast<const uint8_t*>(k_host) == qh8 + qb && static_cast<const uint8_t*>(v_host) == qh8 + qb + kvb &&
         qb == s->q_bytes && kvb == s->kv_bytes) {
         // q | k | v adjacent in host memory and the slot is exactly this shape: one 3x larger PCIe transfer
         // (0.5 MiB copies reach ~2/3 of the link rate of 1.5 MiB ones on this box)
-        e = cudaMemcpyAsync(dq, q_host, qb + 2 * kvb, cudaMemcpyHostToDevice, st);
+        e = cudaMemcpyAsync(dq, q_host, qb + 2 * kvb, cudaMemcpyHostToDevice, s->s_in);
     } else {
-        e = cudaMemcpyAsync(dq, q_host, qb, cudaMemcpyHostToDevice, st);
-        if (e == cudaSuccess) e = cudaMemcpyAsync(dk, k_host, kvb, cudaMemcpyHostToDevice, st);
-        if (e == cudaSuccess) e = cudaMemcpyAsync(dv, v_host, kvb, cudaMemcpyHostToDevice, st);
+        e = cudaMemcpyAsync(dq, q_host, qb, cudaMemcpyHostToDevice, s->s_in);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(dk, k_host, kvb, cudaMemcpyHostToDevice, s->s_in);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(dv, v_host, kvb, cudaMemcpyHostToDevice, s->s_in);
     }
+    if (e == cudaSuccess) e = cudaEventRecord(s->ev_in[i], s->s_in);
+    // ---- launch: inputs landed, and the slot's previous output has been copied out
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(s->s_run, s->ev_in[i], 0);
+    if (e == cudaSuccess && reused) e = cudaStreamWaitEvent(s->s_run, s->ev_out[i], 0);
     if (e != cudaSuccess) return static_cast<int>(e);
-    int rc = lg_attn_hd64_launch(dq, dk, dv, dout, batch, s->heads, n_q, n_kv, s->io_dtype,
-                                 s->ws_bytes ? dws : nullptr, s->ws_bytes, st);
+    int rc = lg_attn_hd64_launch(dq, dk, dv, dout, batch, s->heads, n_q, n_kv, s->io_dtype, nullptr, 0, s->s_run);
     if (rc != 0) return rc;
-    e = cudaMemcpyAsync(o_host, dout, bh * n_q * kHeadDim * out_es, cudaMemcpyDeviceToHost, st);
+    e = cudaEventRecord(s->ev_run[i], s->s_run);
+    // ---- output copy
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(s->s_out, s->ev_run[i], 0);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(o_host, dout, bh * n_q * kHeadDim * out_es, cudaMemcpyDeviceToHost, s->s_out);
+    if (e == cudaSuccess) e = cudaEventRecord(s->ev_out[i], s->s_out);
     return static_cast<int>(e);
 }
 
 int lg_attn_session_sync(lg_attn_session* s) {
     if (s == nullptr) return LG_ATTN_EINVAL;
-    for (int i = 0; i < s->n_slots; ++i) {
-        cudaError_t e = cudaStreamSynchronize(s->streams[i]);
-        if (e != cudaSuccess) return static_cast<int>(e);
-    }
-    return 0;
+    cudaError_t e = cudaStreamSynchronize(s->s_in);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s->s_run);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s->s_out);
+    return static_cast<int>(e);
 }
 
 void lg_attn_session_destroy(lg_attn_session* s) {
     if (s == nullptr) return;
     (void)cudaSetDevice(s->device);
-    if (s->streams != nullptr) {
+    for (cudaStream_t st : {s->s_in, s->s_run, s->s_out})
+        if (st != nullptr) { (void)cudaStreamSynchronize(st); (void)cudaStreamDestroy(st); }
+    for (cudaEvent_t* arr : {s->ev_in, s->ev_run, s->ev_out}) {
+        if (arr == nullptr) continue;
         for (int i = 0; i < s->n_slots; ++i)
-            if (s->streams[i] != nullptr) (void)cudaStreamDestroy(s->streams[i]);
-        delete[] s->streams;
+            if (arr[i] != nullptr) (void)cudaEventDestroy(arr[i]);
+        delete[] arr;
     }
     if (s->pool != nullptr) (void)cudaFree(s->pool);
     delete s;
