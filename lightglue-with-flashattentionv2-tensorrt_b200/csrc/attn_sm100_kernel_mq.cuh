@@ -6,28 +6,29 @@
 // (/root/reference/lightglue_attention_plugin/attention_headdim_64_fp16in_fp32out.cu:400-665 and the FP16-out twin).
 //
 // One CTA per SM owns ALL 512 TMEM columns and kT 128-row Q tiles of one (batch, head) at a time ("work item"); the kT tiles
-// share every K/V tile that TMA brings in (one L2->smem transfer per kT*128 Q rows instead of one per 128), one MMA-issuing
-// thread feeds the in-order tensor pipe for all tiles in a fixed round-robin order, and kT softmax warpgroups (one per Q
-// tile, one S row per thread) run staggered by that order so that one group's TMEM loads / stores, barrier round trips and
-// MMA latency sit under the other groups' exponentials by construction.  Two layouts are instantiated:
+// share every K/V tile that TMA brings in (one L2->smem transfer per kT*128 Q rows instead of one per 128), two MMA-issuing
+// warps feed the in-order tensor pipe (two tiles each, fixed order), and kT softmax warpgroups (one per Q tile, one S row per
+// thread) overlap one another's TMEM loads / stores, barrier round trips and MMA latency.  Two layouts are instantiated:
 //
-//   <kT=2, kBN=128, alias=0>   S[128] | P[64] | O[64] per tile (256 columns): QK(j+1) is issued as soon as the softmax group has
-//                              pulled S(j) into registers, so S(j+1) is ready before the group asks for it.
 //   <kT=4, kBN=64,  alias=1>   S[64] (P aliased onto its first 32 columns) | O[64] per tile (128 columns): four softmax warps
 //                              per scheduler; per tile the chain QK -> softmax -> PV -> QK is serial and the other three
 //                              tiles fill the pipes meanwhile.  With P aliased the tensor pipe's issue order (PV(j) before
 //                              QK(j+1), same thread) is what keeps QK(j+1) from overwriting P(j) early, and s_full(j) also
 //                              tells the softmax group that PV(j-1) is complete (O final, rescale legal) — one barrier wait
-//                              per step.
+//                              per step.  The default full-grid kernel.
+//   <kT=2, kBN=128, alias=0>   S[128] | P[64] | O[64] per tile (256 columns): QK(j+1) is issued as soon as the softmax group has
+//                              pulled S(j) into registers, so S(j+1) is ready before the group asks for it.  Used when the
+//                              Q-tile count packs better into pairs.
 //
 // kLazyMax (alias layouts): the row max is only computed on the first KV step of a Q tile and when the step's row sum says
-// that some probability reached 2^tau (the stale reference is then too small); S is still intact in TMEM at that point and
+// that some probability reached 2^7 (the stale reference is then too small); S is still intact in TMEM at that point and
 // the step is redone with the true max.  That removes the 0.5 FMNMX3 per score of the common step.
 //
-// Warps: [0, 4kT) softmax groups | 4kT: K/V TMA producer | 4kT+1: MMA issuer | 4kT+2: Q TMA producer | 4kT+3: TMEM allocator.
+// Warps: [0, 4kT) softmax groups | 4kT: K/V TMA producer | 4kT+1: Q TMA producer + TMEM allocator | 4kT+2.. : MMA issuers.
+// Service warps run converged and issue through elect.sync (see the comment at their entry).
 // CTAs are persistent: grid = min(#SM, items), items walked blockIdx.x + i * gridDim.x; barrier phases are carried by
 // running step / item counters; K/V stream across item boundaries; Q(i+1) is prefetched when the last QK of item i is done.
-// Q tiles past N inside an item are zero-filled by TMA, computed and never stored (uniform control flow).
+// Items have a variable number of active tiles (struct Sched): idle tiles only exchange barrier arrivals.
 //
 // No CUTLASS; see ptx_sm100.cuh for the hand-written encodings.
 
