@@ -55,13 +55,13 @@ __device__ __forceinline__ void rescale_o_tmem(uint32_t t_o, float alpha) {
     }
 }
 
-// One thread's whole output row (64 FP32 accumulator values) times inv_l to global memory, 16-byte stores.
-template <bool kOutF32>
-__device__ __forceinline__ void store_o_row(void* out_row, const uint32_t (&orow)[kHeadDim], float inv_l) {
+// One thread's output row (kCols FP32 accumulator values, the whole row by default) times inv_l to global memory, 16-byte stores.
+template <bool kOutF32, int kCols = kHeadDim>
+__device__ __forceinline__ void store_o_row(void* out_row, const uint32_t (&orow)[kCols], float inv_l) {
     if constexpr (!kOutF32) {
         __half* o = reinterpret_cast<__half*>(out_row);
 #pragma unroll
-        for (int c = 0; c < 8; ++c) {
+        for (int c = 0; c < kCols / 8; ++c) {
             uint4 v;
             v.x = pack_half2(__uint_as_float(orow[8 * c + 0]) * inv_l, __uint_as_float(orow[8 * c + 1]) * inv_l);
             v.y = pack_half2(__uint_as_float(orow[8 * c + 2]) * inv_l, __uint_as_float(orow[8 * c + 3]) * inv_l);
@@ -72,7 +72,7 @@ __device__ __forceinline__ void store_o_row(void* out_row, const uint32_t (&orow
     } else {
         float* o = reinterpret_cast<float*>(out_row);
 #pragma unroll
-        for (int c = 0; c < 16; ++c) {
+        for (int c = 0; c < kCols / 4; ++c) {
             uint4 v;
             v.x = __float_as_uint(__uint_as_float(orow[4 * c + 0]) * inv_l);
             v.y = __float_as_uint(__uint_as_float(orow[4 * c + 1]) * inv_l);

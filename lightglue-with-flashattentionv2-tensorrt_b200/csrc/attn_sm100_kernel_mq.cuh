@@ -20,6 +20,9 @@
 //                              pulled S(j) into registers, so S(j+1) is ready before the group asks for it.  Used when the
 //                              Q-tile count packs better into pairs.
 //
+// kSplit = 2 (tuning builds only; measured slower): kSplit softmax warps share a 32-row slab and take
+// kBN / kSplit columns of every step each (16 softmax warps on the <2,128> layout).
+//
 // kLazyMax (alias layouts): the row max is only computed on the first KV step of a Q tile and when the step's row sum says
 // that some probability reached 2^7 (the stale reference is then too small); S is still intact in TMEM at that point and
 // the step is redone with the true max.  That removes the 0.5 FMNMX3 per score of the common step.
@@ -91,10 +94,12 @@ __device__ long long g_mq_trace[kTraceCtas][kTraceSteps][kTraceTiles][kTraceEven
 #define LG_ATTN_MQ_MMA_WARPS 2   // MMA-issuing warps; warp m serves tiles [m*kT/n, (m+1)*kT/n) in a fixed order (clamped to kT)
 #endif
 
-template <int kT, int kBN, bool kAlias>
+template <int kT, int kBN, bool kAlias, int kSplit = 1>
 struct Cfg {
     static_assert(kBN == 64 || kBN == 128, "KV step");
-    static constexpr int kSoftmaxWarps = 4 * kT;
+    static_assert(kSplit == 1 || (kSplit == 2 && !kAlias), "column halves: S and P separate");
+    static constexpr int kWarpsPerTile = 4 * kSplit;   // kSplit warps share a 32-row slab, each takes kBN / kSplit columns of it
+    static constexpr int kSoftmaxWarps = kWarpsPerTile * kT;
     static constexpr int kMmaWarps = LG_ATTN_MQ_MMA_WARPS > kT ? kT : (kT % LG_ATTN_MQ_MMA_WARPS == 0 ? LG_ATTN_MQ_MMA_WARPS : 1);
     static constexpr int kServiceWarps = (2 + kMmaWarps + 3) / 4 * 4;   // K/V producer, Q producer (+ TMEM alloc), MMA issuers; setmaxnreg wants whole warpgroups
     static constexpr int kThreads = (kSoftmaxWarps + kServiceWarps) * 32;
@@ -111,7 +116,9 @@ struct Cfg {
                               kBarVFull = kBarKEmpty + kStages, kBarVEmpty = kBarVFull + kStages,
                               kNumBars = kBarVEmpty + kStages;
     static constexpr uint32_t kSmemTmemSlot = kSmemBar + 8 * kNumBars;
-    static constexpr uint32_t kSmemUsed = kSmemTmemSlot + 16;
+    // kSplit == 2: row max / row sum exchange between the two column halves of a row, [tile][parity][half][row] floats
+    static constexpr uint32_t kSmemExch = kSmemTmemSlot + 16;
+    static constexpr uint32_t kSmemUsed = kSmemExch + (kSplit > 1 ? kT * 2 * kSplit * kBlockM * 4 : 0);
     // >= 114 KiB so that a second CTA can never become resident next to this one (it would spin in tcgen05.alloc)
     static constexpr uint32_t kSmemBytes = (kSmemUsed + 1024 > 120 * 1024) ? kSmemUsed + 1024 : 120 * 1024;
     static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
@@ -167,12 +174,12 @@ __device__ __forceinline__ Item item_coord(int w, const Sched& sc, const OutLayo
     return c;
 }
 
-template <int kT, int kBN, bool kAlias, bool kLazyMax, bool kOutF32>
-__global__ void __launch_bounds__(Cfg<kT, kBN, kAlias>::kThreads, 1)
+template <int kT, int kBN, bool kAlias, bool kLazyMax, bool kOutF32, int kSplit = 1>
+__global__ void __launch_bounds__(Cfg<kT, kBN, kAlias, kSplit>::kThreads, 1)
 lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
                  const __grid_constant__ CUtensorMap tm_v, void* __restrict__ out, int n_q, int n_kv, const Sched sc,
                  const OutLayout ol) {
-    using C = Cfg<kT, kBN, kAlias>;
+    using C = Cfg<kT, kBN, kAlias, kSplit>;
     static_assert(!kLazyMax || kAlias, "the lazy row max re-reads S from TMEM: S must survive until P is stored");
     extern __shared__ uint8_t smem_raw[];
     uint32_t smem = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -196,10 +203,10 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
             mbar_init(bar(C::kBarQFull + t), 1);
             mbar_init(bar(C::kBarQEmpty + t), 1);
             mbar_init(bar(C::kBarSFull + t), 1);
-            mbar_init(bar(C::kBarSEmpty + t), 4);   // one arrival per softmax warp of the tile
-            mbar_init(bar(C::kBarPFull + t), 4);
+            mbar_init(bar(C::kBarSEmpty + t), C::kWarpsPerTile);   // one arrival per softmax warp of the tile
+            mbar_init(bar(C::kBarPFull + t), C::kWarpsPerTile);
             mbar_init(bar(C::kBarPVDone + t), 1);
-            mbar_init(bar(C::kBarOEmpty + t), 4);
+            mbar_init(bar(C::kBarOEmpty + t), C::kWarpsPerTile);
         }
 #pragma unroll
         for (int s = 0; s < C::kStages; ++s) {
@@ -405,13 +412,21 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
             }
         }
     } else {
-        // ========================================================================= softmax warpgroups (tile = warp / 4)
+        // ========================================================================= softmax warps (tile = warp / (4 * kSplit))
+        // kSplit == 2: warps q and q + 4 of a tile own the same 32 rows (TMEM lanes 32 * (warp % 4) ..) and one half of the step's
+        // columns each; they agree on the row max through shared memory + a 64-thread named barrier, and each keeps / rescales /
+        // stores its half of the O columns.
         setmaxnreg_inc<C::kRegsSoftmax>();
-        const int tile = warp >> 2;
+        constexpr int kCols = kBN / kSplit, kOCols = kHeadDim / kSplit;
+        const int tile = warp / C::kWarpsPerTile;
+        const int half = (warp >> 2) % kSplit;
         const uint32_t lane_sel = static_cast<uint32_t>((warp & 3) * 32) << 16;
-        const uint32_t t_s = tmem_base + lane_sel + tile * C::kTileCols + C::kColS;
-        const uint32_t t_o = tmem_base + lane_sel + tile * C::kTileCols + C::kColO;
-        const uint32_t t_p = tmem_base + lane_sel + tile * C::kTileCols + C::kColP;
+        const uint32_t t_s = tmem_base + lane_sel + tile * C::kTileCols + C::kColS + half * kCols;
+        const uint32_t t_o = tmem_base + lane_sel + tile * C::kTileCols + C::kColO + half * kOCols;
+        const uint32_t t_p = tmem_base + lane_sel + tile * C::kTileCols + C::kColP + half * (kCols / 2);
+        const uint32_t exch = smem + C::kSmemExch + static_cast<uint32_t>(tile * 2 * kSplit * kBlockM + (warp & 3) * 32 + lane) * 4u;
+        auto exch_addr = [&](int parity, int h) { return exch + static_cast<uint32_t>((parity * kSplit + h) * kBlockM) * 4u; };
+        auto pair_sync = [&]() { named_bar_sync(1u + static_cast<uint32_t>(tile * 4 + (warp & 3)), 64u); };
         const uint32_t bar_s_full = bar(C::kBarSFull + tile), bar_s_empty = bar(C::kBarSEmpty + tile);
         const uint32_t bar_p_full = bar(C::kBarPFull + tile), bar_pv_done = bar(C::kBarPVDone + tile);
         const uint32_t bar_o_empty = bar(C::kBarOEmpty + tile);
@@ -442,17 +457,17 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
                     if (lane == 0) mbar_arrive(bar_p_full);
                     continue;
                 }
-                const int valid = kv_left;
+                const int valid = kv_left - half * kCols;
                 kv_left -= kBN;
 
-                uint32_t pk[kBN / 2];
+                uint32_t pk[kCols / 2];
                 float tile_sum, alpha = 1.f;
                 bool rescale = false;
                 bool need_max = !kLazyMax || j == 0;
                 while (true) {
-                    uint32_t sr[kBN];
+                    uint32_t sr[kCols];
 #pragma unroll
-                    for (int cc = 0; cc < kBN / 32; ++cc) tmem_ld_x32(t_s + 32u * cc, sr + 32 * cc);
+                    for (int cc = 0; cc < kCols / 32; ++cc) tmem_ld_x32(t_s + 32u * cc, sr + 32 * cc);
                     tmem_wait_ld();
                     MQ_TRACE((warp & 3) == 0 && lane == 0, g, tile, 2);
                     if (!kAlias) {   // QK(g+1) may overwrite S now
@@ -460,9 +475,14 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
                         __syncwarp();
                         if (lane == 0) mbar_arrive(bar_s_empty);
                     }
-                    mask_kv_tail<kBN>(sr, valid);   // ragged KV tail: columns past n_kv get -inf
+                    mask_kv_tail<kCols>(sr, valid);   // ragged KV tail: columns past n_kv get -inf
                     if (need_max) {
-                        const float mx = row_max<kBN>(sr);
+                        float mx = row_max<kCols>(sr);
+                        if constexpr (kSplit > 1) {   // both halves continue with the row's max (identical rescale decisions)
+                            st_shared_f32(exch_addr(g & 1, half), mx);
+                            pair_sync();
+                            mx = fmaxf(mx, ld_shared_f32(exch_addr(g & 1, half ^ 1)));
+                        }
                         // lazy rescale decision (warp-uniform so the tcgen05.ld/st below stay aligned)
                         if (j == 0) {
                             m_used = mx;
@@ -484,7 +504,7 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
                     // what-if builds (WRONG results, timing decomposition only; LG_ATTN_TUNING_BUILD): 2 = no exponentials (one FFMA2 +
                     // pack per pair), 3 = no arithmetic at all ("skeleton": S load, P store, barriers, MMAs)
 #pragma unroll
-                    for (int cc = 0; cc < kBN; cc += 2) {
+                    for (int cc = 0; cc < kCols; cc += 2) {
 #if LG_ATTN_WHATIF == 2
                         float x0, x1;
                         unpack_f32x2(fma_f32x2(pack_f32x2(__uint_as_float(sr[cc]), __uint_as_float(sr[cc + 1])),
@@ -496,7 +516,7 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
                     }
                     tile_sum = 1.0f;
 #else
-                    tile_sum = softmax_exp_pass<kBN>(sr, pk, neg_m);
+                    tile_sum = softmax_exp_pass<kCols>(sr, pk, neg_m);
 #endif
                     if (kLazyMax && !need_max) {
                         // a probability >= 2^tau (the polynomial path saturates exactly there) shows in the row sum: the stale
@@ -522,9 +542,9 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
                     }
                 }
 #pragma unroll
-                for (int cc = 0; cc < kBN / 64; ++cc) tmem_st_x32(t_p + 32u * cc, pk + 32 * cc);
+                for (int cc = 0; cc < kCols / 64; ++cc) tmem_st_x32(t_p + 32u * cc, pk + 32 * cc);
                 if (rescale) {
-                    rescale_o_tmem<kHeadDim>(t_o, alpha);
+                    rescale_o_tmem<kOCols>(t_o, alpha);
                     l_sum *= alpha;
                 }
                 l_sum += tile_sum;
@@ -543,19 +563,24 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
                 if (lane == 0) mbar_arrive(bar_o_empty);
                 continue;
             }
-            uint32_t orow[kHeadDim];
-            tmem_ld_x32(t_o, orow);
-            tmem_ld_x32(t_o + 32u, orow + 32);
+            uint32_t orow[kOCols];
+#pragma unroll
+            for (int cc = 0; cc < kOCols / 32; ++cc) tmem_ld_x32(t_o + 32u * cc, orow + 32 * cc);
             tmem_wait_ld();
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(bar_o_empty);  // the next item's first PV may overwrite O now
+            if constexpr (kSplit > 1) {   // row sum = both halves' (the parity slot last written two steps ago is free)
+                st_shared_f32(exch_addr(g & 1, half), l_sum);
+                pair_sync();
+                l_sum += ld_shared_f32(exch_addr(g & 1, half ^ 1));
+            }
             const float inv_l = 1.0f / l_sum;
             const int row = (c.tile_m0 + tile) * kBlockM + (warp & 3) * 32 + lane;
             if (row < n_q) {
-                const long long off = c.bi * ol.sb + c.hi * ol.sh + row * ol.sr;
-                if constexpr (!kOutF32) store_o_row<false>(reinterpret_cast<__half*>(out) + off, orow, inv_l);
-                else store_o_row<true>(reinterpret_cast<float*>(out) + off, orow, inv_l);
+                const long long off = c.bi * ol.sb + c.hi * ol.sh + row * ol.sr + half * kOCols;
+                if constexpr (!kOutF32) store_o_row<false, kOCols>(reinterpret_cast<__half*>(out) + off, orow, inv_l);
+                else store_o_row<true, kOCols>(reinterpret_cast<float*>(out) + off, orow, inv_l);
             }
         }
     }

@@ -46,11 +46,11 @@ std::atomic<int> g_full_grid_kernel{-1};  // full grids: -1 = automatic, 0 = w4,
                                           // (LG_ATTN_FULL_GRID_KERNEL, lg_attn_debug_set_throughput_kernel: tests, A/B runs)
 
 // The multi-Q-tile kernel variants compiled into the library (lg_attn_debug_set_throughput_kernel modes 2, 3, ...).
-template <int T, int BN, bool A, bool L>
+template <int T, int BN, bool A, bool L, int S = 1>
 struct MqVariant {
-    static constexpr int kT = T, kBN = BN;
+    static constexpr int kT = T, kBN = BN, kSplit = S;
     static constexpr bool kAlias = A, kLazy = L;
-    using C = mq::Cfg<T, BN, A>;
+    using C = mq::Cfg<T, BN, A, S>;
 };
 constexpr int kMqModeBase = 1;
 template <typename F>
@@ -61,10 +61,16 @@ void mq_for_each_variant(F&& f) {
     f(MqVariant<4, 64, true, false>{});     // mode 3
     f(MqVariant<3, 64, false, false>{});    // mode 4
     f(MqVariant<3, 64, true, true>{});      // mode 5
+    // mode 6: mode 2's layout with two softmax warps per 32-row slab (64 of the step's 128 columns each, row max agreed through
+    // shared memory every step).  No softmax warp ever waits for the tensor pipe in this layout (phase trace: wait 44 clk / step),
+    // and it is still slower than mode 1 (879 vs 958 TFLOP/s at B64 N2048): the four softmax warps of a sub-partition already
+    // saturate its issue / FMA / MUFU pipes at ~600 clk per 64-column row slice, so hiding the S round trip buys nothing and the
+    // per-step row max (30 FMNMX3 + exchange) costs ~60 clk more.
+    f(MqVariant<2, 128, false, false, 2>{});
 #endif
 }
 #ifdef LG_ATTN_MQ_EXTRA_VARIANTS
-constexpr int kMqVariants = 5;
+constexpr int kMqVariants = 6;
 #else
 constexpr int kMqVariants = 2;
 #endif
@@ -237,8 +243,8 @@ int init_device_locked(int device) {
     opt_in(reinterpret_cast<const void*>(w4::lg_attn_hd64_fwd<true>), w4::kSmemBytes);
     mq_for_each_variant([&](auto v) {
         using V = decltype(v);
-        opt_in(reinterpret_cast<const void*>(mq::lg_attn_hd64_fwd<V::kT, V::kBN, V::kAlias, V::kLazy, false>), V::C::kSmemBytes);
-        opt_in(reinterpret_cast<const void*>(mq::lg_attn_hd64_fwd<V::kT, V::kBN, V::kAlias, V::kLazy, true>), V::C::kSmemBytes);
+        opt_in(reinterpret_cast<const void*>(mq::lg_attn_hd64_fwd<V::kT, V::kBN, V::kAlias, V::kLazy, false, V::kSplit>), V::C::kSmemBytes);
+        opt_in(reinterpret_cast<const void*>(mq::lg_attn_hd64_fwd<V::kT, V::kBN, V::kAlias, V::kLazy, true, V::kSplit>), V::C::kSmemBytes);
     });
     opt_in(reinterpret_cast<const void*>(w8::lg_attn_hd64_fwd<false, false>), w8::kSmemBytes);
     opt_in(reinterpret_cast<const void*>(w8::lg_attn_hd64_fwd<true, false>), w8::kSmemBytes);
@@ -368,8 +374,8 @@ static int launch_core(const void* qh, const void* kh, const void* vh, void* o, 
             cfg.attrs = attrs;
             cfg.numAttrs = 0;
             e = cudaLaunchKernelEx(&cfg,
-                                   !out_f32 ? mq::lg_attn_hd64_fwd<V::kT, V::kBN, V::kAlias, V::kLazy, false>
-                                            : mq::lg_attn_hd64_fwd<V::kT, V::kBN, V::kAlias, V::kLazy, true>,
+                                   !out_f32 ? mq::lg_attn_hd64_fwd<V::kT, V::kBN, V::kAlias, V::kLazy, false, V::kSplit>
+                                            : mq::lg_attn_hd64_fwd<V::kT, V::kBN, V::kAlias, V::kLazy, true, V::kSplit>,
                                    tm_q, tm_k, tm_v, o, n_q, n_kv, sc, ol);
         });
         if (rc != 0) return rc;
