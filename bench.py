@@ -502,13 +502,20 @@ def beside_section(pkg, torch, lib, q, k, v, o) -> dict:
            "method": "chained = us/problem in a CUDA-graph chain of independent problems (ours: PDL lets neighbours overlap = pipelined throughput); "
                      "serialized = the same chain with PDL off: each call starts when its predecessor has finished = latency of one dependent call "
                      "inside a graph; isolated = median us between two CUDA events around ONE stream launch behind a busy predecessor "
-                     "(adds the front end's launch latency, ~10 us for every kernel here)",
+                     "(adds the front end's launch latency; isolated_method_floor_us = the same measurement of a one-row problem)",
            "ours_chained_us": time_graph_chain(torch, ours, calls), "ours_isolated_us": isolated_latency_us(torch, ours, calls)}
     lib.lg_attn_debug_set_pdl(0)
     try:
         out["ours_serialized_us"] = time_graph_chain(torch, ours, calls)
     finally:
         lib.lg_attn_debug_set_pdl(1)
+
+    def floor(i, s):   # the same kernel on a one-row problem: what the "isolated" method costs before any work is done
+        rc = lib.lg_attn_hd64_launch(q[i].data_ptr(), k[i].data_ptr(), v[i].data_ptr(), o[i].data_ptr(), 1, 1, 1, 1, pkg.F16_F16, None, 0, s)
+        if rc != 0:
+            raise RuntimeError(pkg._binding.error_string(rc))
+
+    out["isolated_method_floor_us"] = isolated_latency_us(torch, floor, calls)
     ref = load_ref_kernels()
     if ref is None:
         out["ref_kernel"] = "skipped: oracle/_ref/libref_attn.so not built"
