@@ -112,6 +112,14 @@ int lg_attn_session_create(lg_attn_session** out, int device, int max_batch, int
                            int io_dtype, int n_slots);
 int lg_attn_session_submit(lg_attn_session* s, const void* q_host, const void* k_host, const void* v_host,
                            void* o_host, int batch, int n_q, int n_kv);
+/* `count` problems of one shape in one call.  Problem p reads q at q_host + p * q_stride_bytes, k / v at their pointers +
+ * p * kv_stride_bytes, and writes o at o_host + p * out_stride_bytes.  When the host arrays are packed like the session's device slots — [q | k | v] per problem back to
+ * back, outputs dense, shape = the create-time maxima — `group` consecutive problems (default 4, at most n_slots / 2) move with ONE
+ * H2D and ONE D2H transfer (1.5 MiB copies reach ~42 GB/s of this box's PCIe link beside the return traffic, 6 MiB copies ~49) and
+ * are launched one by one; any other layout falls back to lg_attn_session_submit() per problem.  Asynchronous like submit(). */
+int lg_attn_session_submit_many(lg_attn_session* s, const void* q_host, const void* k_host, const void* v_host, void* o_host,
+                                int count, size_t q_stride_bytes, size_t kv_stride_bytes, size_t out_stride_bytes, int group, int batch,
+                                int n_q, int n_kv);
 int lg_attn_session_sync(lg_attn_session* s);
 void lg_attn_session_destroy(lg_attn_session* s);
 

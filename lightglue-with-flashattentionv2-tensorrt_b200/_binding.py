@@ -43,6 +43,7 @@ C_ABI_SYMBOLS = (
     "lg_attn_error_string",
     "lg_attn_session_create",
     "lg_attn_session_submit",
+    "lg_attn_session_submit_many",
     "lg_attn_session_sync",
     "lg_attn_session_destroy",
 )
@@ -150,6 +151,8 @@ def load() -> ctypes.CDLL:
     lib.lg_attn_session_create.argtypes = [ctypes.POINTER(ctypes.c_void_p)] + [ctypes.c_int] * 7
     lib.lg_attn_session_submit.restype = ctypes.c_int
     lib.lg_attn_session_submit.argtypes = [ctypes.c_void_p] * 5 + [ctypes.c_int] * 3
+    lib.lg_attn_session_submit_many.restype = ctypes.c_int
+    lib.lg_attn_session_submit_many.argtypes = [ctypes.c_void_p] * 5 + [ctypes.c_int] + [ctypes.c_size_t] * 3 + [ctypes.c_int] * 4
     lib.lg_attn_session_sync.restype = ctypes.c_int
     lib.lg_attn_session_sync.argtypes = [ctypes.c_void_p]
     lib.lg_attn_session_destroy.restype = None

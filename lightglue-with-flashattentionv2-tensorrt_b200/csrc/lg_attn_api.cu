@@ -633,6 +633,11 @@ struct lg_attn_session {
     cudaEvent_t* ev_run = nullptr;   // [slot] kernel done: inputs consumed, output written
     cudaEvent_t* ev_out = nullptr;   // [slot] output copied out: the slot's output buffer may be rewritten
     unsigned long long next = 0;
+    // pool layout: [n_slots x (q | k | v)] then [n_slots x o] — consecutive slots are contiguous on the device, so a packed group of
+    // problems moves with ONE copy each way (lg_attn_session_submit_many)
+    size_t in_bytes() const { return q_bytes + 2 * kv_bytes; }
+    uint8_t* slot_in(int i) const { return pool + in_bytes() * static_cast<size_t>(i); }
+    uint8_t* slot_out(int i) const { return pool + in_bytes() * static_cast<size_t>(n_slots) + o_bytes * static_cast<size_t>(i); }
 };
 
 int lg_attn_session_create(lg_attn_session** out, int device, int max_batch, int heads, int max_n_q, int max_n_kv,
@@ -684,11 +689,10 @@ int lg_attn_session_submit(lg_attn_session* s, const void* q_host, const void* k
     const unsigned long long k = s->next++;
     const int i = static_cast<int>(k % static_cast<unsigned long long>(s->n_slots));
     const bool reused = k >= static_cast<unsigned long long>(s->n_slots);
-    const size_t slot = s->q_bytes + 2 * s->kv_bytes + s->o_bytes;
-    uint8_t* dq = s->pool + slot * i;
+    uint8_t* dq = s->slot_in(i);
     uint8_t* dk = dq + s->q_bytes;
     uint8_t* dv = dk + s->kv_bytes;
-    uint8_t* dout = dv + s->kv_bytes;
+    uint8_t* dout = s->slot_out(i);
     const size_t in_es = (s->io_dtype == LG_ATTN_F32_F32) ? 4 : 2;
     const size_t out_es = (s->io_dtype == LG_ATTN_F16_F16) ? 2 : 4;
     const size_t bh = static_cast<size_t>(batch) * s->heads;
@@ -720,6 +724,71 @@ int lg_attn_session_submit(lg_attn_session* s, const void* q_host, const void* k
     if (e == cudaSuccess) e = cudaMemcpyAsync(o_host, dout, bh * n_q * kHeadDim * out_es, cudaMemcpyDeviceToHost, s->s_out);
     if (e == cudaSuccess) e = cudaEventRecord(s->ev_out[i], s->s_out);
     return static_cast<int>(e);
+}
+
+int lg_attn_session_submit_many(lg_attn_session* s, const void* q_host, const void* k_host, const void* v_host, void* o_host,
+                                int count, size_t q_stride_bytes, size_t kv_stride_bytes, size_t out_stride_bytes, int group, int batch,
+                                int n_q, int n_kv) {
+    if (s == nullptr || q_host == nullptr || k_host == nullptr || v_host == nullptr || o_host == nullptr || count <= 0)
+        return LG_ATTN_EINVAL;
+    if (batch <= 0 || batch > s->max_batch || n_q <= 0 || n_q > s->max_n_q || n_kv <= 0 || n_kv > s->max_n_kv)
+        return LG_ATTN_EINVAL;
+    const size_t in_es = (s->io_dtype == LG_ATTN_F32_F32) ? 4 : 2;
+    const size_t out_es = (s->io_dtype == LG_ATTN_F16_F16) ? 2 : 4;
+    const size_t bh = static_cast<size_t>(batch) * s->heads;
+    const size_t qb = bh * n_q * kHeadDim * in_es, kvb = bh * n_kv * kHeadDim * in_es, ob = bh * n_q * kHeadDim * out_es;
+    const uint8_t* q8 = static_cast<const uint8_t*>(q_host);
+    const uint8_t* k8 = static_cast<const uint8_t*>(k_host);
+    const uint8_t* v8 = static_cast<const uint8_t*>(v_host);
+    uint8_t* o8 = static_cast<uint8_t*>(o_host);
+    // packed = the host arrays are laid out exactly like `count` consecutive device slots: [q | k | v] per problem, outputs dense
+    const size_t in_stride_bytes = q_stride_bytes;
+    const bool packed = k8 == q8 + qb && v8 == k8 + kvb && q_stride_bytes == qb + 2 * kvb && kv_stride_bytes == q_stride_bytes && out_stride_bytes == ob &&
+                        qb == s->q_bytes && kvb == s->kv_bytes && ob == s->o_bytes;
+    if (group <= 0) group = 4;
+    if (group > s->n_slots / 2) group = s->n_slots / 2;   // at least two groups of slots in flight
+    if (!packed || group <= 1) {
+        for (int p = 0; p < count; ++p) {
+            const int rc = lg_attn_session_submit(s, q8 + p * q_stride_bytes, k8 + p * kv_stride_bytes, v8 + p * kv_stride_bytes,
+                                                  o8 + p * out_stride_bytes, batch, n_q, n_kv);
+            if (rc != 0) return rc;
+        }
+        return 0;
+    }
+    cudaError_t e = cudaSetDevice(s->device);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    for (int done = 0; done < count;) {
+        const int i0 = static_cast<int>(s->next % static_cast<unsigned long long>(s->n_slots));
+        int g = group < count - done ? group : count - done;
+        if (g > s->n_slots - i0) g = s->n_slots - i0;   // a group never wraps around the pool
+        // ---- ONE H2D copy for the group: every slot's previous kernel must have consumed its inputs
+        for (int j = 0; j < g && e == cudaSuccess; ++j)
+            if (s->next + j >= static_cast<unsigned long long>(s->n_slots)) e = cudaStreamWaitEvent(s->s_in, s->ev_run[i0 + j], 0);
+        if (e == cudaSuccess)
+            e = cudaMemcpyAsync(s->slot_in(i0), q8 + done * in_stride_bytes, g * in_stride_bytes, cudaMemcpyHostToDevice, s->s_in);
+        if (e == cudaSuccess) e = cudaEventRecord(s->ev_in[i0], s->s_in);
+        // ---- g launches (one problem each, as the plugin would enqueue them): inputs landed, previous outputs copied out
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(s->s_run, s->ev_in[i0], 0);
+        for (int j = 0; j < g && e == cudaSuccess; ++j)
+            if (s->next + j >= static_cast<unsigned long long>(s->n_slots)) e = cudaStreamWaitEvent(s->s_run, s->ev_out[i0 + j], 0);
+        if (e != cudaSuccess) return static_cast<int>(e);
+        for (int j = 0; j < g; ++j) {
+            uint8_t* dq = s->slot_in(i0 + j);
+            const int rc = lg_attn_hd64_launch(dq, dq + s->q_bytes, dq + s->q_bytes + s->kv_bytes, s->slot_out(i0 + j), batch, s->heads, n_q,
+                                               n_kv, s->io_dtype, nullptr, 0, s->s_run);
+            if (rc != 0) return rc;
+        }
+        for (int j = 0; j < g && e == cudaSuccess; ++j) e = cudaEventRecord(s->ev_run[i0 + j], s->s_run);
+        // ---- ONE D2H copy for the group
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(s->s_out, s->ev_run[i0 + g - 1], 0);
+        if (e == cudaSuccess)
+            e = cudaMemcpyAsync(o8 + done * out_stride_bytes, s->slot_out(i0), g * out_stride_bytes, cudaMemcpyDeviceToHost, s->s_out);
+        for (int j = 0; j < g && e == cudaSuccess; ++j) e = cudaEventRecord(s->ev_out[i0 + j], s->s_out);
+        if (e != cudaSuccess) return static_cast<int>(e);
+        s->next += static_cast<unsigned long long>(g);
+        done += g;
+    }
+    return 0;
 }
 
 int lg_attn_session_sync(lg_attn_session* s) {

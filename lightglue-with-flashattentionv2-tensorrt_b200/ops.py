@@ -144,6 +144,13 @@ class HostSession:
         B.check(self._lib.lg_attn_session_submit(self._h, q_ptr, k_ptr, v_ptr, o_ptr, batch, n_q, n_kv),
                 "lg_attn_session_submit")
 
+    def submit_many(self, q_ptr: int, k_ptr: int, v_ptr: int, o_ptr: int, count: int, q_stride: int, kv_stride: int, out_stride: int,
+                    batch: int, n_q: int, n_kv: int, group: int = 4) -> None:
+        """``count`` same-shape problems; packed host arrays ([q | k | v] per problem, dense outputs) move ``group`` problems per
+        PCIe transfer each way (``lg_attn_session_submit_many``)."""
+        B.check(self._lib.lg_attn_session_submit_many(self._h, q_ptr, k_ptr, v_ptr, o_ptr, count, q_stride, kv_stride, out_stride, group, batch,
+                                                      n_q, n_kv), "lg_attn_session_submit_many")
+
     def sync(self) -> None:
         B.check(self._lib.lg_attn_session_sync(self._h), "lg_attn_session_sync")
 

@@ -239,6 +239,46 @@ def test_host_buffer_entry(pkg):
     assert orc.rel_err(of, orc.attention_np(q, k, v)) <= orc.TOL_F32_REL
 
 
+def test_host_session_submit_many_coalesced_and_fallback(pkg):
+    """lg_attn_session_submit_many: packed host arrays move `group` problems per transfer (slots wrap, groups never do), any other
+    layout falls back to per-problem submits; mixed with plain submit() the slot bookkeeping stays consistent.  Every output must
+    equal the device-resident call bit for bit."""
+    b, h, n, m, count = 1, 4, 200, 200, 11
+    qkv = torch.randn(count, 3, b, h, n, 64).half().pin_memory()
+    out = torch.zeros(count, b, h, n, 64, dtype=torch.float16).pin_memory()
+    es = b * h * n * 64 * 2
+    want = [pkg.attention(*(qkv[i, j].cuda() for j in range(3))).cpu() for i in range(count)]
+    for slots, group in ((6, 3), (8, 4), (4, 1), (5, 2)):
+        sess = pkg.HostSession(b, h, n, m, pkg.F16_F16, n_slots=slots, device=0)
+        for rep in range(2):   # second pass reuses every slot
+            out.zero_()
+            base = qkv.data_ptr()
+            sess.submit(base, base + es, base + 2 * es, out.data_ptr(), b, n, m)   # problem 0 alone, then the rest as one call
+            sess.submit_many(base + 3 * es, base + 4 * es, base + 5 * es, out.data_ptr() + es, count - 1, 3 * es, 3 * es, es, b, n, m, group=group)
+            sess.sync()
+            for i in range(count):
+                assert torch.equal(out[i], want[i]), (slots, group, rep, i)
+        sess.close()
+    # not packed (q, k, v in separate arrays): per-problem fallback, same results
+    qs, ks, vs = (qkv[:, j].contiguous().pin_memory() for j in range(3))
+    sess = pkg.HostSession(b, h, n, m, pkg.F16_F16, n_slots=6, device=0)
+    out.zero_()
+    sess.submit_many(qs.data_ptr(), ks.data_ptr(), vs.data_ptr(), out.data_ptr(), count, es, es, es, b, n, m, group=3)
+    sess.sync()
+    for i in range(count):
+        assert torch.equal(out[i], want[i]), i
+    # a smaller shape than the session's maxima is never "packed like the slots": fallback again
+    m2 = m - 7
+    q2 = torch.randn(2, b, h, n, 64).half().pin_memory()
+    k2 = torch.randn(2, b, h, m2, 64).half().pin_memory()
+    v2 = torch.randn(2, b, h, m2, 64).half().pin_memory()
+    sess.submit_many(q2.data_ptr(), k2.data_ptr(), v2.data_ptr(), out.data_ptr(), 2, es, b * h * m2 * 64 * 2, es, b, n, m2, group=3)
+    sess.sync()
+    for i in range(2):
+        assert torch.equal(out[i], pkg.attention(q2[i].cuda(), k2[i].cuda(), v2[i].cuda()).cpu())
+    sess.close()
+
+
 def test_kfloat_branch_is_one_launch_without_workspace(pkg):
     """Row a6: the plugin's kFLOAT branch (FP32 tensors at the boundary) runs as ONE launch with no scratch — the FP32 -> FP16
     conversion (round to nearest, like QKV_convert_from_fp32_to_fp16, …fp32out.cu:706-768) happens on the way into shared memory.

@@ -17,7 +17,7 @@ ROOT = Path(__file__).resolve().parent.parent
 H2D, D2H, CALLS, FLOPS = 3 * 4 * 1024 * 64 * 2, 4 * 1024 * 64 * 2, 128, 4.0 * 4 * 1024 * 1024 * 64
 
 
-def worker(rank: int, world: int, steps: int) -> None:
+def worker(rank: int, world: int, steps: int, group: int = 1) -> None:
     import torch
 
     torch.cuda.set_device(rank)
@@ -25,16 +25,16 @@ def worker(rank: int, world: int, steps: int) -> None:
     src = torch.empty(CALLS, H2D, dtype=torch.uint8).pin_memory()
     dst_h = torch.empty(CALLS, D2H, dtype=torch.uint8).pin_memory()
     slots = 4
-    d_in = [torch.empty(H2D, dtype=torch.uint8, device=dev) for _ in range(slots)]
-    d_out = [torch.empty(D2H, dtype=torch.uint8, device=dev) for _ in range(slots)]
+    d_in = [torch.empty(group, H2D, dtype=torch.uint8, device=dev) for _ in range(slots)]
+    d_out = [torch.empty(group, D2H, dtype=torch.uint8, device=dev) for _ in range(slots)]
     streams = [torch.cuda.Stream(dev) for _ in range(slots)]
 
-    def step():
-        for i in range(CALLS):
-            s = i % slots
+    def step():   # `group` problems per transfer each way (bench.py's e2e leg: LG_E2E_GROUP)
+        for j, i in enumerate(range(0, CALLS, group)):
+            s = j % slots
             with torch.cuda.stream(streams[s]):
-                d_in[s].copy_(src[i], non_blocking=True)
-                dst_h[i].copy_(d_out[s], non_blocking=True)
+                d_in[s].copy_(src[i:i + group], non_blocking=True)
+                dst_h[i:i + group].copy_(d_out[s], non_blocking=True)
         torch.cuda.synchronize(dev)
 
     for _ in range(3):
@@ -57,22 +57,23 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--worker", type=int, default=-1)
     ap.add_argument("--world", type=int, default=1)
+    ap.add_argument("--group", type=int, default=4, help="problems per transfer (bench.py moves LG_E2E_GROUP = 4 per copy)")
     args = ap.parse_args()
     if args.worker >= 0:
-        worker(args.worker, args.world, args.steps)
+        worker(args.worker, args.world, args.steps, args.group)
         return
     import tempfile
 
     for world in [n for n in (1, 2, 4, 8) if n <= args.gpus]:
         with tempfile.TemporaryDirectory() as d:
             env = dict(os.environ, PROBE_DIR=d)
-            procs = [subprocess.Popen([sys.executable, __file__, "--worker", str(r), "--world", str(world), "--steps", str(args.steps)],
+            procs = [subprocess.Popen([sys.executable, __file__, "--worker", str(r), "--world", str(world), "--steps", str(args.steps), "--group", str(args.group)],
                                       env=env, stdout=subprocess.PIPE, text=True) for r in range(world)]
             outs = [json.loads(p.communicate()[0].strip().splitlines()[-1]) for p in procs]
         slowest = max(o["seconds"] for o in outs)
         problems = sum(o["problems"] for o in outs)
         gbs = problems * (H2D + D2H) / slowest / 1e9
-        print(json.dumps({"n_gpus": world, "copy_only_GBps_aggregate": round(gbs, 1), "h2d_GBps": round(problems * H2D / slowest / 1e9, 1),
+        print(json.dumps({"n_gpus": world, "problems_per_transfer": args.group, "copy_only_GBps_aggregate": round(gbs, 1), "h2d_GBps": round(problems * H2D / slowest / 1e9, 1),
                           "d2h_GBps": round(problems * D2H / slowest / 1e9, 1), "problems_per_s": round(problems / slowest),
                           "equivalent_e2e_tflops_if_copy_bound": round(problems / slowest * FLOPS / 1e12, 1)}), flush=True)
 
