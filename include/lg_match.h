@@ -55,6 +55,21 @@ int lg_match_assign(const float* sim, const void* z0_half, const void* z1_half, 
                     int batch, int n0, int n1, float threshold, int* matches0, float* mscores0,
                     float* scores, void* workspace, size_t workspace_bytes, void* stream);
 
+/* lg_match_assign for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  No counterpart in the reference.
+ * Same inputs, outputs and kernels as lg_match_assign; the scratch is a file-scope device array of
+ * LG_MATCH_ASSIGN_STATIC_MAX_BYTES (4 MiB) inside the library — every GPU that loads the library holds it until exit.  The call
+ * allocates and frees nothing (first call per device: one cudaGetSymbolAddress lookup, cached).
+ * Limit: lg_match_assign_workspace_bytes(batch, n0, n1) <= LG_MATCH_ASSIGN_STATIC_MAX_BYTES (fits e.g. 64 pairs of 1024 x 1024
+ * keypoints, 16 of 2048 x 2048, 4 of 4096 x 4096); larger shapes return LG_MATCH_ESTATIC_TOO_LARGE and launch nothing — use lg_match_assign with caller memory.
+ * All calls on a device share the one array: calls that may overlap on the GPU (different streams without an ordering between
+ * them) race on it and must be serialised by the caller; nothing in it needs clearing between calls. */
+#define LG_MATCH_ASSIGN_STATIC_MAX_BYTES 4194304
+#define LG_MATCH_ESTATIC_TOO_LARGE 100012 /* shape needs more scratch than LG_MATCH_ASSIGN_STATIC_MAX_BYTES */
+int lg_match_assign_static(const float* sim, const void* z0_half, const void* z1_half, long long z_stride,
+                           int batch, int n0, int n1, float threshold, int* matches0, float* mscores0,
+                           float* scores, void* stream);
+
 /* Number of kernels each entry enqueues (for the bench's gpu_launches accounting). */
 int lg_match_assign_launches(int with_scores);
 

@@ -54,6 +54,7 @@ MATCH_ABI_SYMBOLS = (
     "lg_match_layernorm_gelu",
     "lg_match_assign_workspace_bytes",
     "lg_match_assign",
+    "lg_match_assign_static",
     "lg_match_assign_launches",
 )
 
@@ -72,6 +73,8 @@ MATCHER_ABI_SYMBOLS = (
 )
 ECUBLAS = 100010
 EBLOB = 100011
+ESTATIC_TOO_LARGE = 100012
+ASSIGN_STATIC_MAX_BYTES = 4194304
 
 _lib = None
 
@@ -168,6 +171,8 @@ def load() -> ctypes.CDLL:
     lib.lg_match_assign_workspace_bytes.argtypes = [I, I, I]
     lib.lg_match_assign.restype = I
     lib.lg_match_assign.argtypes = [P, P, P, LL, I, I, I, F, P, P, P, P, ctypes.c_size_t, P]
+    lib.lg_match_assign_static.restype = I
+    lib.lg_match_assign_static.argtypes = [P, P, P, LL, I, I, I, F, P, P, P, P]
     lib.lg_match_assign_launches.restype = I
     lib.lg_match_assign_launches.argtypes = [I]
     lib.lg_matcher_create.restype = I

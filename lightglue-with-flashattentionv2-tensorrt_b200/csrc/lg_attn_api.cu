@@ -823,6 +823,7 @@ const char* lg_attn_error_string(int code) {
         case LG_ATTN_EARCH: return "lg_attn: device is not compute capability 10.x (sm_100a required)";
         case 100010: return "lg_matcher: a cuBLASLt call failed";
         case 100011: return "lg_matcher: malformed weight blob";
+        case 100012: return "lg_match_assign_static: shape needs more scratch than LG_MATCH_ASSIGN_STATIC_MAX_BYTES (4 MiB); use lg_match_assign";
         default: return cudaGetErrorString(static_cast<cudaError_t>(code));
     }
 }

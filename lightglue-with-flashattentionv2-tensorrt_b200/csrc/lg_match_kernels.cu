@@ -14,6 +14,9 @@
 #include <math.h>
 #include <stdint.h>
 
+#include <atomic>
+#include <mutex>
+
 #include "../../include/lg_attn.h"
 #include "../../include/lg_match.h"
 
@@ -459,6 +462,56 @@ size_t lg_match_assign_workspace_bytes(int batch, int n0, int n1) {
 }
 
 int lg_match_assign_launches(int with_scores) { return with_scores ? 8 : 7; }
+
+// ---- lg_match_assign_static: the same assignment with its scratch in a file-scope device array (no allocation anywhere) --------
+// Every GPU that loads the library holds these LG_MATCH_ASSIGN_STATIC_MAX_BYTES until exit.  In host code `g_assign_scratch` is a
+// host-side stand-in for the symbol, NOT a device address: the kernels get the address cudaGetSymbolAddress returns, resolved once
+// per device (with that device current) and cached.
+static __device__ __align__(256) unsigned char g_assign_scratch[LG_MATCH_ASSIGN_STATIC_MAX_BYTES];
+
+namespace {
+constexpr int kMaxScratchDevices = 64;
+void* g_assign_scratch_ptr[kMaxScratchDevices];                 // device address of g_assign_scratch on device i
+std::atomic<int> g_assign_scratch_state[kMaxScratchDevices];    // 0 = unresolved, 1 = resolved (release / acquire publishes the pointer)
+std::mutex g_assign_scratch_mutex;
+
+// Device address of the scratch array on the CURRENT device.  First call per device: cudaGetSymbolAddress (a lookup, not an
+// allocation: the array is part of the loaded module's image).
+int assign_scratch_address(void** out) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    if (dev < 0 || dev >= kMaxScratchDevices) return LG_ATTN_EINVAL;
+    if (g_assign_scratch_state[dev].load(std::memory_order_acquire) == 0) {
+        std::lock_guard<std::mutex> lock(g_assign_scratch_mutex);
+        if (g_assign_scratch_state[dev].load(std::memory_order_relaxed) == 0) {
+            void* p = nullptr;
+            e = cudaGetSymbolAddress(&p, g_assign_scratch);
+            if (e != cudaSuccess) return static_cast<int>(e);
+            if (p == nullptr || (reinterpret_cast<uintptr_t>(p) & 255u) != 0) return LG_ATTN_EINVAL;
+            g_assign_scratch_ptr[dev] = p;
+            g_assign_scratch_state[dev].store(1, std::memory_order_release);
+        }
+    }
+    *out = g_assign_scratch_ptr[dev];
+    return 0;
+}
+}  // namespace
+
+int lg_match_assign_static(const float* sim, const void* z0_half, const void* z1_half, long long z_stride, int batch, int n0,
+                           int n1, float threshold, int* matches0, float* mscores0, float* scores, void* stream) {
+    if (batch <= 0 || n0 <= 0 || n1 <= 0) return LG_ATTN_EINVAL;
+    // the size check comes first and needs no device: shapes beyond the fixed array are refused, never truncated
+    const size_t need = lg_match_assign_workspace_bytes(batch, n0, n1);
+    if (need > static_cast<size_t>(LG_MATCH_ASSIGN_STATIC_MAX_BYTES)) return LG_MATCH_ESTATIC_TOO_LARGE;
+    void* scratch = nullptr;
+    const int rc = assign_scratch_address(&scratch);
+    if (rc != 0) return rc;
+    // Nothing in the scratch has to start at zero: within one call every word (row / column terms, arg-max indices, the column
+    // partial planes) is written by an earlier kernel of the call before a later one reads it, and no kernel accumulates into it —
+    // so the previous call's contents are simply overwritten.  Two calls that overlap on the GPU (different streams) race on it.
+    return lg_match_assign(sim, z0_half, z1_half, z_stride, batch, n0, n1, threshold, matches0, mscores0, scores, scratch, need, stream);
+}
 
 int lg_match_assign(const float* sim, const void* z0_half, const void* z1_half, long long z_stride, int batch, int n0,
                     int n1, float threshold, int* matches0, float* mscores0, float* scores, void* workspace,

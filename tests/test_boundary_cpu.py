@@ -54,6 +54,8 @@ def test_glue_header_symbols_are_exported(pkg, lib):
     assert lib.lg_match_assign_workspace_bytes(2, 300, 200) >= 4 * 2 * (3 * 300 + 2 * 200)
     one = ctypes.c_void_p(256)
     assert lib.lg_match_assign(one, one, one, 1, 1, 8, 8, 0.1, one, one, None, None, 0, None) == pkg._binding.EWORKSPACE
+    # the no-allocation variant refuses shapes beyond its fixed scratch before it touches any device
+    assert lib.lg_match_assign_static(one, one, one, 1, 128, 1024, 1024, 0.1, one, one, None, None) == pkg._binding.ESTATIC_TOO_LARGE
     assert lib.lg_match_assign_launches(0) == 7 and lib.lg_match_assign_launches(1) == 8
 
 
