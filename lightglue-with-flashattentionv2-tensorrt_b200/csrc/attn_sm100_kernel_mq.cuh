@@ -109,7 +109,9 @@ struct Cfg {
     static constexpr uint32_t kSmemQ = 0;
     static constexpr uint32_t kSmemK = kSmemQ + kT * kQBytes;
     static constexpr uint32_t kSmemV = kSmemK + kStages * kKVBytes;
-    static constexpr uint32_t kSmemBar = kSmemV + kStages * kKVBytes;
+    // FP16 output: one 128-row x 128-B staging tile per Q tile for the epilogue's TMA store (same 128-byte swizzle as the loads)
+    static constexpr uint32_t kSmemO = kSmemV + kStages * kKVBytes;
+    static constexpr uint32_t kSmemBar = kSmemO + kT * kQBytes;
     // barriers (8 bytes each): per tile 7, ring 4 * kStages
     static constexpr uint32_t kBarQFull = 0, kBarQEmpty = kT, kBarSFull = 2 * kT, kBarSEmpty = 3 * kT, kBarPFull = 4 * kT,
                               kBarPVDone = 5 * kT, kBarOEmpty = 6 * kT, kBarKFull = 7 * kT, kBarKEmpty = kBarKFull + kStages,
@@ -177,8 +179,8 @@ __device__ __forceinline__ Item item_coord(int w, const Sched& sc, const OutLayo
 template <int kT, int kBN, bool kAlias, bool kLazyMax, bool kOutF32, int kSplit = 1>
 __global__ void __launch_bounds__(Cfg<kT, kBN, kAlias, kSplit>::kThreads, 1)
 lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
-                 const __grid_constant__ CUtensorMap tm_v, void* __restrict__ out, int n_q, int n_kv, const Sched sc,
-                 const OutLayout ol) {
+                 const __grid_constant__ CUtensorMap tm_v, const __grid_constant__ CUtensorMap tm_o, void* __restrict__ out, int n_q,
+                 int n_kv, const Sched sc, const OutLayout ol, int tma_store) {
     using C = Cfg<kT, kBN, kAlias, kSplit>;
     static_assert(!kLazyMax || kAlias, "the lazy row max re-reads S from TMEM: S must survive until P is stored");
     extern __shared__ uint8_t smem_raw[];
@@ -577,7 +579,47 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
             }
             const float inv_l = 1.0f / l_sum;
             const int row = (c.tile_m0 + tile) * kBlockM + (warp & 3) * 32 + lane;
+            if constexpr (!kOutF32 && kSplit == 1) {
+                if (tma_store) {
+                    // FP16 output through shared memory and ONE TMA store per Q tile.  A thread owns a whole output row, so direct
+                    // stores are 16 B per lane at a 128-B stride: 32 LSU wavefronts per instruction, ~4 000 per item, with all 16
+                    // softmax warps of the CTA in their epilogues at the same time (measured: 1.4 us per item, 12 % of a launch at
+                    // N = M = 512).  The staging tile is written with the loads' 128-byte swizzle (4 wavefronts per instruction), the
+                    // tile's four warps meet on a named barrier, one elected thread issues the store; rows past n_q are clipped
+                    // by the tensor map.  The store of item i is waited for (source read) in front of the writes of item i + 1.
+                    const bool issuer = (warp & 3) == 0;
+                    if (issuer) {
+                        if (elect_one()) bulk_wait_group_read0();
+                        __syncwarp();
+                    }
+                    named_bar_sync(1u + static_cast<uint32_t>(tile), 128u);
+                    const int r_in = (warp & 3) * 32 + lane;
+                    const uint32_t stg = smem + C::kSmemO + static_cast<uint32_t>(tile) * C::kQBytes + static_cast<uint32_t>(r_in) * 128u;
+#pragma unroll
+                    for (int cc = 0; cc < 8; ++cc)
+                        st_shared_v4(stg + (static_cast<uint32_t>(cc ^ (r_in & 7)) << 4),
+                                     pack_half2(__uint_as_float(orow[8 * cc + 0]) * inv_l, __uint_as_float(orow[8 * cc + 1]) * inv_l),
+                                     pack_half2(__uint_as_float(orow[8 * cc + 2]) * inv_l, __uint_as_float(orow[8 * cc + 3]) * inv_l),
+                                     pack_half2(__uint_as_float(orow[8 * cc + 4]) * inv_l, __uint_as_float(orow[8 * cc + 5]) * inv_l),
+                                     pack_half2(__uint_as_float(orow[8 * cc + 6]) * inv_l, __uint_as_float(orow[8 * cc + 7]) * inv_l));
+                    fence_proxy_async_smem();
+                    named_bar_sync(1u + static_cast<uint32_t>(tile), 128u);
+                    if (issuer) {
+                        if (elect_one()) {
+                            tma_store_4d(&tm_o, smem + C::kSmemO + static_cast<uint32_t>(tile) * C::kQBytes, 0, (c.tile_m0 + tile) * kBlockM,
+                                         c.hi, c.bi);
+                            bulk_commit_group();
+                        }
+                        __syncwarp();
+                    }
+                    continue;
+                }
+            }
+#ifdef LG_ATTN_WHATIF_NOSTORE   // what-if build (WRONG results, LG_ATTN_TUNING_BUILD): what the per-thread row stores of the epilogue cost
+            if (row < n_q && inv_l == 123.f) {
+#else
             if (row < n_q) {
+#endif
                 const long long off = c.bi * ol.sb + c.hi * ol.sh + row * ol.sr + half * kOCols;
                 if constexpr (!kOutF32) store_o_row<false, kOCols>(reinterpret_cast<__half*>(out) + off, orow, inv_l);
                 else store_o_row<true, kOCols>(reinterpret_cast<float*>(out) + off, orow, inv_l);
@@ -585,6 +627,13 @@ lg_attn_hd64_fwd(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
         }
     }
 
+    if constexpr (!kOutF32 && kSplit == 1) {
+        // the staging tiles must outlive the stores that read them
+        if (warp < C::kSoftmaxWarps && (warp & 3) == 0 && tma_store) {
+            if (elect_one()) bulk_wait_group_read0();
+            __syncwarp();
+        }
+    }
     tc_fence_before();
     __syncthreads();
     if (warp == kWarpAlloc) {

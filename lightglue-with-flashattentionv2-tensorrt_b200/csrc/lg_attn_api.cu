@@ -41,6 +41,7 @@ int g_sm_count[kMaxDevices];              // written once per device under g_ini
 int g_max_clusters[kMaxDevices][4];       // co-resident clusters of 1 << i CTAs (same publication rule)
 int g_max_clusters_f32[kMaxDevices][4];   // same for the FP32-input instantiation (1 CTA per SM)
 std::atomic<int> g_forced_splits{0};      // tuning override (LG_ATTN_SPLITS), 0 = automatic
+std::atomic<int> g_mq_tma_store{1};       // LG_ATTN_MQ_TMA_STORE=0: the multi-Q-tile kernel's FP16 epilogue stores rows per thread (A/B runs)
 std::atomic<int> g_use_pdl{1};            // LG_ATTN_PDL=0 disables programmatic dependent launch
 std::atomic<int> g_full_grid_kernel{-1};  // full grids: -1 = automatic, 0 = w4, 1 = mq (4 Q tiles), 2 = mq (2 Q tiles)
                                           // (LG_ATTN_FULL_GRID_KERNEL, lg_attn_debug_set_throughput_kernel: tests, A/B runs)
@@ -220,6 +221,7 @@ int init_device_locked(int device) {
         const int v = atoi(env);
         if (v == 1 || v == 2 || v == 4 || v == 8) g_forced_splits.store(v, std::memory_order_relaxed);
     }
+    if (const char* env = getenv("LG_ATTN_MQ_TMA_STORE")) g_mq_tma_store.store(atoi(env) != 0 ? 1 : 0, std::memory_order_relaxed);
     if (const char* env = getenv("LG_ATTN_PDL")) g_use_pdl.store(atoi(env) != 0 ? 1 : 0, std::memory_order_relaxed);
     if (const char* env = getenv("LG_ATTN_FULL_GRID_KERNEL")) {
         const int v = atoi(env);
@@ -368,6 +370,13 @@ static int launch_core(const void* qh, const void* kh, const void* vh, void* o, 
             }
             const mq::Sched sc = mq_schedule(bh_ll, tiles_m_ll, V::kT, g_sm_count[device]);
             const long long items = sc.total_items;
+            // FP16 output leaves through a TMA store per Q tile (same map shape as Q's: rows past n_q are clipped); a base or
+            // strides the tensor map cannot express fall back to per-thread row stores
+            CUtensorMap tm_o = tm_q;
+            int tma_store = 0;
+            if (!out_f32 && V::kSplit == 1 && g_mq_tma_store.load(std::memory_order_relaxed) != 0 &&
+                (reinterpret_cast<uintptr_t>(o) & 15u) == 0 && encode_rows_map(&tm_o, o, n_q, heads, batch, so, kBlockM) == 0)
+                tma_store = 1;
             cfg.gridDim = dim3(static_cast<unsigned>(items < g_sm_count[device] ? items : g_sm_count[device]));
             cfg.blockDim = dim3(V::C::kThreads);
             cfg.dynamicSmemBytes = V::C::kSmemBytes;
@@ -376,7 +385,7 @@ static int launch_core(const void* qh, const void* kh, const void* vh, void* o, 
             e = cudaLaunchKernelEx(&cfg,
                                    !out_f32 ? mq::lg_attn_hd64_fwd<V::kT, V::kBN, V::kAlias, V::kLazy, false, V::kSplit>
                                             : mq::lg_attn_hd64_fwd<V::kT, V::kBN, V::kAlias, V::kLazy, true, V::kSplit>,
-                                   tm_q, tm_k, tm_v, o, n_q, n_kv, sc, ol);
+                                   tm_q, tm_k, tm_v, tm_o, o, n_q, n_kv, sc, ol, tma_store);
         });
         if (rc != 0) return rc;
     } else if (full_grid) {

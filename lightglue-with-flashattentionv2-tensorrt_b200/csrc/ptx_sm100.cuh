@@ -148,6 +148,17 @@ __device__ __forceinline__ void tma_load_4d(uint32_t dst_smem, const void* tmap,
         : "memory");
 }
 
+// 4-D tiled store, shared memory -> global (same box / swizzle as the loads; rows of the box past the tensor's extent are not
+// written).  Bulk async-group completion: commit after issuing, wait_group.read before the source buffer is rewritten or the CTA
+// exits (the thread that committed waits).
+__device__ __forceinline__ void tma_store_4d(const void* tmap, uint32_t src_smem, int c0, int c1, int c2, int c3) {
+    asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(reinterpret_cast<uint64_t>(tmap)),
+                 "r"(src_smem), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_commit_group() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_group_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+
 // ----------------------------------------------------------------------------- tcgen05
 template <int kCols>
 __device__ __forceinline__ void tmem_alloc(uint32_t dst_smem) {

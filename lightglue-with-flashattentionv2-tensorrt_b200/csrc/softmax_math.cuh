@@ -18,7 +18,8 @@
 // Build switches that produce WRONG results by design (timing decompositions only) must be asked for twice, so that a stray -D
 // can never ship a kernel that fails parity: csrc/build.py's product build does not define LG_ATTN_TUNING_BUILD, and
 // tests/test_boundary_cpu.py checks the shipped library was built without any of them.
-#if (defined(LG_ATTN_WHATIF) || defined(LG_ATTN_EXPERIMENT_NOSUM) || defined(LG_ATTN_WHATIF_F3)) && !defined(LG_ATTN_TUNING_BUILD)
+#if (defined(LG_ATTN_WHATIF) || defined(LG_ATTN_EXPERIMENT_NOSUM) || defined(LG_ATTN_WHATIF_F3) || defined(LG_ATTN_WHATIF_NOSTORE)) && \
+    !defined(LG_ATTN_TUNING_BUILD)
 #error "LG_ATTN_WHATIF / LG_ATTN_WHATIF_F3 / LG_ATTN_EXPERIMENT_NOSUM give wrong results: tuning builds only (-DLG_ATTN_TUNING_BUILD)"
 #endif
 

@@ -58,3 +58,16 @@ for cta in (0, 5):
     print("mean clk: wait_s", (d[..., 1] - d[..., 0]).mean().round(0), " ldS", (d[..., 2] - d[..., 1]).mean().round(0), " exp", (d[..., 3] - d[..., 2]).mean().round(0),
           " st+arrive", (d[..., 4] - d[..., 3]).mean().round(0), " p_arrive->mma_saw", (d[..., 5] - d[..., 4]).mean().round(0),
           " mma_issue", (d[..., 6] - d[..., 5]).mean().round(0), " mma_issued->next s_full", (d[1:, :, 1] - d[:-1, :, 6]).mean().round(0))
+
+# item boundaries: per-step s_full stamps of tile 0 over the whole trace (a step that starts a new item shows the boundary bubble)
+if os.environ.get("MQ_TRACE_STEPS"):
+    t = buf[0]
+    nsteps = int((t[:, 0, 1] != 0).sum())
+    prev = None
+    for step in range(nsteps):
+        ev = t[step, 0, :7]
+        line = f"step {step:2d}: s_full {int(ev[1] - t[0, 0, 1]):7d}"
+        if prev is not None:
+            line += f"  (+{int(ev[1] - prev):5d})  wait {int(ev[1] - ev[0]):5d}  ld {int(ev[2] - ev[1]):4d}  exp {int(ev[3] - ev[2]):5d}  st {int(ev[4] - ev[3]):4d}  p->mma {int(ev[5] - ev[4]):5d}  issue {int(ev[6] - ev[5]):5d}"
+        prev = ev[1]
+        print(line)
