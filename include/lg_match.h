@@ -11,6 +11,8 @@
  *                            (lightglue.py:143-144, 154-165), in place inside the packed projection
  *   lg_match_layernorm_gelu  the LayerNorm(512) + GELU in the middle of both ffn stacks
  *                            (lightglue.py:131-136, 181-186)
+ *   lg_match_ffn1_ln_gelu    ffn[0..2] of both stacks as one tcgen05 GEMM with the LayerNorm + GELU in its epilogue
+ *                            (lightglue.py:131-136, 181-186)
  *   lg_match_assign          sigmoid_log_double_softmax + filter_matches
  *                            (lightglue.py:216-224, 253-276; demo/lightglue_trt.cpp:291-345)
  *
@@ -41,6 +43,25 @@ int lg_match_rotary(void* packed_half, long long rows, int ld, int n_blocks, con
  * erf-form GELU, statistics in FP32.  gamma, beta: float[512]. */
 int lg_match_layernorm_gelu(void* h_half, long long rows, int ld, const float* gamma, const float* beta,
                             float eps, void* stream);
+
+/* The first half of an ffn stack as ONE launch (lightglue.py:131-136, 181-186: ffn[0] Linear(512, 512), ffn[1] LayerNorm(512),
+ * ffn[2] GELU): hid = GELU(LayerNorm(x @ w^T + bias) * gamma + beta).  A hand-written tcgen05 GEMM (FP32 accumulate) whose epilogue
+ * does the LayerNorm statistics, the affine and the erf-form GELU from registers under the next tile's MMAs — replaces a library
+ * GEMM + lg_match_layernorm_gelu (one pass over [rows, 512] less, and the FP32-issue-bound arithmetic hidden).
+ *   x     [rows, 512] FP16, row stride `ldx` elements (>= 512, multiple of 8): cat(x, context)
+ *   w_nk  [512 (out), 512 (in)] FP16 contiguous — nn.Linear.weight layout (row n = output feature n)
+ *   bias  FP16[512];  gamma, beta: float[512]
+ *   hid   [rows, 512] FP16, row stride `ldh` elements; must not overlap x
+ * x, w_nk, hid 16-byte aligned.  Enqueues on `stream` only (three host-side tensor-map encodes, one launch). */
+int lg_match_ffn1_ln_gelu(const void* x_half, long long rows, int ldx, const void* w_nk_half, const void* bias_half,
+                          const float* gamma, const float* beta, float eps, void* hid_half, int ldh, void* stream);
+/* Per-device one-time set-up of the kernel above (shared-memory opt-in, driver entry point); idempotent, thread-safe, also done
+ * lazily by the first lg_match_ffn1_ln_gelu call on a device. */
+int lg_match_ffn_init_device(int device);
+/* 1 when the fused kernel is expected to beat a library GEMM + lg_match_layernorm_gelu at this row count on the current device,
+ * else 0: its tiles are whole rows (128 x 512), so few rows leave most SMs idle (crossover on B200: about two thirds of the SM
+ * count in tiles).  The matcher's callers ask this once per shape plan. */
+int lg_match_ffn1_prefer_fused(long long rows);
 
 /* Assignment + mutual-nearest-neighbour filter for `batch` pairs.
  *   sim  [batch, n0, n1] float  : mdesc0 . mdesc1^T (already divided by dim^0.25 on both sides)

@@ -52,6 +52,9 @@ MATCH_ABI_SYMBOLS = (
     "lg_match_posenc",
     "lg_match_rotary",
     "lg_match_layernorm_gelu",
+    "lg_match_ffn1_ln_gelu",
+    "lg_match_ffn_init_device",
+    "lg_match_ffn1_prefer_fused",
     "lg_match_assign_workspace_bytes",
     "lg_match_assign",
     "lg_match_assign_static",
@@ -167,6 +170,12 @@ def load() -> ctypes.CDLL:
     lib.lg_match_rotary.argtypes = [P, LL, I, I, P, P]
     lib.lg_match_layernorm_gelu.restype = I
     lib.lg_match_layernorm_gelu.argtypes = [P, LL, I, P, P, F, P]
+    lib.lg_match_ffn1_ln_gelu.restype = I
+    lib.lg_match_ffn1_ln_gelu.argtypes = [P, LL, I, P, P, P, P, F, P, I, P]
+    lib.lg_match_ffn_init_device.restype = I
+    lib.lg_match_ffn_init_device.argtypes = [I]
+    lib.lg_match_ffn1_prefer_fused.restype = I
+    lib.lg_match_ffn1_prefer_fused.argtypes = [LL]
     lib.lg_match_assign_workspace_bytes.restype = ctypes.c_size_t
     lib.lg_match_assign_workspace_bytes.argtypes = [I, I, I]
     lib.lg_match_assign.restype = I

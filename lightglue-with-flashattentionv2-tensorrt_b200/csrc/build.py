@@ -19,7 +19,7 @@ CSRC = Path(__file__).resolve().parent
 BUILD = CSRC / "build"
 LIB = BUILD / "liblightglue_attention_plugin.so"
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
-SOURCES = [CSRC / "lg_attn_api.cu", CSRC / "lg_match_kernels.cu", CSRC / "lg_matcher.cu", CSRC / "plugin" / "lightglue_attention_plugin.cpp",
+SOURCES = [CSRC / "lg_attn_api.cu", CSRC / "lg_match_kernels.cu", CSRC / "lg_ffn_sm100.cu", CSRC / "lg_matcher.cu", CSRC / "plugin" / "lightglue_attention_plugin.cpp",
            CSRC / "plugin" / "mock_trt_host.cpp"]
 HEADERS = [CSRC / "tools" / "lg_pair_bench.cpp", *sorted(CSRC.glob("*.cuh")), CSRC / "attn_sm100.h",
            CSRC / "plugin" / "lightglue_attention_plugin.h", CSRC / "plugin" / "mock_nvinfer" / "NvInfer.h",

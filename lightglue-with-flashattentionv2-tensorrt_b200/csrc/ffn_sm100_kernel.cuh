@@ -1,0 +1,299 @@
+// B200-native (sm_100a) first half of LightGlue's ffn stack as ONE kernel:
+//
+//   hid = GELU(LayerNorm_512(cat(x, context) @ W1'^T + b1') * gamma + beta)          FP16 in, FP32 accumulate / statistics, FP16 out
+//
+// (lightglue_pytorch_with_plugin/lightglue.py:131-136 and :181-186: ffn[0] Linear(512, 512), ffn[1] LayerNorm, ffn[2] GELU; the
+// attention out-projection is folded into W1' on the host, matcher.py).  Round 2 ran this as a cuBLAS GEMM followed by
+// layernorm_gelu_kernel in place: the second pass re-reads and re-writes [rows, 512] FP16 and is bound by FP32 issue, not by HBM
+// (358 warp instructions per row; 11 % of a forward), and nothing else runs beside it.  Here the LayerNorm + GELU arithmetic is
+// the epilogue of a hand-written tcgen05 GEMM and runs UNDER the next tile's MMAs:
+//
+//   * one persistent CTA per SM, tile = 128 rows x all 512 hidden columns: a row's LayerNorm statistics never leave the CTA.
+//     The FP32 accumulator is 128 lanes x 512 columns = all of TMEM, so it cannot be double-buffered; instead the 16 epilogue
+//     warps DRAIN it in one short pass (tcgen05.ld, + bias, shifted sum / sum of squares, pack to FP16: 128 values = 64
+//     registers per thread), hand TMEM back to the MMA warp, and only then do the expensive part (normalise, affine, erf-GELU,
+//     store) from registers while the tensor pipe works on the next tile.
+//   * warp w of the 16: TMEM lane quarter w & 3 (row 32 (w & 3) + lane of the tile), column group w >> 2 (128 columns).  The four
+//     threads that share a row combine their (mean, M2) partials with Chan's formula through shared memory + one 128-thread
+//     named barrier.
+//   * operands by TMA into a 2-stage ring of K = 64 slabs (A 128 x 64, B 512 x 64 as two 256-row boxes, SWIZZLE_128B, K-major:
+//     the same descriptors as the attention kernels' Q / K tiles); per slab 4 x 2 tcgen05.mma of 128 x 256 x 16.
+//   * output: each warp stages 32 rows x 32 columns (2 KiB, SWIZZLE_64B pattern: conflict-free 16-byte stores) and one elected
+//     lane issues a TMA store — rows past `rows` are clipped by the tensor map.
+//
+// Roofline: 2 * 128 * 512 * 512 FLOP per tile = 8 192 clk of tensor pipe; operand traffic 640 KiB per tile (W1' is re-read by
+// every tile: 512 KiB) = 80 B / clk / SM at that rate, above the ~43 B / clk / SM the L2 delivers to 148 SMs at once — so the
+// main loop is L2-bound at ~15 k clk per tile, and the epilogue (~19 instructions per element, 9.7 k issue slots per
+// sub-partition per tile) hides under it.
+//
+// No CUTLASS; encodings in ptx_sm100.cuh.
+#pragma once
+#include "ptx_sm100.cuh"
+
+#include <cuda.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "glue_math.cuh"
+
+// Timing decompositions (WRONG results by construction; tuning builds only, like the attention kernels' LG_ATTN_WHATIF):
+//   LG_FFN_WHATIF 1: no GELU (normalise + affine only)   2: no tcgen05.mma issued (commits stay)
+//                 3: W1' tiles loaded for the first tile of a CTA only (what the re-streaming of W1' through L2 costs)
+#if defined(LG_FFN_WHATIF) && !defined(LG_ATTN_TUNING_BUILD)
+#error "LG_FFN_WHATIF gives wrong results: tuning builds only (-DLG_ATTN_TUNING_BUILD)"
+#endif
+#ifndef LG_FFN_WHATIF
+#define LG_FFN_WHATIF 0
+#endif
+
+namespace lgffn {
+
+using namespace lgattn::ptx;
+
+constexpr int kBM = 128;          // rows per tile (= tcgen05.mma M, one TMEM lane per row)
+constexpr int kN = 512;           // hidden width = LayerNorm width
+constexpr int kK = 512;           // cat(x, context)
+constexpr int kBK = 64;           // K slab: one SWIZZLE_128B atom of halves
+constexpr int kKSteps = kK / kBK;
+constexpr int kStages = 2;
+constexpr int kEpiWarps = 16;
+constexpr int kServiceWarps = 4;  // TMA producer, MMA issuer (+ TMEM allocator), two register donors (setmaxnreg wants a whole warpgroup)
+constexpr int kThreads = 32 * (kEpiWarps + kServiceWarps);
+constexpr int kColsPerWarp = kN / (kEpiWarps / 4);   // 128
+constexpr int kRound = 32;        // columns per staging round
+
+constexpr uint32_t kABytes = kBM * kBK * 2;            // 16 KiB
+constexpr uint32_t kBHalfBytes = 256 * kBK * 2;        // 32 KiB (TMA boxes are at most 256 rows)
+constexpr uint32_t kStageBytes = kABytes + 2 * kBHalfBytes;
+constexpr uint32_t kSmemRing = 0;
+constexpr uint32_t kSmemStage = kSmemRing + kStages * kStageBytes;          // 16 x 2 KiB output staging
+constexpr uint32_t kStageTile = kRound * 32 * 2;                            // 32 rows x 32 halves
+constexpr uint32_t kSmemParams = kSmemStage + kEpiWarps * kStageTile;       // bias | gamma | beta, 512 floats each
+constexpr uint32_t kSmemStats = kSmemParams + 3 * kN * 4;                   // [tile parity][column group][row] (mean, M2)
+constexpr uint32_t kSmemBar = kSmemStats + 2 * 4 * kBM * 8;
+enum : uint32_t { kBarFull = 0, kBarEmpty = kStages, kBarAccFull = 2 * kStages, kBarAccEmpty, kNumBars };
+constexpr uint32_t kSmemTmemSlot = kSmemBar + 8 * kNumBars;
+constexpr uint32_t kSmemUsed = kSmemTmemSlot + 16;
+constexpr uint32_t kSmemBytes = kSmemUsed + 1024;   // + slack for the 1024-byte alignment of the swizzled tiles
+static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
+
+constexpr int kRegsLaunch = (65536 / kThreads) / 8 * 8;   // 96
+constexpr int kRegsService = 32;
+constexpr int kRegsEpi = ((kThreads * kRegsLaunch - kServiceWarps * 32 * kRegsService) / (kEpiWarps * 32)) / 8 * 8;   // 112
+
+__device__ __forceinline__ float2 unpack_half2(uint32_t v) {
+    return __half22float2(*reinterpret_cast<const __half2*>(&v));
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+ffn1_ln_gelu_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w,
+                    const __grid_constant__ CUtensorMap tm_h, const __half* __restrict__ bias, const float* __restrict__ gamma,
+                    const float* __restrict__ beta, float eps, int tiles) {
+    extern __shared__ uint8_t smem_raw[];
+    uint32_t smem = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    asm volatile("mov.u32 %0, %0;" : "+r"(smem));   // pin (see attn_sm100_kernel_mq.cuh)
+    const uint32_t bars = smem + kSmemBar;
+    auto bar = [&](uint32_t i) { return bars + 8u * i; };
+
+    const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
+    const int lane = threadIdx.x & 31;
+    constexpr int kWarpTMA = kEpiWarps, kWarpMMA = kEpiWarps + 1;
+
+    if (warp == kWarpTMA && lane == 0) {
+        prefetch_tmap(&tm_x);
+        prefetch_tmap(&tm_w);
+        prefetch_tmap(&tm_h);
+#pragma unroll
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(bar(kBarFull + s), 1);
+            mbar_init(bar(kBarEmpty + s), 1);
+        }
+        mbar_init(bar(kBarAccFull), 1);
+        mbar_init(bar(kBarAccEmpty), kEpiWarps);
+        fence_mbar_init();
+    }
+    if (warp == kWarpMMA) {
+        tmem_alloc<512>(smem + kSmemTmemSlot);
+        tmem_relinquish();
+    }
+    // bias (FP16 -> FP32), gamma, beta into shared memory: read as broadcast 16-byte loads by every epilogue thread
+    if (threadIdx.x < kN) {
+        st_shared_f32(smem + kSmemParams + 4u * threadIdx.x, __half2float(bias[threadIdx.x]));
+        st_shared_f32(smem + kSmemParams + 4u * (kN + threadIdx.x), gamma[threadIdx.x]);
+        st_shared_f32(smem + kSmemParams + 4u * (2 * kN + threadIdx.x), beta[threadIdx.x]);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    uint32_t tmem_base;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(smem + kSmemTmemSlot));
+
+    const int first = blockIdx.x, stride = gridDim.x;
+
+    if (warp >= kEpiWarps) {
+        setmaxnreg_dec<kRegsService>();
+        // service warps run converged and issue through elect.sync (uniform datapath, see attn_sm100_kernel_mq.cuh)
+        const uint32_t smem_u = (smem_u32(smem_raw) + 1023u) & ~1023u;
+        const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
+        const uint32_t bars_u = smem_u + kSmemBar;
+        auto ubar = [&](uint32_t i) { return bars_u + 8u * i; };
+        if (warp == kWarpTMA) {
+            // ===================================================================== operand producer
+            int g = 0;
+            for (int tile = first; tile < tiles; tile += stride) {
+#pragma unroll 1
+                for (int k = 0; k < kKSteps; ++k, ++g) {
+                    const int s = g % kStages;
+                    if (g >= kStages) mbar_wait_backoff(ubar(kBarEmpty + s), ((g / kStages) - 1) & 1, 64);
+                    if (elect_one()) {
+                        const uint32_t dst = smem_u + kSmemRing + s * kStageBytes;
+                        const bool load_b = LG_FFN_WHATIF != 3 || g < kKSteps;
+                        mbar_arrive_expect_tx(ubar(kBarFull + s), load_b ? kStageBytes : kABytes);
+                        tma_load_4d(dst, &tm_x, ubar(kBarFull + s), k * kBK, tile * kBM, 0, 0);
+                        if (load_b) {
+                            tma_load_4d(dst + kABytes, &tm_w, ubar(kBarFull + s), k * kBK, 0, 0, 0);
+                            tma_load_4d(dst + kABytes + kBHalfBytes, &tm_w, ubar(kBarFull + s), k * kBK, 256, 0, 0);
+                        }
+                    }
+                    __syncwarp();
+                }
+            }
+        } else if (warp == kWarpMMA) {
+            // ===================================================================== MMA issuer
+            constexpr uint32_t idesc = make_idesc_f16_f32acc(kBM, 256, false);
+            int g = 0, it = 0;
+            for (int tile = first; tile < tiles; tile += stride, ++it) {
+                if (it > 0) mbar_wait(ubar(kBarAccEmpty), (it - 1) & 1);   // the epilogue warps have drained the accumulator
+                tc_fence_after();
+#pragma unroll 1
+                for (int k = 0; k < kKSteps; ++k, ++g) {
+                    const int s = g % kStages;
+                    mbar_wait(ubar(kBarFull + s), (g / kStages) & 1);
+                    tc_fence_after();
+                    if (elect_one()) {
+                        const uint32_t a = smem_u + kSmemRing + s * kStageBytes;
+                        const uint64_t desc_a = make_smem_desc_sw128(a, 16, 1024);
+                        const uint64_t desc_b0 = make_smem_desc_sw128(a + kABytes, 16, 1024);
+                        const uint64_t desc_b1 = make_smem_desc_sw128(a + kABytes + kBHalfBytes, 16, 1024);
+#pragma unroll
+                        for (int kk = 0; kk < kBK / 16; ++kk) {
+                            const uint32_t acc = (k > 0 || kk > 0) ? 1u : 0u;
+                            if (LG_FFN_WHATIF != 2) {
+                                mma_f16_ss(tmem_u, desc_a + 2u * kk, desc_b0 + 2u * kk, idesc, acc);
+                                mma_f16_ss(tmem_u + 256u, desc_a + 2u * kk, desc_b1 + 2u * kk, idesc, acc);
+                            }
+                        }
+                        mma_commit(ubar(kBarEmpty + s));
+                        if (k == kKSteps - 1) mma_commit(ubar(kBarAccFull));
+                    }
+                    __syncwarp();
+                }
+            }
+        }
+    } else {
+        // ========================================================================= epilogue warps
+        setmaxnreg_inc<kRegsEpi>();
+        const int quarter = warp & 3, cg = warp >> 2;
+        const int row = quarter * 32 + lane;   // row inside the tile
+        const uint32_t t_acc = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + static_cast<uint32_t>(cg * kColsPerWarp);
+        const uint32_t p_bias = smem + kSmemParams + 4u * (cg * kColsPerWarp);
+        const uint32_t p_gamma = p_bias + 4u * kN, p_beta = p_bias + 8u * kN;
+        const uint32_t stg = smem + kSmemStage + static_cast<uint32_t>(warp) * kStageTile;
+        const uint32_t stg_row = stg + static_cast<uint32_t>(lane) * 64u;
+        const uint32_t swz = static_cast<uint32_t>((lane >> 1) & 3);
+
+        int it = 0;
+        for (int tile = first; tile < tiles; tile += stride, ++it) {
+            mbar_wait(bar(kBarAccFull), it & 1);
+            tc_fence_after();
+            // ---- drain: accumulator + bias -> FP16 pairs in registers, shifted statistics in FP32
+            uint32_t pk[kColsPerWarp / 2];
+            float shift = 0.f, s1 = 0.f, s2 = 0.f;
+#pragma unroll
+            for (int c = 0; c < kColsPerWarp / 32; ++c) {
+                uint32_t v[32];
+                tmem_ld_x32(t_acc + 32u * c, v);
+                tmem_wait_ld();
+#pragma unroll
+                for (int i = 0; i < 32; i += 4) {
+                    const float4 b = ld_shared_v4f(p_bias + 4u * (32 * c + i));
+                    const float a0 = __uint_as_float(v[i]) + b.x, a1 = __uint_as_float(v[i + 1]) + b.y;
+                    const float a2 = __uint_as_float(v[i + 2]) + b.z, a3 = __uint_as_float(v[i + 3]) + b.w;
+                    if (c == 0 && i == 0) shift = a0;
+                    const float d0 = a0 - shift, d1 = a1 - shift, d2 = a2 - shift, d3 = a3 - shift;
+                    s1 += (d0 + d1) + (d2 + d3);
+                    s2 = fmaf(d0, d0, s2);
+                    s2 = fmaf(d1, d1, s2);
+                    s2 = fmaf(d2, d2, s2);
+                    s2 = fmaf(d3, d3, s2);
+                    pk[16 * c + i / 2] = pack_half2(a0, a1);
+                    pk[16 * c + i / 2 + 1] = pack_half2(a2, a3);
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar(kBarAccEmpty));   // the next tile's MMAs may overwrite the accumulator now
+
+            // ---- row statistics: this thread's 128 columns -> (mean, M2), combined with the row's three other column groups
+            constexpr float kInvCols = 1.0f / kColsPerWarp;
+            const float dm = s1 * kInvCols;
+            const float mean_i = shift + dm;
+            const float m2_i = fmaxf(fmaf(-dm, s1, s2), 0.f);
+            const uint32_t st_base = smem + kSmemStats + static_cast<uint32_t>((it & 1) * 4 * kBM + row) * 8u;
+            st_shared_v2f(st_base + static_cast<uint32_t>(cg * kBM) * 8u, mean_i, m2_i);
+            named_bar_sync(1u + static_cast<uint32_t>(quarter), 128u);
+            const float2 p0 = ld_shared_v2f(st_base), p1 = ld_shared_v2f(st_base + kBM * 8u);
+            const float2 p2 = ld_shared_v2f(st_base + 2u * kBM * 8u), p3 = ld_shared_v2f(st_base + 3u * kBM * 8u);
+            const float mean = 0.25f * ((p0.x + p1.x) + (p2.x + p3.x));
+            const float e0 = p0.x - mean, e1 = p1.x - mean, e2 = p2.x - mean, e3 = p3.x - mean;
+            const float m2 = ((p0.y + p1.y) + (p2.y + p3.y)) + kColsPerWarp * ((e0 * e0 + e1 * e1) + (e2 * e2 + e3 * e3));
+            const float rstd = rsqrtf(m2 * (1.0f / kN) + eps);
+            const float nmr = -mean * rstd;
+
+            // ---- apply: normalise, affine, GELU, FP16, 32 columns per staging round, one TMA store per round
+#pragma unroll
+            for (int c = 0; c < kColsPerWarp / kRound; ++c) {
+                uint32_t o[kRound / 2];
+#pragma unroll
+                for (int i = 0; i < kRound; i += 4) {
+                    const float4 g4 = ld_shared_v4f(p_gamma + 4u * (kRound * c + i));
+                    const float4 b4 = ld_shared_v4f(p_beta + 4u * (kRound * c + i));
+                    const float2 x01 = unpack_half2(pk[(kRound * c + i) / 2]), x23 = unpack_half2(pk[(kRound * c + i) / 2 + 1]);
+                    auto act = [](float v) { return LG_FFN_WHATIF == 1 ? v : lgmatch::gelu_erf(v); };
+                    const float y0 = act(fmaf(fmaf(x01.x, rstd, nmr), g4.x, b4.x));
+                    const float y1 = act(fmaf(fmaf(x01.y, rstd, nmr), g4.y, b4.y));
+                    const float y2 = act(fmaf(fmaf(x23.x, rstd, nmr), g4.z, b4.z));
+                    const float y3 = act(fmaf(fmaf(x23.y, rstd, nmr), g4.w, b4.w));
+                    o[i / 2] = pack_half2(y0, y1);
+                    o[i / 2 + 1] = pack_half2(y2, y3);
+                }
+                // the previous round's TMA store must have read the staging tile
+                if (elect_one()) bulk_wait_group_read0();
+                __syncwarp();
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    st_shared_v4(stg_row + ((static_cast<uint32_t>(j) ^ swz) << 4), o[4 * j], o[4 * j + 1], o[4 * j + 2], o[4 * j + 3]);
+                fence_proxy_async_smem();
+                __syncwarp();
+                if (elect_one()) {
+                    tma_store_4d(&tm_h, stg, cg * kColsPerWarp + kRound * c, tile * kBM + quarter * 32, 0, 0);
+                    bulk_commit_group();
+                }
+                __syncwarp();
+            }
+        }
+        // the staging tiles must outlive the stores that read them
+        if (elect_one()) bulk_wait_group_read0();
+        __syncwarp();
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == kWarpMMA) {
+        tc_fence_after();
+        tmem_dealloc<512>(tmem_base);
+    }
+}
+
+}  // namespace lgffn

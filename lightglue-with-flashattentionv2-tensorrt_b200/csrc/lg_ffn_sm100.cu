@@ -1,0 +1,121 @@
+// C-ABI of the fused ffn-up kernel (declared in include/lg_match.h): host-side glue only — argument checks, per-device one-time
+// set-up, three TMA tensor maps per call (cuTensorMapEncodeTiled through cudaGetDriverEntryPoint: a pure host call, legal while a
+// stream is being captured) and one launch.  Never allocates, never synchronises.
+
+#include "ffn_sm100_kernel.cuh"
+
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <mutex>
+
+#include "../../include/lg_attn.h"
+#include "../../include/lg_match.h"
+
+namespace {
+
+using namespace lgffn;
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+constexpr int kMaxDevices = 64;
+std::mutex g_mutex;
+std::atomic<int> g_ready[kMaxDevices];
+std::atomic<EncodeTiledFn> g_encode{nullptr};
+int g_sms[kMaxDevices];
+
+int init_locked(int device) {
+    cudaDeviceProp prop;
+    cudaError_t e = cudaGetDeviceProperties(&prop, device);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    if (prop.major != 10) return LG_ATTN_EARCH;
+    if (g_encode.load(std::memory_order_acquire) == nullptr) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+        if (e != cudaSuccess || fn == nullptr || qres != cudaDriverEntryPointSuccess) {
+            (void)cudaGetLastError();
+            return LG_ATTN_EDRIVER;
+        }
+        g_encode.store(reinterpret_cast<EncodeTiledFn>(fn), std::memory_order_release);
+    }
+    int prev = 0;
+    if ((e = cudaGetDevice(&prev)) != cudaSuccess) return static_cast<int>(e);
+    if ((e = cudaSetDevice(device)) != cudaSuccess) return static_cast<int>(e);
+    e = cudaFuncSetAttribute(ffn1_ln_gelu_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemBytes));
+    (void)cudaSetDevice(prev);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    g_sms[device] = prop.multiProcessorCount;
+    return 0;
+}
+
+// 2-D row-major FP16 matrix [rows, cols] with row stride `ld` elements, as a 4-D map (cols, rows, 1, 1) so that the kernels'
+// tma_load_4d / tma_store_4d wrappers serve it; rows past `rows` read as zeros / are not written.
+int encode_matrix(CUtensorMap* map, const void* base, long long rows, int cols, long long ld, int box_cols, int box_rows,
+                  CUtensorMapSwizzle swizzle) {
+    const cuuint64_t dims[4] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows), 1, 1};
+    const cuuint64_t srow = static_cast<cuuint64_t>(ld) * 2;
+    const cuuint64_t strides[3] = {srow, srow, srow};   // extent-1 dimensions never advance; any legal stride
+    const cuuint32_t box[4] = {static_cast<cuuint32_t>(box_cols), static_cast<cuuint32_t>(box_rows), 1, 1};
+    const cuuint32_t estr[4] = {1, 1, 1, 1};
+    const CUresult r = g_encode.load(std::memory_order_acquire)(
+        map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+        swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? 0 : LG_ATTN_EDRIVER;
+}
+
+}  // namespace
+
+extern "C" {
+
+int lg_match_ffn_init_device(int device) {
+    if (device < 0 || device >= kMaxDevices) return LG_ATTN_EINVAL;
+    if (g_ready[device].load(std::memory_order_acquire)) return 0;
+    std::lock_guard<std::mutex> lock(g_mutex);
+    if (g_ready[device].load(std::memory_order_relaxed)) return 0;
+    const int rc = init_locked(device);
+    if (rc == 0) g_ready[device].store(1, std::memory_order_release);
+    return rc;
+}
+
+int lg_match_ffn1_prefer_fused(long long rows) {
+    // Tiles are 128 rows x all 512 columns (a row's LayerNorm never leaves the CTA), one tile per CTA at a time: small row counts
+    // leave most SMs idle (a single 1024-keypoint pair is 16 tiles) and the library GEMM + lg_match_layernorm_gelu pair, which
+    // spreads the same work over every SM, finishes first.  Measured crossover on B200 (tools/pairs_sweep.py): between 64 and 128 tiles.
+    int device = 0, sms = 148;
+    if (cudaGetDevice(&device) == cudaSuccess && device >= 0 && device < kMaxDevices && g_ready[device].load(std::memory_order_acquire))
+        sms = g_sms[device];
+    const long long tiles = (rows + kBM - 1) / kBM;
+    return tiles * 3 >= static_cast<long long>(sms) * 2 ? 1 : 0;
+}
+
+int lg_match_ffn1_ln_gelu(const void* x_half, long long rows, int ldx, const void* w_nk_half, const void* bias_half,
+                          const float* gamma, const float* beta, float eps, void* hid_half, int ldh, void* stream) {
+    if (x_half == nullptr || w_nk_half == nullptr || bias_half == nullptr || gamma == nullptr || beta == nullptr ||
+        hid_half == nullptr || rows <= 0 || rows > (1LL << 31) - kBM)
+        return LG_ATTN_EINVAL;
+    if (ldx < kK || ldh < kN || (ldx & 7) != 0 || (ldh & 7) != 0) return LG_ATTN_EINVAL;
+    if (((reinterpret_cast<uintptr_t>(x_half) | reinterpret_cast<uintptr_t>(w_nk_half) | reinterpret_cast<uintptr_t>(hid_half)) & 15u) != 0)
+        return LG_ATTN_EINVAL;
+    int device = 0;
+    cudaError_t e = cudaGetDevice(&device);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    int rc = lg_match_ffn_init_device(device);
+    if (rc != 0) return rc;
+
+    CUtensorMap tm_x, tm_w, tm_h;
+    if ((rc = encode_matrix(&tm_x, x_half, rows, kK, ldx, kBK, kBM, CU_TENSOR_MAP_SWIZZLE_128B)) != 0) return rc;
+    if ((rc = encode_matrix(&tm_w, w_nk_half, kN, kK, kK, kBK, 256, CU_TENSOR_MAP_SWIZZLE_128B)) != 0) return rc;
+    if ((rc = encode_matrix(&tm_h, hid_half, rows, kN, ldh, kRound, 32, CU_TENSOR_MAP_SWIZZLE_64B)) != 0) return rc;
+    const int tiles = static_cast<int>((rows + kBM - 1) / kBM);
+    const int grid = tiles < g_sms[device] ? tiles : g_sms[device];
+    ffn1_ln_gelu_kernel<<<grid, kThreads, kSmemBytes, static_cast<cudaStream_t>(stream)>>>(
+        tm_x, tm_w, tm_h, static_cast<const __half*>(bias_half), gamma, beta, eps, tiles);
+    e = cudaGetLastError();
+    return static_cast<int>(e);
+}
+
+}  // extern "C"

@@ -19,6 +19,7 @@
 
 #include "../../include/lg_attn.h"
 #include "../../include/lg_match.h"
+#include "glue_math.cuh"
 
 namespace lgmatch {
 
@@ -85,23 +86,7 @@ __global__ void __launch_bounds__(256) rotary_kernel(__half* __restrict__ buf, l
 }
 
 // ------------------------------------------------------------------------------------------ LN + GELU
-// erf-form GELU, 0.5 x (1 + erf(x / sqrt 2)) = 0.5 x + 0.5 |x| erf(|x| / sqrt 2), with erf by Abramowitz-Stegun 7.1.25
-// (three coefficients, |err| <= 2.5e-5: below half an FP16 ulp of the result everywhere) — 10 FP32 ops + 2 MUFU (rcp, ex2) per
-// element.  The kernel is bound by FP32 issue, not by HBM (~0.7 element-ops / clk / scheduler, tools/microbench/pipe_rates.cu), so
-// every op per element counts: round 1's 7.1.26 form (five coefficients) cost two more FMAs for accuracy FP16 cannot hold.
-__device__ __forceinline__ float gelu_erf(float x) {
-    const float z = fabsf(x) * 0.70710678118654752f;
-    float t, e;
-    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.47047f, z, 1.0f)));
-    float p = fmaf(0.7478556f, t, -0.0958798f);
-    p = fmaf(p, t, 0.3480242f);
-    p *= t;
-    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"((z * -1.4426950408889634f) * z));
-    const float erf_abs = fmaf(-p, e, 1.0f);
-    const float hx = 0.5f * x;
-    return fmaf(fabsf(hx), erf_abs, hx);
-}
-
+// erf-form GELU: gelu_erf() in glue_math.cuh (shared with the fused ffn kernel).
 // One warp per row of 512: lane owns columns [8*lane, 8*lane+8) and [256 + 8*lane, ...).
 __global__ void __launch_bounds__(256) layernorm_gelu_kernel(__half* __restrict__ h, long long rows, int ld,
                                                              const float* __restrict__ gamma,

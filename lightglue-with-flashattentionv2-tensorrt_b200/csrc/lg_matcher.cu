@@ -17,6 +17,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <utility>
@@ -49,6 +50,7 @@ struct BlockW {           // device pointers into the blob copy
     const float* beta;    // [512]
     const __half* w2_t;   // [512, 256]
     int n_in;
+    const __half* w1_nk;  // [512 out, 512 in]: w1_t transposed at create time (outside the blob) — the fused ffn kernel's B operand
 };
 
 size_t block_bytes(int n_in) {
@@ -161,6 +163,8 @@ struct lg_matcher : ShapePlan {   // the inherited members are the ACTIVE plan
     float threshold = 0.1f;
     cublasLtHandle_t lt = nullptr;
     uint8_t* blob = nullptr;  // device copy of the weight blob
+    __half* w1_nk = nullptr;  // [2 * n_layers][512][512]: every block's W1' in nn.Linear layout (see BlockW::w1_nk)
+    bool fused_ffn = true;    // LG_MATCH_FUSED_FFN=0: library GEMM + lg_match_layernorm_gelu instead (A/B runs)
     const float* wr = nullptr;
     std::vector<BlockW> self_w, cross_w;
     const __half *wf_t = nullptr, *bf = nullptr;
@@ -211,10 +215,17 @@ int forward(lg_matcher* m, cudaStream_t st, int* launches_out) {
         return lg_attn_hd64_launch_strided(q, k, v, o, batch, kHeads, nq, nkv, 0, &sq, &sk, &sk, &so, shift, st);
     };
     auto ffn = [&](const BlockW& w) {
-        int e = run_gemm(m->lt, m->g_ffn1, m->xc, w.w1_t, m->hid, w.b1, m->lt_ws, kLtWorkspace, st);   // cat(x, ctx) @ W1'^T
-        if (e == 0) e = lg_match_layernorm_gelu(m->hid, R, kFfn, w.gamma, w.beta, 1e-5f, st);
+        int e;
+        if (m->fused_ffn && lg_match_ffn1_prefer_fused(R)) {
+            // cat(x, ctx) @ W1'^T + b1', LayerNorm, GELU in one tcgen05 kernel (LayerNorm + GELU in the GEMM's epilogue)
+            e = lg_match_ffn1_ln_gelu(m->xc, R, kFfn, w.w1_nk, w.b1, w.gamma, w.beta, 1e-5f, m->hid, kFfn, st);
+            launches += 2;
+        } else {
+            e = run_gemm(m->lt, m->g_ffn1, m->xc, w.w1_t, m->hid, w.b1, m->lt_ws, kLtWorkspace, st);
+            if (e == 0) e = lg_match_layernorm_gelu(m->hid, R, kFfn, w.gamma, w.beta, 1e-5f, st);
+            launches += 3;
+        }
         if (e == 0) e = run_gemm(m->lt, m->g_ffn2, m->hid, w.w2_t, x, nullptr, m->lt_ws, kLtWorkspace, st);  // x += hid @ W2^T
-        launches += 3;
         return e;
     };
 
@@ -303,6 +314,7 @@ int lg_matcher_create(lg_matcher** out, int device, int n_layers, const void* we
     cudaError_t e = cudaSetDevice(device);
     if (e != cudaSuccess) return static_cast<int>(e);
     int rc = lg_attn_hd64_init_device(device);
+    if (rc == 0) rc = lg_match_ffn_init_device(device);
     if (rc != 0) return rc;
     lg_matcher* m = new (std::nothrow) lg_matcher();
     if (m == nullptr) return static_cast<int>(cudaErrorMemoryAllocation);
@@ -318,10 +330,15 @@ int lg_matcher_create(lg_matcher** out, int device, int n_layers, const void* we
         e = cudaEventCreateWithFlags(&m->ev_in[i], cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&m->ev_free[i], cudaEventDisableTiming);
     }
+    if (const char* env = getenv("LG_MATCH_FUSED_FFN")) m->fused_ffn = atoi(env) != 0;
+    const size_t w1_elems = static_cast<size_t>(kFfn) * kFfn;
+    if (e == cudaSuccess) e = cudaMalloc(&m->w1_nk, 2 * static_cast<size_t>(n_layers) * w1_elems * 2);
     if (e != cudaSuccess) { lg_matcher_destroy(m); return static_cast<int>(e); }
     // carve the device copy
     uint8_t* p = m->blob + align256(sizeof(BlobHeader));
     auto take = [&](size_t bytes) { uint8_t* q = p; p += align256(bytes); return q; };
+    std::vector<uint16_t> w1_host(w1_elems);
+    int n_blocks = 0;
     m->wr = reinterpret_cast<const float*>(take(32 * 2 * 4));
     auto take_block = [&](int n_in) {
         BlockW w{};
@@ -333,6 +350,14 @@ int lg_matcher_create(lg_matcher** out, int device, int n_layers, const void* we
         w.gamma = reinterpret_cast<const float*>(take(kFfn * 4));
         w.beta = reinterpret_cast<const float*>(take(kFfn * 4));
         w.w2_t = reinterpret_cast<const __half*>(take(static_cast<size_t>(kFfn) * kDim * 2));
+        // W1' the other way round ([out, in], rows = output features), transposed on the host from the caller's blob
+        const uint16_t* src = reinterpret_cast<const uint16_t*>(static_cast<const uint8_t*>(weights_host) +
+                                                                (reinterpret_cast<const uint8_t*>(w.w1_t) - m->blob));
+        for (int k = 0; k < kFfn; ++k)
+            for (int n = 0; n < kFfn; ++n) w1_host[static_cast<size_t>(n) * kFfn + k] = src[static_cast<size_t>(k) * kFfn + n];
+        __half* dst = m->w1_nk + static_cast<size_t>(n_blocks++) * w1_elems;
+        if (e == cudaSuccess) e = cudaMemcpy(dst, w1_host.data(), w1_elems * 2, cudaMemcpyHostToDevice);
+        w.w1_nk = dst;
         return w;
     };
     for (int l = 0; l < n_layers; ++l) {
@@ -341,6 +366,7 @@ int lg_matcher_create(lg_matcher** out, int device, int n_layers, const void* we
     }
     m->wf_t = reinterpret_cast<const __half*>(take(static_cast<size_t>(kDim) * kMdCols * 2));
     m->bf = reinterpret_cast<const __half*>(take(kMdCols * 2));
+    if (e != cudaSuccess) { lg_matcher_destroy(m); return static_cast<int>(e); }
     *out = m;
     return 0;
 }
@@ -574,6 +600,7 @@ void lg_matcher_destroy(lg_matcher* m) {
         if (m->ev_free[i]) (void)cudaEventDestroy(m->ev_free[i]);
     }
     if (m->blob) (void)cudaFree(m->blob);
+    if (m->w1_nk) (void)cudaFree(m->w1_nk);
     if (m->lt) cublasLtDestroy(m->lt);
     delete m;
 }

@@ -29,6 +29,7 @@ There is no CPU path: tensors must be on a CUDA device and the C-ABI library mus
 from __future__ import annotations
 
 import math
+import os
 from collections import OrderedDict
 from dataclasses import dataclass
 
@@ -111,6 +112,7 @@ class _Block:
     gamma: torch.Tensor     # FP32 [512]
     beta: torch.Tensor
     w2_t: torch.Tensor      # [512, 256]
+    w1_nk: torch.Tensor = None   # [512 out, 512 in]: w1_t the other way round (nn.Linear layout), the fused ffn kernel's B operand
 
 
 class MatcherWeights:
@@ -150,7 +152,8 @@ class MatcherWeights:
                 b1f = b1 + w1m @ bo + w1x @ c
                 b_inf = b_in + w_in @ c
                 pair.append(_Block(h(w_in), vec(b_inf), h(w1f), vec(b1f), vec(f64[p + "ffn.1.weight"], torch.float32),
-                                   vec(f64[p + "ffn.1.bias"], torch.float32), h(f64[p + "ffn.3.weight"])))
+                                   vec(f64[p + "ffn.1.bias"], torch.float32), h(f64[p + "ffn.3.weight"]),
+                                   w1f.contiguous().to(dev, torch.float16)))
                 c = c + f64[p + "ffn.3.bias"]
             self.blocks.append(tuple(pair))
         p = f"log_assignment.{n_layers - 1}."
@@ -295,6 +298,25 @@ def rotary_(packed: torch.Tensor, n_blocks: int, cs: torch.Tensor) -> torch.Tens
     return packed
 
 
+def ffn1_ln_gelu(x: torch.Tensor, w_nk: torch.Tensor, bias: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor,
+                 out: torch.Tensor, eps: float = 1e-5) -> torch.Tensor:
+    """``out = GELU(LayerNorm(x @ w_nk^T + bias) * gamma + beta)`` as ONE launch (``lg_match_ffn1_ln_gelu``): x [rows, 512] FP16
+    (row stride free), w_nk [512 out, 512 in] FP16 contiguous (``nn.Linear.weight`` layout), bias FP16 [512], gamma / beta FP32
+    [512], out [rows, 512] FP16.  Reference: ffn[0..2], lightglue_pytorch_with_plugin/lightglue.py:131-136."""
+    for t in (x, w_nk, bias, gamma, beta, out):
+        if not t.is_cuda:
+            raise RuntimeError("lg_match_ffn1_ln_gelu: tensors must live on the CUDA device (no CPU path)")
+    if (x.dtype != torch.float16 or out.dtype != torch.float16 or w_nk.dtype != torch.float16 or bias.dtype != torch.float16
+            or gamma.dtype != torch.float32 or beta.dtype != torch.float32):
+        raise ValueError("lg_match_ffn1_ln_gelu: x / w / bias / out FP16, gamma / beta FP32")
+    if (x.dim() != 2 or x.shape[1] != FFN or x.stride(1) != 1 or out.shape != x.shape or out.stride(1) != 1
+            or w_nk.shape != (FFN, FFN) or not w_nk.is_contiguous() or bias.numel() != FFN or gamma.numel() != FFN or beta.numel() != FFN):
+        raise ValueError("lg_match_ffn1_ln_gelu: expected x / out [rows, 512], w [512, 512] contiguous, 512-vectors")
+    B.check(B.load().lg_match_ffn1_ln_gelu(x.data_ptr(), x.shape[0], x.stride(0), w_nk.data_ptr(), bias.data_ptr(), gamma.data_ptr(),
+                                           beta.data_ptr(), eps, out.data_ptr(), out.stride(0), _stream(x)), "lg_match_ffn1_ln_gelu")
+    return out
+
+
 def layernorm_gelu_(h: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: float = 1e-5) -> torch.Tensor:
     """In-place ``GELU(LayerNorm(h))`` on an FP16 [rows, 512] buffer (lightglue.py:131-136)."""
     if not h.is_cuda or h.dtype != torch.float16 or h.dim() != 2 or h.shape[1] != FFN or h.stride(1) != 1:
@@ -403,6 +425,8 @@ class PairMatcher:
         self.device = torch.device(device)
         self.threshold = threshold
         self.use_graph = use_graph
+        # LG_MATCH_FUSED_FFN=0: ffn[0..2] as library GEMM + lg_match_layernorm_gelu (round 2's path; kept for A/B runs)
+        self.fused_ffn = os.environ.get("LG_MATCH_FUSED_FFN", "1") != "0"
         sd = state_dict if state_dict is not None else reference_init_state_dict(seed, n_layers)
         self.w = MatcherWeights(sd, n_layers, self.device)
         # shape plans, least recently used first.  The reference engine is dynamic (1..2048 keypoints per image, different for
@@ -458,13 +482,17 @@ class PairMatcher:
         launches += 2 + B.load().lg_match_assign_launches(int(want_scores))
         return launches
 
-    @staticmethod
-    def _ffn(p: _Plan, blk: _Block) -> int:
+    def _ffn(self, p: _Plan, blk: _Block) -> int:
         x = p.xc[:, :DIM]
-        torch.addmm(blk.b1, p.xc, blk.w1_t, out=p.hid)      # cat(x, context) @ W1'^T
-        layernorm_gelu_(p.hid, blk.gamma, blk.beta)
+        fused = self.fused_ffn and p.prefer_fused_ffn
+        if fused:
+            # cat(x, context) @ W1'^T + b1', LayerNorm, GELU: one tcgen05 kernel, the LayerNorm + GELU in its epilogue
+            ffn1_ln_gelu(p.xc, blk.w1_nk, blk.b1, blk.gamma, blk.beta, p.hid)
+        else:
+            torch.addmm(blk.b1, p.xc, blk.w1_t, out=p.hid)      # library GEMM, then LayerNorm + GELU in place
+            layernorm_gelu_(p.hid, blk.gamma, blk.beta)
         torch.addmm(x, p.hid, blk.w2_t, out=x)              # residual accumulate in place
-        return 3
+        return 2 if fused else 3
 
     def plan(self, b: int, n0: int, n1: int, want_scores: bool = False) -> _Plan:
         key = (b, n0, n1, want_scores)
@@ -481,6 +509,8 @@ class PairMatcher:
             with torch.cuda.device(self.device):
                 p = _Plan(b, n0, n1, self.device, want_scores)
                 B.check(B.load().lg_attn_hd64_init_device(self.device.index or 0), "lg_attn_hd64_init_device")
+                B.check(B.load().lg_match_ffn_init_device(self.device.index or 0), "lg_match_ffn_init_device")
+                p.prefer_fused_ffn = bool(B.load().lg_match_ffn1_prefer_fused(p.rows))   # few rows: library GEMM + LayerNorm/GELU kernel
                 if self.use_graph:
                     # warm up on a side stream (cuBLAS handles / workspaces), then capture once
                     p.kpts.zero_()

@@ -69,6 +69,40 @@ def test_layernorm_gelu_kernel(pkg, rows, ld):
     assert torch.equal(got[:, 512:], h[:, 512:])
 
 
+@pytest.mark.parametrize("rows,ldx,ldh", [(1, 512, 512), (77, 512, 512), (128, 512, 512), (1031, 512, 640), (20000, 512, 512), (40000, 768, 512)])
+def test_fused_ffn1_ln_gelu_kernel(pkg, rows, ldx, ldh):
+    """ffn[0..2] (Linear 512->512, LayerNorm, erf GELU; lightglue.py:131-136) as one tcgen05 kernel against an FP64 restatement:
+    ragged last tile, several tiles per persistent CTA (20000 rows = 157 tiles on 148 SMs), strided input / output rows with a
+    sentinel in the gaps and past the last row."""
+    g = torch.Generator().manual_seed(rows + ldx)
+    x = torch.randn(rows, ldx, generator=g).half()
+    w = (torch.randn(512, 512, generator=g) / 512 ** 0.5 * 1.5).half()
+    bias = (torch.randn(512, generator=g) * 0.5).half()
+    gamma = torch.randn(512, generator=g)
+    beta = torch.randn(512, generator=g)
+    guard = 3
+    out = torch.full((rows + guard, ldh), -7.0).half()
+    od = out.clone().to(DEV)
+    pkg.matcher.ffn1_ln_gelu(x.to(DEV)[:, :512], w.to(DEV), bias.to(DEV), gamma.to(DEV), beta.to(DEV), od[:rows, :512])
+    got = od.cpu()
+    pre = x[:, :512].double() @ w.double().t() + bias.double()
+    want = F.gelu(F.layer_norm(pre, (512,), gamma.double(), beta.double(), 1e-5))
+    # Like the library GEMM + lg_match_layernorm_gelu path, the kernel holds the pre-LayerNorm values in FP16 (statistics are taken
+    # in FP32 before that rounding).  Bars: against the same computation on FP16-rounded pre-activations only the output rounding
+    # (2^-11 relative) and the erf approximation remain; against exact arithmetic the rounding of values up to ~6 adds up to
+    # ~5e-3 after the affine (|gamma| up to ~3.5).
+    want_h = F.gelu(F.layer_norm(pre.half().double(), (512,), gamma.double(), beta.double(), 1e-5))
+    g = got[:rows, :512].double()
+    # (elementwise, except where the FP32 accumulator and the FP64 product round to different FP16 neighbours: rare, <= 1 ulp of
+    # the pre-activation)
+    off = ((g - want_h).abs() > 6e-4 * want_h.abs() + 4e-4).double().mean()
+    assert float(off) <= 2e-3, float(off)
+    err = (g - want).abs()
+    assert float(err.max()) <= 1.2e-2, float(err.max())
+    assert float(err.mean()) <= 6e-4, float(err.mean())
+    assert torch.equal(got[rows:], out[rows:]) and torch.equal(got[:, 512:], out[:, 512:])   # nothing written outside [rows, 512]
+
+
 @pytest.mark.parametrize("b,n0,n1", [(1, 1, 1), (1, 1, 70), (1, 160, 130), (3, 257, 64), (2, 512, 515), (1, 1024, 1024)])
 def test_assignment_kernels_match_oracle(pkg, b, n0, n1):
     g = torch.Generator().manual_seed(n0 * 3 + n1)
@@ -155,6 +189,30 @@ def test_batched_ragged_pairs_match_oracle(pkg):
         assert torch.equal(alone["matches0"].cpu()[0], m0[i])
 
 
+def test_fused_and_unfused_ffn_paths_agree(pkg, monkeypatch):
+    """The same forward through the fused ffn-up kernel and through library GEMM + lg_match_layernorm_gelu (LG_MATCH_FUSED_FFN=0),
+    at a shape big enough for the fused path to be chosen: scores agree to FP16-path noise, match sets almost entirely."""
+    n_layers, b, n = 3, 6, 1100   # 13 200 rows = 104 tiles: fused by the heuristic
+    sd = pkg.reference_init_state_dict(5, n_layers)
+    feats = [mo.synth_pair(300 + i, n, n) for i in range(b)]
+    f = [torch.cat([x[j] for x in feats]).to(DEV) for j in range(4)]
+    assert pkg.load().lg_match_ffn1_prefer_fused(2 * b * n) == 1
+    a = pkg.PairMatcher(sd, n_layers=n_layers, threshold=0.0, device=DEV)
+    assert a.fused_ffn
+    ra = a.match(*f, want_scores=True)
+    sa, ma, la = ra["scores"].clone(), ra["matches0"].clone(), ra["launches"]
+    monkeypatch.setenv("LG_MATCH_FUSED_FFN", "0")
+    c = pkg.PairMatcher(sd, n_layers=n_layers, threshold=0.0, device=DEV)
+    assert not c.fused_ffn
+    rc = c.match(*f, want_scores=True)
+    assert rc["launches"] == la + 2 * n_layers
+    assert float((rc["scores"] - sa).abs().max()) <= 0.03
+    assert float((rc["matches0"] == ma).float().mean()) >= 0.98
+    # and against the FP32 CPU oracle, first pair
+    want = mo.forward(sd, *feats[0], n_layers=n_layers, threshold=0.0)
+    assert float((sa[0].cpu() - want["scores"][0]).abs().max()) <= TOL_SCORES_MAX
+
+
 def test_graph_replay_equals_eager(pkg):
     n_layers = 2
     sd = pkg.reference_init_state_dict(8, n_layers)
@@ -222,6 +280,32 @@ def test_config4_full_size_pair_matches_oracle(pkg, n, capsys):
               f"disagreements {gap:.4f})")
     assert float(err.max()) <= TOL_SCORES_MAX and float(err.mean()) <= TOL_SCORES_MEAN
     assert agree >= MIN_MATCH_AGREEMENT and gap < 0.1
+
+
+def test_batched_full_depth_pairs_through_the_fused_ffn_match_oracle(pkg, capsys):
+    """The batched configuration the pairs/s numbers are quoted on runs the fused ffn-up kernel (a single pair does not: too few
+    rows, lg_match_ffn1_prefer_fused): 8 pairs x 1024 keypoints, all 9 layers, every pair against the FP32 CPU oracle."""
+    b, n = 8, 1024
+    sd = pkg.reference_init_state_dict(0, 9)
+    feats = [mo.synth_pair(2000 + i, n, n) for i in range(b)]
+    matcher = pkg.PairMatcher(sd, n_layers=9, threshold=0.0, device=DEV)
+    out = matcher.match(*(torch.cat([f[j] for f in feats]).to(DEV) for j in range(4)), want_scores=True)
+    assert matcher.fused_ffn and matcher.plan(b, n, n, True).prefer_fused_ffn
+    worst_max = worst_mean = 0.0
+    n_ref = n_same = 0
+    for i, f in enumerate(feats):
+        want = mo.forward(sd, *f, n_layers=9, threshold=0.0)
+        err = (out["scores"][i:i + 1].cpu() - want["scores"]).abs()
+        worst_max, worst_mean = max(worst_max, float(err.max())), max(worst_mean, float(err.mean()))
+        agree, gap = _agreement(want["scores"], out["matches0"][i:i + 1])
+        assert agree >= MIN_MATCH_AGREEMENT and gap < 0.1, (i, agree, gap)
+        ref_m = want["matches0"][0]
+        n_ref += int((ref_m >= 0).sum())
+        n_same += int(((out["matches0"][i].cpu().long() == ref_m) & (ref_m >= 0)).sum())
+    with capsys.disabled():
+        print(f"\n[fused ffn parity] {b} pairs x {n} kpts, 9 layers: scores max-abs err {worst_max:.4f}, worst mean-abs {worst_mean:.5f}; "
+              f"mutual-NN matches in the reference {n_ref}, reproduced {n_same} ({100.0 * n_same / max(n_ref, 1):.2f} %)")
+    assert worst_max <= TOL_SCORES_MAX and worst_mean <= TOL_SCORES_MEAN
 
 
 def test_assignment_survives_nan_and_inf_rows(pkg):
@@ -313,7 +397,9 @@ def test_native_engine_host_buffers_batches_and_replanning(pkg):
         feats = [mo.synth_pair(70 + i, n0, n1) for i in range(b)]
         k0, k1, d0, d1 = (torch.cat([f[j] for f in feats]) for j in range(4))
         launches = eng.plan(b, n0, n1)
-        assert launches == (1 + n_layers * (13 if n0 != n1 else 11) + 9)
+        # per layer: 2 x (in-proj, [rotary,] attention x 1 or 2, ffn-up (fused: 1 launch, else GEMM + LayerNorm/GELU), ffn-down)
+        fused = pkg.load().lg_match_ffn1_prefer_fused(b * (n0 + n1))
+        assert launches == (1 + n_layers * ((13 if n0 != n1 else 11) - (2 if fused else 0)) + 9)
         host = eng.match_host(k0.numpy(), k1.numpy(), d0.half().numpy(), d1.half().numpy())
         dev = eng.match(k0.to(DEV), k1.to(DEV), d0.half().to(DEV), d1.half().to(DEV))
         torch.cuda.synchronize()
