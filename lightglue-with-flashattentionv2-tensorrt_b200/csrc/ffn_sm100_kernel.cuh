@@ -296,4 +296,217 @@ ffn1_ln_gelu_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_const
     }
 }
 
+// ================================================================================================================================
+// Few rows (a single image pair: 16 or 32 tiles): the kernel above would leave most SMs idle, one whole tile of arithmetic per CTA on
+// the critical path.  Here a CLUSTER of 4 CTAs shares a 128-row tile and each takes 128 of the 512 hidden columns (a quarter of
+// the MMAs, of W1' and of the epilogue); the LayerNorm statistics cross the cluster once per tile: every CTA pushes its per-row
+// (mean, M2) over 128 columns into all four CTAs' shared memory (st.shared::cluster), one release / acquire cluster barrier
+// publishes them.  One tile per cluster (no persistence), programmatic dependent launch: barrier init, TMEM allocation and the
+// parameter loads (weights, not produced by the previous kernel) run before griddepcontrol.wait.
+namespace small {
+
+constexpr int kSplit = 4;                 // cluster size = column quarters
+constexpr int kNC = kN / kSplit;          // 128 columns per CTA
+constexpr int kStagesS = 4;
+constexpr int kColsPerWarpS = kNC / (kEpiWarps / 4);   // 32
+constexpr uint32_t kBBytesS = kNC * kBK * 2;           // 16 KiB
+constexpr uint32_t kStageBytesS = kABytes + kBBytesS;  // 32 KiB
+constexpr uint32_t kSmemRingS = 0;
+constexpr uint32_t kSmemStageS = kSmemRingS + kStagesS * kStageBytesS;       // 16 x 2 KiB output staging
+constexpr uint32_t kSmemParamsS = kSmemStageS + kEpiWarps * kStageTile;      // bias | gamma | beta, this CTA's 128 columns each
+constexpr uint32_t kSmemStatsS = kSmemParamsS + 3 * kNC * 4;                 // [column group][row] (mean, M2) inside the CTA
+constexpr uint32_t kSmemXStatsS = kSmemStatsS + 4 * kBM * 8;                 // [source CTA][row] (mean, M2) across the cluster
+constexpr uint32_t kSmemBarS = kSmemXStatsS + kSplit * kBM * 8;
+enum : uint32_t { kBarFullS = 0, kBarEmptyS = kStagesS, kBarAccFullS = 2 * kStagesS, kNumBarsS };
+constexpr uint32_t kSmemTmemSlotS = kSmemBarS + 8 * kNumBarsS;
+constexpr uint32_t kSmemBytesS = kSmemTmemSlotS + 16 + 1024;
+static_assert(kSmemBytesS <= 227 * 1024, "shared memory budget");
+
+// Chan's parallel-variance combine of four partials over n values each: (mean, M2) of the 4 n values
+__device__ __forceinline__ float2 combine4(float2 p0, float2 p1, float2 p2, float2 p3, float n) {
+    const float mean = 0.25f * ((p0.x + p1.x) + (p2.x + p3.x));
+    const float e0 = p0.x - mean, e1 = p1.x - mean, e2 = p2.x - mean, e3 = p3.x - mean;
+    return make_float2(mean, ((p0.y + p1.y) + (p2.y + p3.y)) + n * ((e0 * e0 + e1 * e1) + (e2 * e2 + e3 * e3)));
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+ffn1_ln_gelu_small_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w,
+                          const __grid_constant__ CUtensorMap tm_h, const __half* __restrict__ bias, const float* __restrict__ gamma,
+                          const float* __restrict__ beta, float eps) {
+    extern __shared__ uint8_t smem_raw[];
+    uint32_t smem = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    asm volatile("mov.u32 %0, %0;" : "+r"(smem));
+    const uint32_t bars = smem + kSmemBarS;
+    auto bar = [&](uint32_t i) { return bars + 8u * i; };
+
+    const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
+    const int lane = threadIdx.x & 31;
+    constexpr int kWarpTMA = kEpiWarps, kWarpMMA = kEpiWarps + 1;
+    const int rank = static_cast<int>(cluster_ctarank());
+    const int tile = blockIdx.x / kSplit;
+    const int col0 = rank * kNC;   // this CTA's first hidden column
+
+    cluster_arrive();   // barrier #1 (waited for in front of the statistics push): every CTA of the cluster is running
+    if (warp == kWarpTMA && lane == 0) {
+        prefetch_tmap(&tm_x);
+        prefetch_tmap(&tm_w);
+        prefetch_tmap(&tm_h);
+#pragma unroll
+        for (int s = 0; s < kStagesS; ++s) {
+            mbar_init(bar(kBarFullS + s), 1);
+            mbar_init(bar(kBarEmptyS + s), 1);
+        }
+        mbar_init(bar(kBarAccFullS), 1);
+        fence_mbar_init();
+    }
+    if (warp == kWarpMMA) {
+        tmem_alloc<kNC>(smem + kSmemTmemSlotS);
+        tmem_relinquish();
+    }
+    if (threadIdx.x < kNC) {
+        st_shared_f32(smem + kSmemParamsS + 4u * threadIdx.x, __half2float(bias[col0 + threadIdx.x]));
+        st_shared_f32(smem + kSmemParamsS + 4u * (kNC + threadIdx.x), gamma[col0 + threadIdx.x]);
+        st_shared_f32(smem + kSmemParamsS + 4u * (2 * kNC + threadIdx.x), beta[col0 + threadIdx.x]);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    uint32_t tmem_base;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(smem + kSmemTmemSlotS));
+
+    // everything above touched only weights and this CTA's own state; the activations belong to the previous kernel
+    pdl_wait_prior_grids();
+    if (threadIdx.x == 0) pdl_launch_dependents();
+
+    if (warp >= kEpiWarps) {
+        const uint32_t smem_u = (smem_u32(smem_raw) + 1023u) & ~1023u;
+        const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
+        const uint32_t bars_u = smem_u + kSmemBarS;
+        auto ubar = [&](uint32_t i) { return bars_u + 8u * i; };
+        if (warp == kWarpTMA) {
+#pragma unroll 1
+            for (int k = 0; k < kKSteps; ++k) {
+                const int s = k % kStagesS;
+                if (k >= kStagesS) mbar_wait_backoff(ubar(kBarEmptyS + s), ((k / kStagesS) - 1) & 1, 64);
+                if (elect_one()) {
+                    const uint32_t dst = smem_u + kSmemRingS + s * kStageBytesS;
+                    mbar_arrive_expect_tx(ubar(kBarFullS + s), kStageBytesS);
+                    tma_load_4d(dst, &tm_x, ubar(kBarFullS + s), k * kBK, tile * kBM, 0, 0);
+                    tma_load_4d(dst + kABytes, &tm_w, ubar(kBarFullS + s), k * kBK, col0, 0, 0);
+                }
+                __syncwarp();
+            }
+        } else if (warp == kWarpMMA) {
+            constexpr uint32_t idesc = make_idesc_f16_f32acc(kBM, kNC, false);
+#pragma unroll 1
+            for (int k = 0; k < kKSteps; ++k) {
+                const int s = k % kStagesS;
+                mbar_wait(ubar(kBarFullS + s), (k / kStagesS) & 1);
+                tc_fence_after();
+                if (elect_one()) {
+                    const uint32_t a = smem_u + kSmemRingS + s * kStageBytesS;
+                    const uint64_t desc_a = make_smem_desc_sw128(a, 16, 1024);
+                    const uint64_t desc_b = make_smem_desc_sw128(a + kABytes, 16, 1024);
+#pragma unroll
+                    for (int kk = 0; kk < kBK / 16; ++kk)
+                        mma_f16_ss(tmem_u, desc_a + 2u * kk, desc_b + 2u * kk, idesc, (k > 0 || kk > 0) ? 1u : 0u);
+                    mma_commit(ubar(kBarEmptyS + s));
+                    if (k == kKSteps - 1) mma_commit(ubar(kBarAccFullS));
+                }
+                __syncwarp();
+            }
+        }
+        cluster_wait();     // #1
+        cluster_arrive();   // #2: the service warps have nothing to publish
+        cluster_wait();
+    } else {
+        const int quarter = warp & 3, cg = warp >> 2;
+        const int row = quarter * 32 + lane;
+        const uint32_t t_acc = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + static_cast<uint32_t>(cg * kColsPerWarpS);
+        const uint32_t p_bias = smem + kSmemParamsS + 4u * (cg * kColsPerWarpS);
+        const uint32_t p_gamma = p_bias + 4u * kNC, p_beta = p_bias + 8u * kNC;
+        const uint32_t stg = smem + kSmemStageS + static_cast<uint32_t>(warp) * kStageTile;
+        const uint32_t stg_row = stg + static_cast<uint32_t>(lane) * 64u;
+        const uint32_t swz = static_cast<uint32_t>((lane >> 1) & 3);
+
+        mbar_wait(bar(kBarAccFullS), 0);
+        tc_fence_after();
+        uint32_t v[32];
+        tmem_ld_x32(t_acc, v);
+        tmem_wait_ld();
+        float a[kColsPerWarpS];
+        float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+        for (int i = 0; i < kColsPerWarpS; i += 4) {
+            const float4 b = ld_shared_v4f(p_bias + 4u * i);
+            a[i] = __uint_as_float(v[i]) + b.x;
+            a[i + 1] = __uint_as_float(v[i + 1]) + b.y;
+            a[i + 2] = __uint_as_float(v[i + 2]) + b.z;
+            a[i + 3] = __uint_as_float(v[i + 3]) + b.w;
+        }
+        const float shift = a[0];
+#pragma unroll
+        for (int i = 0; i < kColsPerWarpS; ++i) {
+            const float d = a[i] - shift;
+            s1 += d;
+            s2 = fmaf(d, d, s2);
+            // hold the pre-activation at FP16 precision, like the large-shape kernel and the library-GEMM path (identical numerics
+            // whichever path a shape takes)
+            a[i] = __half2float(__float2half_rn(a[i]));
+        }
+        constexpr float kInv = 1.0f / kColsPerWarpS;
+        const float dm = s1 * kInv;
+        st_shared_v2f(smem + kSmemStatsS + static_cast<uint32_t>(cg * kBM + row) * 8u, shift + dm, fmaxf(fmaf(-dm, s1, s2), 0.f));
+        named_bar_sync(1u + static_cast<uint32_t>(quarter), 128u);
+        const uint32_t sb = smem + kSmemStatsS + static_cast<uint32_t>(row) * 8u;
+        const float2 cta = combine4(ld_shared_v2f(sb), ld_shared_v2f(sb + kBM * 8u), ld_shared_v2f(sb + 2u * kBM * 8u),
+                                    ld_shared_v2f(sb + 3u * kBM * 8u), static_cast<float>(kColsPerWarpS));
+        cluster_wait();     // #1: the peers are running, their shared memory may be written
+        if (cg == 0) {
+            const uint32_t mine = smem + kSmemXStatsS + static_cast<uint32_t>(rank * kBM + row) * 8u;
+#pragma unroll
+            for (int r = 0; r < kSplit; ++r) st_dsmem_v2(dsmem_addr(mine, static_cast<uint32_t>(r)), cta.x, cta.y);
+        }
+        cluster_arrive();   // #2 (release): the four CTAs' partials of every row are published ...
+        cluster_wait();     //    (acquire) ... and visible; nobody writes a peer's shared memory after this
+        const uint32_t xb = smem + kSmemXStatsS + static_cast<uint32_t>(row) * 8u;
+        const float2 full = combine4(ld_shared_v2f(xb), ld_shared_v2f(xb + kBM * 8u), ld_shared_v2f(xb + 2u * kBM * 8u),
+                                     ld_shared_v2f(xb + 3u * kBM * 8u), static_cast<float>(kNC));
+        const float rstd = rsqrtf(full.y * (1.0f / kN) + eps);
+        const float nmr = -full.x * rstd;
+        uint32_t o[kColsPerWarpS / 2];
+#pragma unroll
+        for (int i = 0; i < kColsPerWarpS; i += 4) {
+            const float4 g4 = ld_shared_v4f(p_gamma + 4u * i);
+            const float4 b4 = ld_shared_v4f(p_beta + 4u * i);
+            const float y0 = lgmatch::gelu_erf(fmaf(fmaf(a[i], rstd, nmr), g4.x, b4.x));
+            const float y1 = lgmatch::gelu_erf(fmaf(fmaf(a[i + 1], rstd, nmr), g4.y, b4.y));
+            const float y2 = lgmatch::gelu_erf(fmaf(fmaf(a[i + 2], rstd, nmr), g4.z, b4.z));
+            const float y3 = lgmatch::gelu_erf(fmaf(fmaf(a[i + 3], rstd, nmr), g4.w, b4.w));
+            o[i / 2] = pack_half2(y0, y1);
+            o[i / 2 + 1] = pack_half2(y2, y3);
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            st_shared_v4(stg_row + ((static_cast<uint32_t>(j) ^ swz) << 4), o[4 * j], o[4 * j + 1], o[4 * j + 2], o[4 * j + 3]);
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (elect_one()) {
+            tma_store_4d(&tm_h, stg, col0 + cg * kColsPerWarpS, tile * kBM + quarter * 32, 0, 0);
+            bulk_commit_group();
+            bulk_wait_group_read0();
+        }
+        __syncwarp();
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == kWarpMMA) {
+        tc_fence_after();
+        tmem_dealloc<kNC>(tmem_base);
+    }
+}
+
+}  // namespace small
+
 }  // namespace lgffn

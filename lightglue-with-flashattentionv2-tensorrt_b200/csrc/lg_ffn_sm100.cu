@@ -8,6 +8,7 @@
 #include <cuda_runtime.h>
 
 #include <atomic>
+#include <cstdlib>
 #include <mutex>
 
 #include "../../include/lg_attn.h"
@@ -26,6 +27,9 @@ std::mutex g_mutex;
 std::atomic<int> g_ready[kMaxDevices];
 std::atomic<EncodeTiledFn> g_encode{nullptr};
 int g_sms[kMaxDevices];
+int g_small_clusters[kMaxDevices];   // co-resident 4-CTA clusters of the few-rows kernel
+std::atomic<int> g_small_enabled{1}; // LG_MATCH_FFN_SMALL=0: no few-rows kernel (A/B runs)
+std::atomic<int> g_pdl{1};           // LG_ATTN_PDL=0: no programmatic dependent launch
 
 int init_locked(int device) {
     cudaDeviceProp prop;
@@ -46,9 +50,34 @@ int init_locked(int device) {
     if ((e = cudaGetDevice(&prev)) != cudaSuccess) return static_cast<int>(e);
     if ((e = cudaSetDevice(device)) != cudaSuccess) return static_cast<int>(e);
     e = cudaFuncSetAttribute(ffn1_ln_gelu_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemBytes));
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(small::ffn1_ln_gelu_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 static_cast<int>(small::kSmemBytesS));
+    if (e == cudaSuccess) {
+        // how many 4-CTA clusters of the few-rows kernel are resident at once (one tile each, no persistence: a launch must fit)
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(static_cast<unsigned>(prop.multiProcessorCount / small::kSplit * small::kSplit));
+        cfg.blockDim = dim3(kThreads);
+        cfg.dynamicSmemBytes = small::kSmemBytesS;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = small::kSplit;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        int n = 0;
+        if (cudaOccupancyMaxActiveClusters(&n, small::ffn1_ln_gelu_small_kernel, &cfg) != cudaSuccess) {
+            (void)cudaGetLastError();
+            n = 0;
+        }
+        g_small_clusters[device] = n;
+    }
     (void)cudaSetDevice(prev);
     if (e != cudaSuccess) return static_cast<int>(e);
     g_sms[device] = prop.multiProcessorCount;
+    if (const char* env = getenv("LG_MATCH_FFN_SMALL")) g_small_enabled.store(atoi(env) != 0 ? 1 : 0, std::memory_order_relaxed);
+    if (const char* env = getenv("LG_ATTN_PDL")) g_pdl.store(atoi(env) != 0 ? 1 : 0, std::memory_order_relaxed);
     return 0;
 }
 
@@ -65,6 +94,11 @@ int encode_matrix(CUtensorMap* map, const void* base, long long rows, int cols, 
         map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
         swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     return r == CUDA_SUCCESS ? 0 : LG_ATTN_EDRIVER;
+}
+
+bool use_small(int device, long long tiles) {
+    return device >= 0 && device < kMaxDevices && g_ready[device].load(std::memory_order_acquire) &&
+           g_small_enabled.load(std::memory_order_relaxed) && tiles <= g_small_clusters[device];
 }
 
 }  // namespace
@@ -89,7 +123,9 @@ int lg_match_ffn1_prefer_fused(long long rows) {
     if (cudaGetDevice(&device) == cudaSuccess && device >= 0 && device < kMaxDevices && g_ready[device].load(std::memory_order_acquire))
         sms = g_sms[device];
     const long long tiles = (rows + kBM - 1) / kBM;
-    return tiles * 3 >= static_cast<long long>(sms) * 2 ? 1 : 0;
+    if (tiles * 3 >= static_cast<long long>(sms) * 2) return 1;
+    // very few rows (a single pair): the 4-CTA-cluster kernel, one tile per cluster, when every cluster is resident at once
+    return use_small(device, tiles) ? 1 : 0;
 }
 
 int lg_match_ffn1_ln_gelu(const void* x_half, long long rows, int ldx, const void* w_nk_half, const void* bias_half,
@@ -106,11 +142,38 @@ int lg_match_ffn1_ln_gelu(const void* x_half, long long rows, int ldx, const voi
     int rc = lg_match_ffn_init_device(device);
     if (rc != 0) return rc;
 
+    const int tiles = static_cast<int>((rows + kBM - 1) / kBM);
+    const bool small_shape = use_small(device, tiles);
     CUtensorMap tm_x, tm_w, tm_h;
     if ((rc = encode_matrix(&tm_x, x_half, rows, kK, ldx, kBK, kBM, CU_TENSOR_MAP_SWIZZLE_128B)) != 0) return rc;
-    if ((rc = encode_matrix(&tm_w, w_nk_half, kN, kK, kK, kBK, 256, CU_TENSOR_MAP_SWIZZLE_128B)) != 0) return rc;
+    if ((rc = encode_matrix(&tm_w, w_nk_half, kN, kK, kK, kBK, small_shape ? small::kNC : 256, CU_TENSOR_MAP_SWIZZLE_128B)) != 0) return rc;
     if ((rc = encode_matrix(&tm_h, hid_half, rows, kN, ldh, kRound, 32, CU_TENSOR_MAP_SWIZZLE_64B)) != 0) return rc;
-    const int tiles = static_cast<int>((rows + kBM - 1) / kBM);
+    if (small_shape) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(static_cast<unsigned>(tiles) * small::kSplit);
+        cfg.blockDim = dim3(kThreads);
+        cfg.dynamicSmemBytes = small::kSmemBytesS;
+        cfg.stream = static_cast<cudaStream_t>(stream);
+        cudaLaunchAttribute attrs[2];
+        int n_attrs = 0;
+        attrs[n_attrs].id = cudaLaunchAttributeClusterDimension;
+        attrs[n_attrs].val.clusterDim.x = small::kSplit;
+        attrs[n_attrs].val.clusterDim.y = 1;
+        attrs[n_attrs].val.clusterDim.z = 1;
+        ++n_attrs;
+        if (g_pdl.load(std::memory_order_relaxed)) {
+            // the prologue (barriers, TMEM, parameter loads) may overlap the previous kernel's tail; the kernel waits at
+            // griddepcontrol.wait before it touches an activation
+            attrs[n_attrs].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            attrs[n_attrs].val.programmaticStreamSerializationAllowed = 1;
+            ++n_attrs;
+        }
+        cfg.attrs = attrs;
+        cfg.numAttrs = static_cast<unsigned>(n_attrs);
+        e = cudaLaunchKernelEx(&cfg, small::ffn1_ln_gelu_small_kernel, tm_x, tm_w, tm_h, static_cast<const __half*>(bias_half), gamma,
+                               beta, eps);
+        return static_cast<int>(e);
+    }
     const int grid = tiles < g_sms[device] ? tiles : g_sms[device];
     ffn1_ln_gelu_kernel<<<grid, kThreads, kSmemBytes, static_cast<cudaStream_t>(stream)>>>(
         tm_x, tm_w, tm_h, static_cast<const __half*>(bias_half), gamma, beta, eps, tiles);

@@ -69,11 +69,12 @@ def test_layernorm_gelu_kernel(pkg, rows, ld):
     assert torch.equal(got[:, 512:], h[:, 512:])
 
 
-@pytest.mark.parametrize("rows,ldx,ldh", [(1, 512, 512), (77, 512, 512), (128, 512, 512), (1031, 512, 640), (20000, 512, 512), (40000, 768, 512)])
+@pytest.mark.parametrize("rows,ldx,ldh", [(1, 512, 512), (77, 512, 512), (128, 512, 512), (1031, 512, 640), (4736, 512, 512), (4737, 768, 512), (20000, 512, 512), (40000, 768, 512)])
 def test_fused_ffn1_ln_gelu_kernel(pkg, rows, ldx, ldh):
     """ffn[0..2] (Linear 512->512, LayerNorm, erf GELU; lightglue.py:131-136) as one tcgen05 kernel against an FP64 restatement:
     ragged last tile, several tiles per persistent CTA (20000 rows = 157 tiles on 148 SMs), strided input / output rows with a
-    sentinel in the gaps and past the last row."""
+    sentinel in the gaps and past the last row.  Up to 37 tiles (4736 rows) the launcher takes the few-rows kernel (4-CTA clusters
+    splitting the 512 columns, statistics exchanged through distributed shared memory), above that the persistent one."""
     g = torch.Generator().manual_seed(rows + ldx)
     x = torch.randn(rows, ldx, generator=g).half()
     w = (torch.randn(512, 512, generator=g) / 512 ** 0.5 * 1.5).half()
