@@ -15,6 +15,7 @@
 #include <stdint.h>
 
 #include <atomic>
+#include <cstdlib>
 #include <mutex>
 
 #include "../../include/lg_attn.h"
@@ -44,9 +45,21 @@ __device__ __forceinline__ float warp_sum(float v) {
     return v;
 }
 
+// Programmatic dependent launch (the single-pair forward is a chain of ~100 short kernels, launch-to-launch latency is a large
+// part of it): every glue kernel is launched with the programmatic-stream-serialization attribute (launch_glue below), so it may
+// be scheduled while its predecessor is still running; it must therefore wait for the predecessor's completion before touching
+// memory, and it lets its own successor be scheduled at once.  Completion is transitive along the chain: the predecessor did the
+// same wait before its first access.  Without the attribute (LG_ATTN_PDL=0) both instructions are no-ops.
+#define LG_GLUE_PDL_ENTRY()                                        \
+    do {                                                           \
+        asm volatile("griddepcontrol.wait;" ::: "memory");         \
+        asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); \
+    } while (0)
+
 // ------------------------------------------------------------------------------------------ posenc
 __global__ void __launch_bounds__(256) posenc_kernel(const float2* __restrict__ kpts, const float2* __restrict__ wr,
                                                      float2* __restrict__ cs, long long total) {
+    LG_GLUE_PDL_ENTRY();
     for (long long t = blockIdx.x * 256LL + threadIdx.x; t < total; t += gridDim.x * 256LL) {
         const long long r = t >> 5;
         const int i = static_cast<int>(t & 31);
@@ -63,6 +76,9 @@ __global__ void __launch_bounds__(256) posenc_kernel(const float2* __restrict__ 
 // One thread = 8 halves (4 rotary pairs) of one head of one block of one row.
 __global__ void __launch_bounds__(256) rotary_kernel(__half* __restrict__ buf, long long rows, int ld, int chunks_per_row,
                                                      const float4* __restrict__ cs) {
+    // (the attention launch that follows is a programmatic dependent launch too: its CTAs set up — barriers, TMEM, tensor-map
+    // prefetch — while this kernel runs, and wait for this grid to complete before they read q / k)
+    LG_GLUE_PDL_ENTRY();
     const long long total = rows * chunks_per_row;
     for (long long t = blockIdx.x * 256LL + threadIdx.x; t < total; t += gridDim.x * 256LL) {
         const long long r = t / chunks_per_row;
@@ -91,6 +107,7 @@ __global__ void __launch_bounds__(256) rotary_kernel(__half* __restrict__ buf, l
 __global__ void __launch_bounds__(256) layernorm_gelu_kernel(__half* __restrict__ h, long long rows, int ld,
                                                              const float* __restrict__ gamma,
                                                              const float* __restrict__ beta, float eps) {
+    LG_GLUE_PDL_ENTRY();
     const int lane = threadIdx.x & 31;
     const long long warp0 = blockIdx.x * 8LL + (threadIdx.x >> 5);
     float g[16], b[16];
@@ -204,6 +221,7 @@ __global__ void __launch_bounds__(256) row_pass_kernel(const float* __restrict__
                                                        const __half* __restrict__ z0, long long z_stride,
                                                        const float* __restrict__ col_term, float* __restrict__ row_term,
                                                        int* __restrict__ m0, float* __restrict__ score0) {
+    LG_GLUE_PDL_ENTRY();
     const int lane = threadIdx.x & 31;
     for (long long r = blockIdx.x * 8LL + (threadIdx.x >> 5); r < rows; r += gridDim.x * 8LL) {
         const float* p = sim + r * n1;
@@ -261,6 +279,7 @@ template <int MODE, int VEC>
 __global__ void __launch_bounds__(256) col_partial_kernel(const float* __restrict__ sim, int n0, int n1,
                                                           const float* __restrict__ row_term,
                                                           float* __restrict__ part_a, float* __restrict__ part_b) {
+    LG_GLUE_PDL_ENTRY();
     __shared__ float sh_a[8][32 * VEC + 1];
     __shared__ float sh_b[8][32 * VEC + 1];
     const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
@@ -326,6 +345,7 @@ __global__ void __launch_bounds__(256) col_combine_kernel(const float* __restric
                                                           int n_parts, int n1, long long cols,
                                                           const __half* __restrict__ z1, long long z_stride,
                                                           float* __restrict__ col_term, int* __restrict__ m1) {
+    LG_GLUE_PDL_ENTRY();
     for (long long t = blockIdx.x * 256LL + threadIdx.x; t < cols; t += gridDim.x * 256LL) {
         const long long b = t / n1;
         const long long base = b * n_parts * n1 + (t - b * n1);
@@ -350,6 +370,7 @@ __global__ void __launch_bounds__(256) mutual_kernel(const int* __restrict__ m0,
                                                      const float* __restrict__ score0, int batch, int n0, int n1,
                                                      float threshold, int* __restrict__ matches0,
                                                      float* __restrict__ mscores0) {
+    LG_GLUE_PDL_ENTRY();
     const long long rows = static_cast<long long>(batch) * n0;
     for (long long r = blockIdx.x * 256LL + threadIdx.x; r < rows; r += gridDim.x * 256LL) {
         const long long b = r / n0;
@@ -369,6 +390,7 @@ __global__ void __launch_bounds__(256) mutual_kernel(const int* __restrict__ m0,
 __global__ void __launch_bounds__(256) scores_kernel(const float4* __restrict__ sim, long long rows, int n0, int n1,
                                                      const float* __restrict__ row_term,
                                                      const float* __restrict__ col_term, float4* __restrict__ scores) {
+    LG_GLUE_PDL_ENTRY();
     const int q = n1 >> 2;  // n1 % 4 == 0 on this path
     const long long total = rows * q;
     for (long long t = blockIdx.x * 256LL + threadIdx.x; t < total; t += gridDim.x * 256LL) {
@@ -385,6 +407,7 @@ __global__ void __launch_bounds__(256) scores_kernel_scalar(const float* __restr
                                                             const float* __restrict__ row_term,
                                                             const float* __restrict__ col_term,
                                                             float* __restrict__ scores) {
+    LG_GLUE_PDL_ENTRY();
     const long long total = rows * n1;
     for (long long t = blockIdx.x * 256LL + threadIdx.x; t < total; t += gridDim.x * 256LL) {
         const long long r = t / n1;
@@ -404,6 +427,31 @@ unsigned grid_for(long long work_items, int per_block, int waves = 8) {
 
 size_t align256(size_t x) { return (x + 255) & ~static_cast<size_t>(255); }
 
+// LG_ATTN_PDL=0 turns programmatic dependent launch off for the glue kernels as well (same switch as the attention launcher)
+bool glue_pdl() {
+    static const bool on = [] {
+        const char* env = getenv("LG_ATTN_PDL");
+        return env == nullptr || atoi(env) != 0;
+    }();
+    return on;
+}
+
+// <<<grid, 256, 0, stream>>> with the programmatic-stream-serialization attribute (see LG_GLUE_PDL_ENTRY)
+template <typename... KArgs, typename... Args>
+void launch_glue(void (*kernel)(KArgs...), dim3 grid, cudaStream_t stream, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(256);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = glue_pdl() ? 1u : 0u;
+    (void)cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);   // errors surface through last_error()
+}
+
 int last_error() { return static_cast<int>(cudaGetLastError()); }
 
 }  // namespace lgmatch
@@ -415,7 +463,7 @@ extern "C" {
 int lg_match_posenc(const float* kpts, const float* wr, float* cs, long long rows, void* stream) {
     if (kpts == nullptr || wr == nullptr || cs == nullptr || rows <= 0) return LG_ATTN_EINVAL;
     const long long total = rows * kAngles;
-    posenc_kernel<<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+    launch_glue(posenc_kernel, dim3(grid_for(total, 256)), static_cast<cudaStream_t>(stream), 
         reinterpret_cast<const float2*>(kpts), reinterpret_cast<const float2*>(wr), reinterpret_cast<float2*>(cs), total);
     return last_error();
 }
@@ -424,7 +472,7 @@ int lg_match_rotary(void* packed_half, long long rows, int ld, int n_blocks, con
     if (packed_half == nullptr || cs == nullptr || rows <= 0 || n_blocks <= 0) return LG_ATTN_EINVAL;
     if (ld < n_blocks * 256 || (ld & 7) != 0 || (reinterpret_cast<uintptr_t>(packed_half) & 15u) != 0) return LG_ATTN_EINVAL;
     const int chunks = n_blocks * 32;  // 16-byte chunks per row that carry rotary data
-    rotary_kernel<<<grid_for(rows * chunks, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+    launch_glue(rotary_kernel, dim3(grid_for(rows * chunks, 256)), static_cast<cudaStream_t>(stream), 
         static_cast<__half*>(packed_half), rows, ld, chunks, reinterpret_cast<const float4*>(cs));
     return last_error();
 }
@@ -433,7 +481,7 @@ int lg_match_layernorm_gelu(void* h_half, long long rows, int ld, const float* g
                             void* stream) {
     if (h_half == nullptr || gamma == nullptr || beta == nullptr || rows <= 0) return LG_ATTN_EINVAL;
     if (ld < kFfnCols || (ld & 7) != 0 || (reinterpret_cast<uintptr_t>(h_half) & 15u) != 0) return LG_ATTN_EINVAL;
-    layernorm_gelu_kernel<<<grid_for(rows, 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+    launch_glue(layernorm_gelu_kernel, dim3(grid_for(rows, 8)), static_cast<cudaStream_t>(stream), 
         static_cast<__half*>(h_half), rows, ld, gamma, beta, eps);
     return last_error();
 }
@@ -528,28 +576,28 @@ int lg_match_assign(const float* sim, const void* z0_half, const void* z1_half, 
     const unsigned row_grid = grid_for(rows0, 8, 16), cmb_grid = grid_for(rows1, 256);
 
     if (vec) {
-        row_pass_kernel<0, 4><<<row_grid, 256, 0, stream>>>(sim, n0, n1, rows0, z0, z_stride, nullptr, row_term, nullptr, nullptr);
-        col_partial_kernel<0, 4><<<col_grid, 256, 0, stream>>>(sim, n0, n1, row_term, part_a, part_b);
+        launch_glue(row_pass_kernel<0, 4>, dim3(row_grid), stream, sim, n0, n1, rows0, z0, z_stride, nullptr, row_term, nullptr, nullptr);
+        launch_glue(col_partial_kernel<0, 4>, dim3(col_grid), stream, sim, n0, n1, row_term, part_a, part_b);
     } else {
-        row_pass_kernel<0, 1><<<row_grid, 256, 0, stream>>>(sim, n0, n1, rows0, z0, z_stride, nullptr, row_term, nullptr, nullptr);
-        col_partial_kernel<0, 1><<<col_grid, 256, 0, stream>>>(sim, n0, n1, row_term, part_a, part_b);
+        launch_glue(row_pass_kernel<0, 1>, dim3(row_grid), stream, sim, n0, n1, rows0, z0, z_stride, nullptr, row_term, nullptr, nullptr);
+        launch_glue(col_partial_kernel<0, 1>, dim3(col_grid), stream, sim, n0, n1, row_term, part_a, part_b);
     }
-    col_combine_kernel<0><<<cmb_grid, 256, 0, stream>>>(part_a, part_b, parts, n1, rows1, z1, z_stride, col_term, nullptr);
+    launch_glue(col_combine_kernel<0>, dim3(cmb_grid), stream, part_a, part_b, parts, n1, rows1, z1, z_stride, col_term, nullptr);
     if (vec) {
-        row_pass_kernel<1, 4><<<row_grid, 256, 0, stream>>>(sim, n0, n1, rows0, z0, z_stride, col_term, row_term, m0, score0);
-        col_partial_kernel<1, 4><<<col_grid, 256, 0, stream>>>(sim, n0, n1, row_term, part_a, part_b);
+        launch_glue(row_pass_kernel<1, 4>, dim3(row_grid), stream, sim, n0, n1, rows0, z0, z_stride, col_term, row_term, m0, score0);
+        launch_glue(col_partial_kernel<1, 4>, dim3(col_grid), stream, sim, n0, n1, row_term, part_a, part_b);
     } else {
-        row_pass_kernel<1, 1><<<row_grid, 256, 0, stream>>>(sim, n0, n1, rows0, z0, z_stride, col_term, row_term, m0, score0);
-        col_partial_kernel<1, 1><<<col_grid, 256, 0, stream>>>(sim, n0, n1, row_term, part_a, part_b);
+        launch_glue(row_pass_kernel<1, 1>, dim3(row_grid), stream, sim, n0, n1, rows0, z0, z_stride, col_term, row_term, m0, score0);
+        launch_glue(col_partial_kernel<1, 1>, dim3(col_grid), stream, sim, n0, n1, row_term, part_a, part_b);
     }
-    col_combine_kernel<1><<<cmb_grid, 256, 0, stream>>>(part_a, part_b, parts, n1, rows1, z1, z_stride, nullptr, m1);
-    mutual_kernel<<<grid_for(rows0, 256), 256, 0, stream>>>(m0, m1, score0, batch, n0, n1, threshold, matches0, mscores0);
+    launch_glue(col_combine_kernel<1>, dim3(cmb_grid), stream, part_a, part_b, parts, n1, rows1, z1, z_stride, nullptr, m1);
+    launch_glue(mutual_kernel, dim3(grid_for(rows0, 256)), stream, m0, m1, score0, batch, n0, n1, threshold, matches0, mscores0);
     if (scores != nullptr) {
         if (vec && (reinterpret_cast<uintptr_t>(scores) & 15u) == 0)
-            scores_kernel<<<grid_for(rows0 * (n1 >> 2), 256), 256, 0, stream>>>(
+            launch_glue(scores_kernel, dim3(grid_for(rows0 * (n1 >> 2), 256)), stream, 
                 reinterpret_cast<const float4*>(sim), rows0, n0, n1, row_term, col_term, reinterpret_cast<float4*>(scores));
         else
-            scores_kernel_scalar<<<grid_for(rows0 * n1, 256), 256, 0, stream>>>(sim, rows0, n0, n1, row_term, col_term, scores);
+            launch_glue(scores_kernel_scalar, dim3(grid_for(rows0 * n1, 256)), stream, sim, rows0, n0, n1, row_term, col_term, scores);
     }
     return last_error();
 }
