@@ -13,6 +13,7 @@
  *                            (lightglue.py:131-136, 181-186)
  *   lg_match_ffn1_ln_gelu    ffn[0..2] of both stacks as one tcgen05 GEMM with the LayerNorm + GELU in its epilogue
  *                            (lightglue.py:131-136, 181-186)
+ *   lg_match_proj_rotary     Wqkv / to_qk|to_v projection with the rotary in the GEMM epilogue (lightglue.py:139-147, 190-193)
  *   lg_match_assign          sigmoid_log_double_softmax + filter_matches
  *                            (lightglue.py:216-224, 253-276; demo/lightglue_trt.cpp:291-345)
  *
@@ -62,6 +63,18 @@ int lg_match_ffn_init_device(int device);
  * else 0: its tiles are whole rows (128 x 512), so few rows leave most SMs idle (crossover on B200: about two thirds of the SM
  * count in tiles).  The matcher's callers ask this once per shape plan. */
 int lg_match_ffn1_prefer_fused(long long rows);
+
+/* Input projection of a transformer block with the rotary embedding in its epilogue, ONE launch (lightglue.py:139-147: Wqkv +
+ * apply_cached_rotary_emb on q, k; :190-193: to_qk | to_v): out[:, 256 t ..] = x @ w[256 t .., :]^T + bias for t < n_blocks, then
+ * blocks t < n_rot_blocks are rotated like lg_match_rotary does.  A hand-written tcgen05 GEMM (K = 256) with double-buffered TMEM
+ * accumulators; replaces a library GEMM + lg_match_rotary (no second pass over q | k, rotation applied before the FP16 rounding).
+ *   x    [rows, 256] FP16, row stride `ldx` elements;  w_nk [256 n_blocks (out), 256 (in)] FP16 contiguous (nn.Linear.weight layout)
+ *   bias FP16[256 n_blocks];  cs [rows, 32, 2] float from lg_match_posenc (may be NULL when n_rot_blocks == 0)
+ *   out  [rows, 256 n_blocks] FP16, row stride `ldo` elements;  n_blocks <= 3;  x, w_nk, out, cs 16-byte aligned. */
+int lg_match_proj_rotary(const void* x_half, long long rows, int ldx, const void* w_nk_half, const void* bias_half, int n_blocks,
+                         int n_rot_blocks, const float* cs, void* out_half, int ldo, void* stream);
+/* 1 when lg_match_proj_rotary is expected to beat a library GEMM (+ lg_match_rotary) for this shape on the current device. */
+int lg_match_proj_prefer_fused(long long rows, int n_blocks, int n_rot_blocks);
 
 /* Assignment + mutual-nearest-neighbour filter for `batch` pairs.
  *   sim  [batch, n0, n1] float  : mdesc0 . mdesc1^T (already divided by dim^0.25 on both sides)

@@ -55,6 +55,8 @@ MATCH_ABI_SYMBOLS = (
     "lg_match_ffn1_ln_gelu",
     "lg_match_ffn_init_device",
     "lg_match_ffn1_prefer_fused",
+    "lg_match_proj_rotary",
+    "lg_match_proj_prefer_fused",
     "lg_match_assign_workspace_bytes",
     "lg_match_assign",
     "lg_match_assign_static",
@@ -176,6 +178,10 @@ def load() -> ctypes.CDLL:
     lib.lg_match_ffn_init_device.argtypes = [I]
     lib.lg_match_ffn1_prefer_fused.restype = I
     lib.lg_match_ffn1_prefer_fused.argtypes = [LL]
+    lib.lg_match_proj_rotary.restype = I
+    lib.lg_match_proj_rotary.argtypes = [P, LL, I, P, P, I, I, P, P, I, P]
+    lib.lg_match_proj_prefer_fused.restype = I
+    lib.lg_match_proj_prefer_fused.argtypes = [LL, I, I]
     lib.lg_match_assign_workspace_bytes.restype = ctypes.c_size_t
     lib.lg_match_assign_workspace_bytes.argtypes = [I, I, I]
     lib.lg_match_assign.restype = I

@@ -1,8 +1,10 @@
-// C-ABI of the fused ffn-up kernel (declared in include/lg_match.h): host-side glue only — argument checks, per-device one-time
+// C-ABI of the matcher's hand-written GEMM kernels — fused ffn-up (ffn_sm100_kernel.cuh) and input projection + rotary
+// (proj_sm100_kernel.cuh) — declared in include/lg_match.h: host-side glue only — argument checks, per-device one-time
 // set-up, three TMA tensor maps per call (cuTensorMapEncodeTiled through cudaGetDriverEntryPoint: a pure host call, legal while a
 // stream is being captured) and one launch.  Never allocates, never synchronises.
 
 #include "ffn_sm100_kernel.cuh"
+#include "proj_sm100_kernel.cuh"
 
 #include <cuda.h>
 #include <cuda_runtime.h>
@@ -53,6 +55,9 @@ int init_locked(int device) {
     if (e == cudaSuccess)
         e = cudaFuncSetAttribute(small::ffn1_ln_gelu_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  static_cast<int>(small::kSmemBytesS));
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(lgproj::proj_rotary_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 static_cast<int>(lgproj::kSmemBytes));
     if (e == cudaSuccess) {
         // how many 4-CTA clusters of the few-rows kernel are resident at once (one tile each, no persistence: a launch must fit)
         cudaLaunchConfig_t cfg = {};
@@ -178,6 +183,61 @@ int lg_match_ffn1_ln_gelu(const void* x_half, long long rows, int ldx, const voi
     ffn1_ln_gelu_kernel<<<grid, kThreads, kSmemBytes, static_cast<cudaStream_t>(stream)>>>(
         tm_x, tm_w, tm_h, static_cast<const __half*>(bias_half), gamma, beta, eps, tiles);
     e = cudaGetLastError();
+    return static_cast<int>(e);
+}
+
+int lg_match_proj_prefer_fused(long long rows, int n_blocks, int n_rot_blocks) {
+    // Items are (128-row tile, 256-column block), one per CTA at a time.  Measured inside the matcher's CUDA graph (B200,
+    // tools/pairs_sweep.py, LG_MATCH_FUSED_PROJ=0/1): at 32 pairs x 1024 / 2048 keypoints the kernel gains 2 % of a forward (the
+    // rotary pass is gone, the GEMM itself runs at the library's speed: both sit at the ~4.3 TB/s a write-heavy stream reaches); for
+    // a single pair (16 - 32 row tiles) the library GEMM + lg_match_rotary pair is faster (0.478 vs 0.498 ms per 1024-keypoint pair):
+    // same rule as the ffn kernel, row tiles >= two thirds of the SM count.
+    (void)n_blocks;
+    (void)n_rot_blocks;
+    int device = 0, sms = 148;
+    if (cudaGetDevice(&device) == cudaSuccess && device >= 0 && device < kMaxDevices && g_ready[device].load(std::memory_order_acquire))
+        sms = g_sms[device];
+    if (const char* env = getenv("LG_MATCH_FUSED_PROJ")) {
+        const int v = atoi(env);
+        if (v == 0) return 0;
+        if (v == 2) return 1;   // always (A/B runs)
+    }
+    const long long tiles = (rows + lgproj::kBM - 1) / lgproj::kBM;
+    return tiles * 3 >= static_cast<long long>(sms) * 2 ? 1 : 0;
+}
+
+int lg_match_proj_rotary(const void* x_half, long long rows, int ldx, const void* w_nk_half, const void* bias_half, int n_blocks,
+                         int n_rot_blocks, const float* cs, void* out_half, int ldo, void* stream) {
+    if (x_half == nullptr || w_nk_half == nullptr || bias_half == nullptr || out_half == nullptr || rows <= 0 ||
+        rows > (1LL << 31) - lgproj::kBM || n_blocks < 1 || n_blocks > lgproj::kMaxBlocks || n_rot_blocks < 0 || n_rot_blocks > n_blocks ||
+        (n_rot_blocks > 0 && cs == nullptr))
+        return LG_ATTN_EINVAL;
+    if (ldx < lgproj::kK || ldo < n_blocks * lgproj::kBN || (ldx & 7) != 0 || (ldo & 7) != 0) return LG_ATTN_EINVAL;
+    if (((reinterpret_cast<uintptr_t>(x_half) | reinterpret_cast<uintptr_t>(w_nk_half) | reinterpret_cast<uintptr_t>(out_half) |
+          reinterpret_cast<uintptr_t>(cs)) & 15u) != 0)
+        return LG_ATTN_EINVAL;
+    int device = 0;
+    cudaError_t e = cudaGetDevice(&device);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    int rc = lg_match_ffn_init_device(device);
+    if (rc != 0) return rc;
+    CUtensorMap tm_x, tm_w, tm_o;
+    if ((rc = encode_matrix(&tm_x, x_half, rows, lgproj::kK, ldx, lgproj::kBK, lgproj::kBM, CU_TENSOR_MAP_SWIZZLE_128B)) != 0) return rc;
+    if ((rc = encode_matrix(&tm_w, w_nk_half, static_cast<long long>(n_blocks) * lgproj::kBN, lgproj::kK, lgproj::kK, lgproj::kBK, lgproj::kBN, CU_TENSOR_MAP_SWIZZLE_128B)) != 0) return rc;
+    if ((rc = encode_matrix(&tm_o, out_half, rows, n_blocks * lgproj::kBN, ldo, 32, 32, CU_TENSOR_MAP_SWIZZLE_64B)) != 0) return rc;
+    const long long items = (rows + lgproj::kBM - 1) / lgproj::kBM * n_blocks;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(static_cast<unsigned>(items < g_sms[device] ? items : g_sms[device]));
+    cfg.blockDim = dim3(lgproj::kThreads);
+    cfg.dynamicSmemBytes = lgproj::kSmemBytes;
+    cfg.stream = static_cast<cudaStream_t>(stream);
+    cudaLaunchAttribute attrs[1];
+    attrs[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attrs[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attrs;
+    cfg.numAttrs = g_pdl.load(std::memory_order_relaxed) ? 1u : 0u;
+    e = cudaLaunchKernelEx(&cfg, lgproj::proj_rotary_kernel, tm_x, tm_w, tm_o, static_cast<const __half*>(bias_half),
+                           reinterpret_cast<const float4*>(cs), rows, n_blocks, n_rot_blocks, static_cast<int>(items));
     return static_cast<int>(e);
 }
 

@@ -51,6 +51,7 @@ struct BlockW {           // device pointers into the blob copy
     const __half* w2_t;   // [512, 256]
     int n_in;
     const __half* w1_nk;  // [512 out, 512 in]: w1_t transposed at create time (outside the blob) — the fused ffn kernel's B operand
+    const __half* w_in_nk; // [n_in out, 256 in]: w_in_t transposed likewise — the fused projection kernel's B operand
 };
 
 size_t block_bytes(int n_in) {
@@ -165,6 +166,8 @@ struct lg_matcher : ShapePlan {   // the inherited members are the ACTIVE plan
     uint8_t* blob = nullptr;  // device copy of the weight blob
     __half* w1_nk = nullptr;  // [2 * n_layers][512][512]: every block's W1' in nn.Linear layout (see BlockW::w1_nk)
     bool fused_ffn = true;    // LG_MATCH_FUSED_FFN=0: library GEMM + lg_match_layernorm_gelu instead (A/B runs)
+    __half* w_in_nk = nullptr; // [n_layers][(768 + 512)][256]: every block's input projection in nn.Linear layout
+    bool fused_proj = true;   // LG_MATCH_FUSED_PROJ=0: library GEMM (+ lg_match_rotary) instead of lg_match_proj_rotary
     const float* wr = nullptr;
     std::vector<BlockW> self_w, cross_w;
     const __half *wf_t = nullptr, *bf = nullptr;
@@ -232,9 +235,15 @@ int forward(lg_matcher* m, cudaStream_t st, int* launches_out) {
     for (int l = 0; l < m->n_layers; ++l) {
         // ---- self attention on both images (lightglue.py:137-151)
         const BlockW& sw = m->self_w[l];
-        if ((rc = run_gemm(m->lt, m->g_qkv, x, sw.w_in_t, m->proj, sw.b_in, m->lt_ws, kLtWorkspace, st)) != 0) return rc;
-        if ((rc = lg_match_rotary(m->proj, R, 3 * kDim, 2, m->cs, st)) != 0) return rc;
-        launches += 2;
+        if (m->fused_proj && lg_match_proj_prefer_fused(R, 3, 2)) {
+            // Wqkv with the rotary of q, k in the GEMM epilogue: one launch, no second pass over q | k
+            if ((rc = lg_match_proj_rotary(x, R, kFfn, sw.w_in_nk, sw.b_in, 3, 2, m->cs, m->proj, 3 * kDim, st)) != 0) return rc;
+            ++launches;
+        } else {
+            if ((rc = run_gemm(m->lt, m->g_qkv, x, sw.w_in_t, m->proj, sw.b_in, m->lt_ws, kLtWorkspace, st)) != 0) return rc;
+            if ((rc = lg_match_rotary(m->proj, R, 3 * kDim, 2, m->cs, st)) != 0) return rc;
+            launches += 2;
+        }
         const long long ldp = 3 * kDim;
         if (n0 == n1) {
             rc = attention(m->proj, m->proj + kDim, m->proj + 2 * kDim, ldp, m->xc + kDim, 2 * B, n0, n0, 0);
@@ -248,7 +257,11 @@ int forward(lg_matcher* m, cudaStream_t st, int* launches_out) {
         if (rc != 0 || (rc = ffn(sw)) != 0) return rc;
         // ---- cross attention, both directions (lightglue.py:188-206); PROJ reused as [R, 512]: qk | v
         const BlockW& cw = m->cross_w[l];
-        if ((rc = run_gemm(m->lt, m->g_cross_in, x, cw.w_in_t, m->proj, cw.b_in, m->lt_ws, kLtWorkspace, st)) != 0) return rc;
+        if (m->fused_proj && lg_match_proj_prefer_fused(R, 2, 0))
+            rc = lg_match_proj_rotary(x, R, kFfn, cw.w_in_nk, cw.b_in, 2, 0, nullptr, m->proj, 2 * kDim, st);
+        else
+            rc = run_gemm(m->lt, m->g_cross_in, x, cw.w_in_t, m->proj, cw.b_in, m->lt_ws, kLtWorkspace, st);
+        if (rc != 0) return rc;
         ++launches;
         const long long ldc = 2 * kDim;
         if (n0 == n1) {
@@ -331,14 +344,17 @@ int lg_matcher_create(lg_matcher** out, int device, int n_layers, const void* we
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&m->ev_free[i], cudaEventDisableTiming);
     }
     if (const char* env = getenv("LG_MATCH_FUSED_FFN")) m->fused_ffn = atoi(env) != 0;
+    if (const char* env = getenv("LG_MATCH_FUSED_PROJ")) m->fused_proj = atoi(env) != 0;
     const size_t w1_elems = static_cast<size_t>(kFfn) * kFfn;
     if (e == cudaSuccess) e = cudaMalloc(&m->w1_nk, 2 * static_cast<size_t>(n_layers) * w1_elems * 2);
+    if (e == cudaSuccess) e = cudaMalloc(&m->w_in_nk, static_cast<size_t>(n_layers) * 5 * kDim * kDim * 2);
     if (e != cudaSuccess) { lg_matcher_destroy(m); return static_cast<int>(e); }
     // carve the device copy
     uint8_t* p = m->blob + align256(sizeof(BlobHeader));
     auto take = [&](size_t bytes) { uint8_t* q = p; p += align256(bytes); return q; };
     std::vector<uint16_t> w1_host(w1_elems);
     int n_blocks = 0;
+    size_t w_in_used = 0;   // elements of m->w_in_nk handed out
     m->wr = reinterpret_cast<const float*>(take(32 * 2 * 4));
     auto take_block = [&](int n_in) {
         BlockW w{};
@@ -358,6 +374,14 @@ int lg_matcher_create(lg_matcher** out, int device, int n_layers, const void* we
         __half* dst = m->w1_nk + static_cast<size_t>(n_blocks++) * w1_elems;
         if (e == cudaSuccess) e = cudaMemcpy(dst, w1_host.data(), w1_elems * 2, cudaMemcpyHostToDevice);
         w.w1_nk = dst;
+        const uint16_t* src_in = reinterpret_cast<const uint16_t*>(static_cast<const uint8_t*>(weights_host) +
+                                                                   (reinterpret_cast<const uint8_t*>(w.w_in_t) - m->blob));
+        for (int k = 0; k < kDim; ++k)
+            for (int n = 0; n < n_in; ++n) w1_host[static_cast<size_t>(n) * kDim + k] = src_in[static_cast<size_t>(k) * n_in + n];
+        __half* dst_in = m->w_in_nk + w_in_used;
+        w_in_used += static_cast<size_t>(n_in) * kDim;
+        if (e == cudaSuccess) e = cudaMemcpy(dst_in, w1_host.data(), static_cast<size_t>(n_in) * kDim * 2, cudaMemcpyHostToDevice);
+        w.w_in_nk = dst_in;
         return w;
     };
     for (int l = 0; l < n_layers; ++l) {
@@ -601,6 +625,7 @@ void lg_matcher_destroy(lg_matcher* m) {
     }
     if (m->blob) (void)cudaFree(m->blob);
     if (m->w1_nk) (void)cudaFree(m->w1_nk);
+    if (m->w_in_nk) (void)cudaFree(m->w_in_nk);
     if (m->lt) cublasLtDestroy(m->lt);
     delete m;
 }

@@ -113,6 +113,7 @@ class _Block:
     beta: torch.Tensor
     w2_t: torch.Tensor      # [512, 256]
     w1_nk: torch.Tensor = None   # [512 out, 512 in]: w1_t the other way round (nn.Linear layout), the fused ffn kernel's B operand
+    w_in_nk: torch.Tensor = None # [768 | 512 out, 256 in]: w_in_t the other way round, the fused projection kernel's B operand
 
 
 class MatcherWeights:
@@ -153,7 +154,7 @@ class MatcherWeights:
                 b_inf = b_in + w_in @ c
                 pair.append(_Block(h(w_in), vec(b_inf), h(w1f), vec(b1f), vec(f64[p + "ffn.1.weight"], torch.float32),
                                    vec(f64[p + "ffn.1.bias"], torch.float32), h(f64[p + "ffn.3.weight"]),
-                                   w1f.contiguous().to(dev, torch.float16)))
+                                   w1f.contiguous().to(dev, torch.float16), w_in.contiguous().to(dev, torch.float16)))
                 c = c + f64[p + "ffn.3.bias"]
             self.blocks.append(tuple(pair))
         p = f"log_assignment.{n_layers - 1}."
@@ -298,6 +299,27 @@ def rotary_(packed: torch.Tensor, n_blocks: int, cs: torch.Tensor) -> torch.Tens
     return packed
 
 
+def proj_rotary(x: torch.Tensor, w_nk: torch.Tensor, bias: torch.Tensor, n_rot_blocks: int, cs: torch.Tensor | None,
+                out: torch.Tensor) -> torch.Tensor:
+    """``out = x @ w_nk^T + bias`` with the first ``n_rot_blocks`` 256-column blocks rotated (``lg_match_proj_rotary``): x [rows, 256]
+    FP16, w_nk [256 T, 256] FP16 contiguous (``nn.Linear.weight`` layout, T <= 3), bias FP16 [256 T], cs [rows, 32, 2] FP32 from
+    ``posenc_table``, out [rows, 256 T] FP16.  Reference: lightglue_pytorch_with_plugin/lightglue.py:139-147, 190-193."""
+    for t in (x, w_nk, bias, out) + ((cs,) if cs is not None else ()):
+        if not t.is_cuda:
+            raise RuntimeError("lg_match_proj_rotary: tensors must live on the CUDA device (no CPU path)")
+    n_blocks = w_nk.shape[0] // DIM
+    if (x.dtype != torch.float16 or out.dtype != torch.float16 or w_nk.dtype != torch.float16 or bias.dtype != torch.float16
+            or x.dim() != 2 or x.shape[1] != DIM or x.stride(1) != 1 or w_nk.shape != (n_blocks * DIM, DIM) or not w_nk.is_contiguous()
+            or bias.numel() != n_blocks * DIM or out.shape != (x.shape[0], n_blocks * DIM) or out.stride(1) != 1):
+        raise ValueError("lg_match_proj_rotary: expected FP16 x [rows, 256], w [256 T, 256] contiguous, bias [256 T], out [rows, 256 T]")
+    if n_rot_blocks and (cs is None or cs.dtype != torch.float32 or cs.numel() != x.shape[0] * 64 or not cs.is_contiguous()):
+        raise ValueError("lg_match_proj_rotary: cs must be the contiguous FP32 [rows, 32, 2] table of posenc_table")
+    B.check(B.load().lg_match_proj_rotary(x.data_ptr(), x.shape[0], x.stride(0), w_nk.data_ptr(), bias.data_ptr(), n_blocks,
+                                          n_rot_blocks, cs.data_ptr() if cs is not None else None, out.data_ptr(), out.stride(0),
+                                          _stream(x)), "lg_match_proj_rotary")
+    return out
+
+
 def ffn1_ln_gelu(x: torch.Tensor, w_nk: torch.Tensor, bias: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor,
                  out: torch.Tensor, eps: float = 1e-5) -> torch.Tensor:
     """``out = GELU(LayerNorm(x @ w_nk^T + bias) * gamma + beta)`` as ONE launch (``lg_match_ffn1_ln_gelu``): x [rows, 512] FP16
@@ -427,6 +449,8 @@ class PairMatcher:
         self.use_graph = use_graph
         # LG_MATCH_FUSED_FFN=0: ffn[0..2] as library GEMM + lg_match_layernorm_gelu (round 2's path; kept for A/B runs)
         self.fused_ffn = os.environ.get("LG_MATCH_FUSED_FFN", "1") != "0"
+        # LG_MATCH_FUSED_PROJ=0: input projections as library GEMM (+ lg_match_rotary) instead of lg_match_proj_rotary
+        self.fused_proj = os.environ.get("LG_MATCH_FUSED_PROJ", "1") != "0"
         sd = state_dict if state_dict is not None else reference_init_state_dict(seed, n_layers)
         self.w = MatcherWeights(sd, n_layers, self.device)
         # shape plans, least recently used first.  The reference engine is dynamic (1..2048 keypoints per image, different for
@@ -443,9 +467,13 @@ class PairMatcher:
         launches += 1
         for self_blk, cross_blk in w.blocks:
             # ---- self attention on both images (lightglue.py:137-151)
-            torch.addmm(self_blk.b_in, x, self_blk.w_in_t, out=p.proj)
-            rotary_(p.proj, 2, p.cs)
-            launches += 2
+            if p.fused_proj_self:   # Wqkv with the rotary of q, k in the GEMM epilogue: one launch, no second pass over q | k
+                proj_rotary(x, self_blk.w_in_nk, self_blk.b_in, 2, p.cs, p.proj)
+                launches += 1
+            else:
+                torch.addmm(self_blk.b_in, x, self_blk.w_in_t, out=p.proj)
+                rotary_(p.proj, 2, p.cs)
+                launches += 2
             if p.n0 == p.n1:   # both images are one uniform [2B, N, .] batch: a single launch
                 pj = p.stacked(p.proj)
                 attention_strided(_heads_view(pj, 0), _heads_view(pj, DIM), _heads_view(pj, 2 * DIM),
@@ -460,7 +488,10 @@ class PairMatcher:
             launches += self._ffn(p, self_blk)
             # ---- cross attention, both directions (lightglue.py:188-206)
             pc = p.proj.view(-1)[: p.rows * 2 * DIM].view(p.rows, 2 * DIM)
-            torch.addmm(cross_blk.b_in, x, cross_blk.w_in_t, out=pc)
+            if p.fused_proj_cross:
+                proj_rotary(x, cross_blk.w_in_nk, cross_blk.b_in, 0, None, pc)
+            else:
+                torch.addmm(cross_blk.b_in, x, cross_blk.w_in_t, out=pc)
             launches += 1
             if p.n0 == p.n1:   # batch entry b attends to entry (b + B) mod 2B: both directions in one launch
                 st = p.stacked(pc)
@@ -511,6 +542,8 @@ class PairMatcher:
                 B.check(B.load().lg_attn_hd64_init_device(self.device.index or 0), "lg_attn_hd64_init_device")
                 B.check(B.load().lg_match_ffn_init_device(self.device.index or 0), "lg_match_ffn_init_device")
                 p.prefer_fused_ffn = bool(B.load().lg_match_ffn1_prefer_fused(p.rows))   # few rows: library GEMM + LayerNorm/GELU kernel
+                p.fused_proj_self = self.fused_proj and bool(B.load().lg_match_proj_prefer_fused(p.rows, 3, 2))
+                p.fused_proj_cross = self.fused_proj and bool(B.load().lg_match_proj_prefer_fused(p.rows, 2, 0))
                 if self.use_graph:
                     # warm up on a side stream (cuBLAS handles / workspaces), then capture once
                     p.kpts.zero_()

@@ -69,6 +69,35 @@ def test_layernorm_gelu_kernel(pkg, rows, ld):
     assert torch.equal(got[:, 512:], h[:, 512:])
 
 
+@pytest.mark.parametrize("rows,n_blocks,n_rot,ldx,ldo", [(1, 3, 2, 256, 768), (77, 3, 2, 512, 768), (1031, 2, 0, 256, 512), (2048, 3, 2, 512, 768),
+                                                         (20000, 3, 2, 512, 1024), (20001, 2, 0, 512, 768), (9000, 1, 1, 256, 256)])
+def test_fused_projection_rotary_kernel(pkg, rows, n_blocks, n_rot, ldx, ldo):
+    """Wqkv / to_qk|to_v projection with the rotary in the GEMM epilogue (lightglue.py:139-147, 190-193) against an FP64 restatement
+    (x @ W^T + b, then oracle rotary on the first n_rot blocks): ragged last tile, several items per persistent CTA, strided rows
+    with a sentinel in the gaps and past the last row."""
+    g = torch.Generator().manual_seed(rows + n_blocks)
+    n = 256 * n_blocks
+    x = torch.randn(rows, ldx, generator=g).half()
+    w = (torch.randn(n, 256, generator=g) / 16 * 1.5).half()
+    bias = (torch.randn(n, generator=g) * 0.5).half()
+    kpts = torch.rand(1, rows, 2, generator=g) * 2 - 1
+    wr = torch.randn(32, 2, generator=g)
+    cs = pkg.matcher.posenc_table(kpts[0].to(DEV), wr.to(DEV))
+    guard = 3
+    out = torch.full((rows + guard, ldo), -7.0).half()
+    od = out.clone().to(DEV)
+    pkg.matcher.proj_rotary(x.to(DEV)[:, :256], w.to(DEV), bias.to(DEV), n_rot, cs if n_rot else None, od[:rows, :n])
+    got = od.cpu()
+    want = x[:, :256].double() @ w.double().t() + bias.double()
+    enc = mo.posenc(kpts.double(), wr.double())
+    for blk in range(n_rot):
+        t = want[:, blk * 256:(blk + 1) * 256].unflatten(-1, (4, 64)).transpose(0, 1)[None]
+        want[:, blk * 256:(blk + 1) * 256] = mo.rotary(t, enc)[0].transpose(0, 1).flatten(-2)
+    err = (got[:rows, :n].double() - want).abs()
+    assert bool((err <= 6e-4 * want.abs() + 3e-4).all()), float(err.max())   # FP16 rounding of the result (2^-11 relative) + cos / sin in FP32
+    assert torch.equal(got[rows:], out[rows:]) and torch.equal(got[:, n:], out[:, n:])   # nothing written outside [rows, n]
+
+
 @pytest.mark.parametrize("rows,ldx,ldh", [(1, 512, 512), (77, 512, 512), (128, 512, 512), (1031, 512, 640), (4736, 512, 512), (4737, 768, 512), (20000, 512, 512), (40000, 768, 512)])
 def test_fused_ffn1_ln_gelu_kernel(pkg, rows, ldx, ldh):
     """ffn[0..2] (Linear 512->512, LayerNorm, erf GELU; lightglue.py:131-136) as one tcgen05 kernel against an FP64 restatement:
@@ -210,6 +239,28 @@ def test_fused_and_unfused_ffn_paths_agree(pkg, monkeypatch):
     assert float((rc["scores"] - sa).abs().max()) <= 0.03
     assert float((rc["matches0"] == ma).float().mean()) >= 0.98
     # and against the FP32 CPU oracle, first pair
+    want = mo.forward(sd, *feats[0], n_layers=n_layers, threshold=0.0)
+    assert float((sa[0].cpu() - want["scores"][0]).abs().max()) <= TOL_SCORES_MAX
+
+
+def test_fused_and_unfused_projection_paths_agree(pkg, monkeypatch):
+    """The same forward with the input projections through lg_match_proj_rotary (rotary in the GEMM epilogue) and through library
+    GEMM + lg_match_rotary (LG_MATCH_FUSED_PROJ=0): scores agree to FP16-path noise, and both agree with the FP32 CPU oracle."""
+    n_layers, b, n0, n1 = 3, 7, 1100, 1000   # 14 700 rows: 115 row tiles (fused by the heuristic), ragged, both cross directions as separate launches
+    sd = pkg.reference_init_state_dict(6, n_layers)
+    feats = [mo.synth_pair(400 + i, n0, n1) for i in range(b)]
+    f = [torch.cat([x[j] for x in feats]).to(DEV) for j in range(4)]
+    a = pkg.PairMatcher(sd, n_layers=n_layers, threshold=0.0, device=DEV)
+    ra = a.match(*f, want_scores=True)
+    assert a.plan(b, n0, n1, True).fused_proj_self and a.plan(b, n0, n1, True).fused_proj_cross
+    sa, ma, la = ra["scores"].clone(), ra["matches0"].clone(), ra["launches"]
+    monkeypatch.setenv("LG_MATCH_FUSED_PROJ", "0")
+    c = pkg.PairMatcher(sd, n_layers=n_layers, threshold=0.0, device=DEV)
+    rc = c.match(*f, want_scores=True)
+    assert not c.plan(b, n0, n1, True).fused_proj_self
+    assert rc["launches"] == la + n_layers
+    assert float((rc["scores"] - sa).abs().max()) <= 0.03
+    assert float((rc["matches0"] == ma).float().mean()) >= 0.98
     want = mo.forward(sd, *feats[0], n_layers=n_layers, threshold=0.0)
     assert float((sa[0].cpu() - want["scores"][0]).abs().max()) <= TOL_SCORES_MAX
 
@@ -400,7 +451,8 @@ def test_native_engine_host_buffers_batches_and_replanning(pkg):
         launches = eng.plan(b, n0, n1)
         # per layer: 2 x (in-proj, [rotary,] attention x 1 or 2, ffn-up (fused: 1 launch, else GEMM + LayerNorm/GELU), ffn-down)
         fused = pkg.load().lg_match_ffn1_prefer_fused(b * (n0 + n1))
-        assert launches == (1 + n_layers * ((13 if n0 != n1 else 11) - (2 if fused else 0)) + 9)
+        fused_proj = pkg.load().lg_match_proj_prefer_fused(b * (n0 + n1), 3, 2)   # Wqkv + rotary as one launch
+        assert launches == (1 + n_layers * ((13 if n0 != n1 else 11) - (2 if fused else 0) - (1 if fused_proj else 0)) + 9)
         host = eng.match_host(k0.numpy(), k1.numpy(), d0.half().numpy(), d1.half().numpy())
         dev = eng.match(k0.to(DEV), k1.to(DEV), d0.half().to(DEV), d1.half().to(DEV))
         torch.cuda.synchronize()
