@@ -217,9 +217,10 @@ PAIR_KPTS = (1024, 2048, 4096)     # configs[3] (1x1024x1024 engine shape) and c
 
 
 def pairs_sub_batch(kpts: int) -> int:
-    """Pairs per forward: keeps the packed activations of one forward around the L2 size
-    (measured sweep, tools/pairs_sweep.py: 64 / 32 / 8 pairs at 1024 / 2048 / 4096 keypoints)."""
-    return max(1, min(PAIRS_PER_GPU, 65536 // kpts if kpts <= 2048 else 32768 // kpts))
+    """Pairs per forward (measured sweep, tools/pairs_sweep.py, with the fused ffn / projection kernels: 64 / 32 / 16 pairs at
+    1024 / 2048 / 4096 keypoints — 131 072 keypoint rows per forward; larger forwards fall out of L2, smaller ones leave the
+    persistent kernels a partial last wave)."""
+    return max(1, min(PAIRS_PER_GPU, 65536 // kpts))
 
 
 def synth_features_host(torch, pairs: int, kpts: int, seed: int):
