@@ -55,6 +55,7 @@ MATCH_ABI_SYMBOLS = (
     "lg_match_ffn1_ln_gelu",
     "lg_match_ffn_init_device",
     "lg_match_ffn1_prefer_fused",
+    "lg_match_debug_set_ffn_pair",
     "lg_match_proj_rotary",
     "lg_match_proj_prefer_fused",
     "lg_match_assign_workspace_bytes",
@@ -178,6 +179,8 @@ def load() -> ctypes.CDLL:
     lib.lg_match_ffn_init_device.argtypes = [I]
     lib.lg_match_ffn1_prefer_fused.restype = I
     lib.lg_match_ffn1_prefer_fused.argtypes = [LL]
+    lib.lg_match_debug_set_ffn_pair.restype = I
+    lib.lg_match_debug_set_ffn_pair.argtypes = [I]
     lib.lg_match_proj_rotary.restype = I
     lib.lg_match_proj_rotary.argtypes = [P, LL, I, P, P, I, I, P, P, I, P]
     lib.lg_match_proj_prefer_fused.restype = I

@@ -47,6 +47,15 @@
 #define LG_FFN_WHATIF 0
 #endif
 
+// -DLG_FFN_TRACE (tuning builds): CTA 0 prints clock64 stamps of its first tiles — epilogue warp 0: accumulator full seen, drained
+// (TMEM handed back), statistics agreed, tile stored; MMA warp: accumulator free seen, last MMA of the tile issued.
+#ifdef LG_FFN_TRACE
+#include <cstdio>
+#define FFN_TRACE(arr, idx, slot) do { if (blockIdx.x == 0 && lane == 0 && (idx) < 8) arr[(idx) * 4 + (slot)] = clock64(); } while (0)
+#else
+#define FFN_TRACE(arr, idx, slot)
+#endif
+
 namespace lgffn {
 
 using namespace lgattn::ptx;
@@ -72,7 +81,8 @@ constexpr uint32_t kStageTile = kRound * 32 * 2;                            // 3
 constexpr uint32_t kSmemParams = kSmemStage + kEpiWarps * kStageTile;       // bias | gamma | beta, 512 floats each
 constexpr uint32_t kSmemStats = kSmemParams + 3 * kN * 4;                   // [tile parity][column group][row] (mean, M2)
 constexpr uint32_t kSmemBar = kSmemStats + 2 * 4 * kBM * 8;
-enum : uint32_t { kBarFull = 0, kBarEmpty = kStages, kBarAccFull = 2 * kStages, kBarAccEmpty, kNumBars };
+constexpr int kMaxStages = 3;      // the CTA-pair variant has stages of 48 KiB: three fit where the one-CTA variant has two of 80 KiB
+enum : uint32_t { kBarFull = 0, kBarEmpty = kMaxStages, kBarAccFull = 2 * kMaxStages, kBarAccEmpty, kNumBars };
 constexpr uint32_t kSmemTmemSlot = kSmemBar + 8 * kNumBars;
 constexpr uint32_t kSmemUsed = kSmemTmemSlot + 16;
 constexpr uint32_t kSmemBytes = kSmemUsed + 1024;   // + slack for the 1024-byte alignment of the swizzled tiles
@@ -86,10 +96,25 @@ __device__ __forceinline__ float2 unpack_half2(uint32_t v) {
     return __half22float2(*reinterpret_cast<const __half2*>(&v));
 }
 
+// kPair: CTA pairs (clusters of 2, cta_group::2).  A pair works on 256 rows at a time: rank r holds rows 128 r .. of A, its own
+// accumulator lanes and HALF of every W1' tile (rows 256 h + 128 r .. of column half h), the leader (rank 0) issues
+// tcgen05.mma of M = 256.  Shared-memory traffic per SM drops from 96 B/clk of operand reads + 80 of TMA writes (above the
+// 128 B/clk the memory delivers: the one-CTA main loop runs at ~1 000 TFLOP/s) to 64 + 47.  `tiles` counts 128-row tiles; a pair
+// walks super-tiles blockIdx.x / 2 + i * gridDim.x / 2, rank r takes tile 2 * super-tile + r (rows past the end: TMA zero fill in,
+// clipped out).
+template <bool kPair>
 __global__ void __launch_bounds__(kThreads, 1)
 ffn1_ln_gelu_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w,
                     const __grid_constant__ CUtensorMap tm_h, const __half* __restrict__ bias, const float* __restrict__ gamma,
                     const float* __restrict__ beta, float eps, int tiles) {
+    // pair layout of a ring stage: A (16 KiB) | W1' rows of column half 0 (128 x 64: 16 KiB) | of column half 1 (16 KiB)
+    constexpr uint32_t kBQuarterBytes = 128 * kBK * 2;
+    constexpr uint32_t kStageStride = kPair ? kABytes + 2 * kBQuarterBytes : kStageBytes;   // 48 | 80 KiB
+    constexpr int kNumStages = kPair ? 3 : kStages;   // ring depth (both fit the 160 KiB ring region)
+    static_assert(kNumStages <= kMaxStages && kNumStages * kStageStride <= kStages * kStageBytes, "ring region");
+    constexpr uint32_t kStageTx = kPair ? 2 * (kABytes + 2 * kBQuarterBytes) : kStageBytes;   // bytes landing per stage (pair: both CTAs')
+    const uint32_t rank = kPair ? cluster_ctarank() : 0u;
+    const bool leader = rank == 0;
     extern __shared__ uint8_t smem_raw[];
     uint32_t smem = (smem_u32(smem_raw) + 1023u) & ~1023u;
     asm volatile("mov.u32 %0, %0;" : "+r"(smem));   // pin (see attn_sm100_kernel_mq.cuh)
@@ -105,17 +130,22 @@ ffn1_ln_gelu_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_const
         prefetch_tmap(&tm_w);
         prefetch_tmap(&tm_h);
 #pragma unroll
-        for (int s = 0; s < kStages; ++s) {
+        for (int s = 0; s < kNumStages; ++s) {
             mbar_init(bar(kBarFull + s), 1);
             mbar_init(bar(kBarEmpty + s), 1);
         }
         mbar_init(bar(kBarAccFull), 1);
-        mbar_init(bar(kBarAccEmpty), kEpiWarps);
+        mbar_init(bar(kBarAccEmpty), kPair ? 2 * kEpiWarps : kEpiWarps);   // pair: the leader's barrier collects both CTAs' epilogue warps
         fence_mbar_init();
     }
     if (warp == kWarpMMA) {
-        tmem_alloc<512>(smem + kSmemTmemSlot);
-        tmem_relinquish();
+        if constexpr (kPair) {
+            tmem_alloc_pair<512>(smem + kSmemTmemSlot);
+            tmem_relinquish_pair();
+        } else {
+            tmem_alloc<512>(smem + kSmemTmemSlot);
+            tmem_relinquish();
+        }
     }
     // bias (FP16 -> FP32), gamma, beta into shared memory: read as broadcast 16-byte loads by every epilogue thread
     if (threadIdx.x < kN) {
@@ -125,11 +155,18 @@ ffn1_ln_gelu_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_const
     }
     tc_fence_before();
     __syncthreads();
+    if constexpr (kPair) {   // the peer's barriers must exist before anything (TMA bytes, commits, arrivals) is aimed at them
+        cluster_arrive();
+        cluster_wait();
+    }
     tc_fence_after();
     uint32_t tmem_base;
     asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(smem + kSmemTmemSlot));
 
-    const int first = blockIdx.x, stride = gridDim.x;
+    // one-CTA variant: tile index; pair variant: super-tile index (256 rows), this CTA's tile is 2 * index + rank
+    const int first = kPair ? blockIdx.x / 2 : blockIdx.x, stride = kPair ? gridDim.x / 2 : gridDim.x;
+    const int work = kPair ? (tiles + 1) / 2 : tiles;
+    auto tile_of = [&](int w) { return kPair ? 2 * w + static_cast<int>(rank) : w; };
 
     if (warp >= kEpiWarps) {
         setmaxnreg_dec<kRegsService>();
@@ -141,55 +178,84 @@ ffn1_ln_gelu_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_const
         if (warp == kWarpTMA) {
             // ===================================================================== operand producer
             int g = 0;
-            for (int tile = first; tile < tiles; tile += stride) {
+            for (int w = first; w < work; w += stride) {
+                const int tile = tile_of(w);
 #pragma unroll 1
                 for (int k = 0; k < kKSteps; ++k, ++g) {
-                    const int s = g % kStages;
-                    if (g >= kStages) mbar_wait_backoff(ubar(kBarEmpty + s), ((g / kStages) - 1) & 1, 64);
+                    const int s = g % kNumStages;
+                    if (g >= kNumStages) mbar_wait_backoff(ubar(kBarEmpty + s), ((g / kNumStages) - 1) & 1, 64);
                     if (elect_one()) {
-                        const uint32_t dst = smem_u + kSmemRing + s * kStageBytes;
-                        const bool load_b = LG_FFN_WHATIF != 3 || g < kKSteps;
-                        mbar_arrive_expect_tx(ubar(kBarFull + s), load_b ? kStageBytes : kABytes);
-                        tma_load_4d(dst, &tm_x, ubar(kBarFull + s), k * kBK, tile * kBM, 0, 0);
-                        if (load_b) {
-                            tma_load_4d(dst + kABytes, &tm_w, ubar(kBarFull + s), k * kBK, 0, 0, 0);
-                            tma_load_4d(dst + kABytes + kBHalfBytes, &tm_w, ubar(kBarFull + s), k * kBK, 256, 0, 0);
+                        const uint32_t dst = smem_u + kSmemRing + s * kStageStride;
+                        if constexpr (kPair) {
+                            // both CTAs' bytes complete on the leader's barrier; only the leader announces them
+                            if (leader) mbar_arrive_expect_tx(ubar(kBarFull + s), kStageTx);
+                            tma_load_4d_pair(dst, &tm_x, ubar(kBarFull + s), k * kBK, tile * kBM, 0, 0);
+                            tma_load_4d_pair(dst + kABytes, &tm_w, ubar(kBarFull + s), k * kBK, 128 * static_cast<int>(rank), 0, 0);
+                            tma_load_4d_pair(dst + kABytes + kBQuarterBytes, &tm_w, ubar(kBarFull + s), k * kBK, 256 + 128 * static_cast<int>(rank), 0, 0);
+                        } else {
+                            const bool load_b = LG_FFN_WHATIF != 3 || g < kKSteps;
+                            mbar_arrive_expect_tx(ubar(kBarFull + s), load_b ? kStageBytes : kABytes);
+                            tma_load_4d(dst, &tm_x, ubar(kBarFull + s), k * kBK, tile * kBM, 0, 0);
+                            if (load_b) {
+                                tma_load_4d(dst + kABytes, &tm_w, ubar(kBarFull + s), k * kBK, 0, 0, 0);
+                                tma_load_4d(dst + kABytes + kBHalfBytes, &tm_w, ubar(kBarFull + s), k * kBK, 256, 0, 0);
+                            }
                         }
                     }
                     __syncwarp();
                 }
             }
-        } else if (warp == kWarpMMA) {
-            // ===================================================================== MMA issuer
-            constexpr uint32_t idesc = make_idesc_f16_f32acc(kBM, 256, false);
+        } else if (warp == kWarpMMA && leader) {
+            // ===================================================================== MMA issuer (pair variant: the leader CTA only)
+            constexpr uint32_t idesc = make_idesc_f16_f32acc(kPair ? 2 * kBM : kBM, 256, false);
             int g = 0, it = 0;
-            for (int tile = first; tile < tiles; tile += stride, ++it) {
-                if (it > 0) mbar_wait(ubar(kBarAccEmpty), (it - 1) & 1);   // the epilogue warps have drained the accumulator
+#ifdef LG_FFN_TRACE
+            long long tm[32] = {};
+#endif
+            for (int w = first; w < work; w += stride, ++it) {
+                if (it > 0) {   // the epilogue warps (of both CTAs) have drained the accumulator
+                    if constexpr (kPair) mbar_wait_acquire_cluster(ubar(kBarAccEmpty), (it - 1) & 1);
+                    else mbar_wait(ubar(kBarAccEmpty), (it - 1) & 1);
+                }
+                FFN_TRACE(tm, it, 0);
                 tc_fence_after();
 #pragma unroll 1
                 for (int k = 0; k < kKSteps; ++k, ++g) {
-                    const int s = g % kStages;
-                    mbar_wait(ubar(kBarFull + s), (g / kStages) & 1);
+                    const int s = g % kNumStages;
+                    mbar_wait(ubar(kBarFull + s), (g / kNumStages) & 1);
                     tc_fence_after();
                     if (elect_one()) {
-                        const uint32_t a = smem_u + kSmemRing + s * kStageBytes;
+                        const uint32_t a = smem_u + kSmemRing + s * kStageStride;
                         const uint64_t desc_a = make_smem_desc_sw128(a, 16, 1024);
                         const uint64_t desc_b0 = make_smem_desc_sw128(a + kABytes, 16, 1024);
-                        const uint64_t desc_b1 = make_smem_desc_sw128(a + kABytes + kBHalfBytes, 16, 1024);
+                        const uint64_t desc_b1 = make_smem_desc_sw128(a + kABytes + (kPair ? kBQuarterBytes : kBHalfBytes), 16, 1024);
 #pragma unroll
                         for (int kk = 0; kk < kBK / 16; ++kk) {
                             const uint32_t acc = (k > 0 || kk > 0) ? 1u : 0u;
-                            if (LG_FFN_WHATIF != 2) {
+                            if constexpr (kPair) {
+                                mma_f16_ss_pair(tmem_u, desc_a + 2u * kk, desc_b0 + 2u * kk, idesc, acc);
+                                mma_f16_ss_pair(tmem_u + 256u, desc_a + 2u * kk, desc_b1 + 2u * kk, idesc, acc);
+                            } else if (LG_FFN_WHATIF != 2) {
                                 mma_f16_ss(tmem_u, desc_a + 2u * kk, desc_b0 + 2u * kk, idesc, acc);
                                 mma_f16_ss(tmem_u + 256u, desc_a + 2u * kk, desc_b1 + 2u * kk, idesc, acc);
                             }
                         }
-                        mma_commit(ubar(kBarEmpty + s));
-                        if (k == kKSteps - 1) mma_commit(ubar(kBarAccFull));
+                        if constexpr (kPair) {
+                            mma_commit_pair(ubar(kBarEmpty + s), 3);   // both producers may refill this stage
+                            if (k == kKSteps - 1) mma_commit_pair(ubar(kBarAccFull), 3);
+                        } else {
+                            mma_commit(ubar(kBarEmpty + s));
+                            if (k == kKSteps - 1) mma_commit(ubar(kBarAccFull));
+                        }
                     }
                     __syncwarp();
                 }
+                FFN_TRACE(tm, it, 1);
             }
+#ifdef LG_FFN_TRACE
+            if (blockIdx.x == 0 && lane == 0)
+                for (int i = 1; i < 6; ++i) printf("mma tile %d: acc free seen +%lld, issued +%lld\n", i, tm[4 * i] - tm[4], tm[4 * i + 1] - tm[4]);
+#endif
         }
     } else {
         // ========================================================================= epilogue warps
@@ -204,9 +270,14 @@ ffn1_ln_gelu_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_const
         const uint32_t swz = static_cast<uint32_t>((lane >> 1) & 3);
 
         int it = 0;
-        for (int tile = first; tile < tiles; tile += stride, ++it) {
+#ifdef LG_FFN_TRACE
+        long long te[32] = {};
+#endif
+        for (int w = first; w < work; w += stride, ++it) {
+            const int tile = tile_of(w);
             mbar_wait(bar(kBarAccFull), it & 1);
             tc_fence_after();
+            FFN_TRACE(te, it, 0);
             // ---- drain: accumulator + bias -> FP16 pairs in registers, shifted statistics in FP32
             uint32_t pk[kColsPerWarp / 2];
             float shift = 0.f, s1 = 0.f, s2 = 0.f;
@@ -233,8 +304,12 @@ ffn1_ln_gelu_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_const
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(bar(kBarAccEmpty));   // the next tile's MMAs may overwrite the accumulator now
+            if (lane == 0) {   // the next tile's MMAs may overwrite the accumulator now
+                if (kPair && !leader) mbar_arrive_remote_release(dsmem_addr(bar(kBarAccEmpty), 0));
+                else mbar_arrive(bar(kBarAccEmpty));
+            }
 
+            FFN_TRACE(te, it, 1);
             // ---- row statistics: this thread's 128 columns -> (mean, M2), combined with the row's three other column groups
             constexpr float kInvCols = 1.0f / kColsPerWarp;
             const float dm = s1 * kInvCols;
@@ -250,6 +325,7 @@ ffn1_ln_gelu_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_const
             const float m2 = ((p0.y + p1.y) + (p2.y + p3.y)) + kColsPerWarp * ((e0 * e0 + e1 * e1) + (e2 * e2 + e3 * e3));
             const float rstd = rsqrtf(m2 * (1.0f / kN) + eps);
             const float nmr = -mean * rstd;
+            FFN_TRACE(te, it, 2);
 
             // ---- apply: normalise, affine, GELU, FP16, 32 columns per staging round, one TMA store per round
 #pragma unroll
@@ -268,7 +344,8 @@ ffn1_ln_gelu_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_const
                     o[i / 2] = pack_half2(y0, y1);
                     o[i / 2 + 1] = pack_half2(y2, y3);
                 }
-                // the previous round's TMA store must have read the staging tile
+                // the previous round's TMA store must have read the staging tile.  (Coalesced global stores read back from the
+                // staging tile instead — no asynchronous read to wait for — were measured slower: 176 vs 161 us at 262 144 rows.)
                 if (elect_one()) bulk_wait_group_read0();
                 __syncwarp();
 #pragma unroll
@@ -282,7 +359,14 @@ ffn1_ln_gelu_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_const
                 }
                 __syncwarp();
             }
+            FFN_TRACE(te, it, 3);
         }
+#ifdef LG_FFN_TRACE
+        if (blockIdx.x == 0 && warp == 0 && lane == 0)
+            for (int i = 1; i < 6; ++i)
+                printf("epi tile %d: acc full seen +%lld, drained +%lld, stats +%lld, stored +%lld\n", i, te[4 * i] - te[4], te[4 * i + 1] - te[4],
+                       te[4 * i + 2] - te[4], te[4 * i + 3] - te[4]);
+#endif
         // the staging tiles must outlive the stores that read them
         if (elect_one()) bulk_wait_group_read0();
         __syncwarp();
@@ -290,9 +374,14 @@ ffn1_ln_gelu_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_const
 
     tc_fence_before();
     __syncthreads();
+    if constexpr (kPair) {   // neither CTA may leave (or free TMEM) while the other can still signal its barriers / use its operands
+        cluster_arrive();
+        cluster_wait();
+    }
     if (warp == kWarpMMA) {
         tc_fence_after();
-        tmem_dealloc<512>(tmem_base);
+        if constexpr (kPair) tmem_dealloc_pair<512>(tmem_base);
+        else tmem_dealloc<512>(tmem_base);
     }
 }
 

@@ -32,6 +32,7 @@ int g_sms[kMaxDevices];
 int g_small_clusters[kMaxDevices];   // co-resident 4-CTA clusters of the few-rows kernel
 std::atomic<int> g_small_enabled{1}; // LG_MATCH_FFN_SMALL=0: no few-rows kernel (A/B runs)
 std::atomic<int> g_pdl{1};           // LG_ATTN_PDL=0: no programmatic dependent launch
+std::atomic<int> g_pair{0};          // LG_MATCH_FFN_PAIR=1 / lg_match_debug_set_ffn_pair: the persistent ffn kernel as CTA pairs (cta_group::2); measured equal, off
 
 int init_locked(int device) {
     cudaDeviceProp prop;
@@ -51,7 +52,9 @@ int init_locked(int device) {
     int prev = 0;
     if ((e = cudaGetDevice(&prev)) != cudaSuccess) return static_cast<int>(e);
     if ((e = cudaSetDevice(device)) != cudaSuccess) return static_cast<int>(e);
-    e = cudaFuncSetAttribute(ffn1_ln_gelu_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemBytes));
+    e = cudaFuncSetAttribute(ffn1_ln_gelu_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemBytes));
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(ffn1_ln_gelu_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemBytes));
     if (e == cudaSuccess)
         e = cudaFuncSetAttribute(small::ffn1_ln_gelu_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  static_cast<int>(small::kSmemBytesS));
@@ -83,6 +86,7 @@ int init_locked(int device) {
     g_sms[device] = prop.multiProcessorCount;
     if (const char* env = getenv("LG_MATCH_FFN_SMALL")) g_small_enabled.store(atoi(env) != 0 ? 1 : 0, std::memory_order_relaxed);
     if (const char* env = getenv("LG_ATTN_PDL")) g_pdl.store(atoi(env) != 0 ? 1 : 0, std::memory_order_relaxed);
+    if (const char* env = getenv("LG_MATCH_FFN_PAIR")) g_pair.store(atoi(env) != 0 ? 1 : 0, std::memory_order_relaxed);
     return 0;
 }
 
@@ -118,6 +122,11 @@ int lg_match_ffn_init_device(int device) {
     const int rc = init_locked(device);
     if (rc == 0) g_ready[device].store(1, std::memory_order_release);
     return rc;
+}
+
+int lg_match_debug_set_ffn_pair(int enabled) {
+    g_pair.store(enabled != 0 ? 1 : 0, std::memory_order_relaxed);
+    return 0;
 }
 
 int lg_match_ffn1_prefer_fused(long long rows) {
@@ -179,8 +188,28 @@ int lg_match_ffn1_ln_gelu(const void* x_half, long long rows, int ldx, const voi
                                beta, eps);
         return static_cast<int>(e);
     }
+    if (g_pair.load(std::memory_order_relaxed)) {
+        // CTA pairs (cta_group::2): W1' tiles of 128 rows per CTA, clusters of 2, a pair per 256-row super-tile
+        if ((rc = encode_matrix(&tm_w, w_nk_half, kN, kK, kK, kBK, 128, CU_TENSOR_MAP_SWIZZLE_128B)) != 0) return rc;
+        const int pairs_max = g_sms[device] / 2, super_tiles = (tiles + 1) / 2;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(2u * static_cast<unsigned>(super_tiles < pairs_max ? super_tiles : pairs_max));
+        cfg.blockDim = dim3(kThreads);
+        cfg.dynamicSmemBytes = kSmemBytes;
+        cfg.stream = static_cast<cudaStream_t>(stream);
+        cudaLaunchAttribute attrs[1];
+        attrs[0].id = cudaLaunchAttributeClusterDimension;
+        attrs[0].val.clusterDim.x = 2;
+        attrs[0].val.clusterDim.y = 1;
+        attrs[0].val.clusterDim.z = 1;
+        cfg.attrs = attrs;
+        cfg.numAttrs = 1;
+        e = cudaLaunchKernelEx(&cfg, ffn1_ln_gelu_kernel<true>, tm_x, tm_w, tm_h, static_cast<const __half*>(bias_half), gamma, beta,
+                               eps, tiles);
+        return static_cast<int>(e);
+    }
     const int grid = tiles < g_sms[device] ? tiles : g_sms[device];
-    ffn1_ln_gelu_kernel<<<grid, kThreads, kSmemBytes, static_cast<cudaStream_t>(stream)>>>(
+    ffn1_ln_gelu_kernel<false><<<grid, kThreads, kSmemBytes, static_cast<cudaStream_t>(stream)>>>(
         tm_x, tm_w, tm_h, static_cast<const __half*>(bias_half), gamma, beta, eps, tiles);
     e = cudaGetLastError();
     return static_cast<int>(e);

@@ -133,6 +133,32 @@ def test_fused_ffn1_ln_gelu_kernel(pkg, rows, ldx, ldh):
     assert torch.equal(got[rows:], out[rows:]) and torch.equal(got[:, 512:], out[:, 512:])   # nothing written outside [rows, 512]
 
 
+@pytest.mark.parametrize("rows", [300, 20000, 40001])
+def test_fused_ffn1_cta_pair_variant_is_bit_equal(pkg, rows):
+    """The persistent ffn-up kernel as CTA pairs (cta_group::2: M = 256 MMAs, half of every W1' tile per CTA, TMA bytes of both
+    CTAs completing on the leader's barrier, multicast commits) computes exactly what the one-CTA variant computes."""
+    g = torch.Generator().manual_seed(rows)
+    x = torch.randn(rows, 512, generator=g).half().to(DEV)
+    w = (torch.randn(512, 512, generator=g) / 512 ** 0.5 * 1.5).half().to(DEV)
+    bias = (torch.randn(512, generator=g) * 0.5).half().to(DEV)
+    gamma, beta = torch.randn(512, generator=g).to(DEV), torch.randn(512, generator=g).to(DEV)
+    lib = pkg.load()
+    # rows <= 4736 would take the few-rows cluster kernel: force the persistent one by going through a strided view?  No — the
+    # launcher picks by tile count only, so 300 rows exercises the few-rows kernel in both settings (must still agree).
+    outs = []
+    try:
+        for pair in (0, 1):
+            lib.lg_match_debug_set_ffn_pair(pair)
+            o = torch.full((rows + 2, 512), -3.0, dtype=torch.float16, device=DEV)
+            pkg.matcher.ffn1_ln_gelu(x, w, bias, gamma, beta, o[:rows])
+            torch.cuda.synchronize()
+            outs.append(o.cpu())
+    finally:
+        lib.lg_match_debug_set_ffn_pair(0)
+    assert torch.equal(outs[0], outs[1])
+    assert bool((outs[1][rows:] == -3.0).all())
+
+
 @pytest.mark.parametrize("b,n0,n1", [(1, 1, 1), (1, 1, 70), (1, 160, 130), (3, 257, 64), (2, 512, 515), (1, 1024, 1024)])
 def test_assignment_kernels_match_oracle(pkg, b, n0, n1):
     g = torch.Generator().manual_seed(n0 * 3 + n1)
