@@ -303,8 +303,13 @@ def pairs_section(pkg, torch, dist, dev, rank: int, world: int, steps: int, with
         ev_in = [torch.cuda.Event() for _ in range(2)]
         ev_used = [torch.cuda.Event() for _ in range(2)]
 
+        # a single-forward step gives the copy stream nothing to overlap with (the whole H2D transfer would sit in front of the
+        # forward): the host-buffer legs split such a step in two
+        half = max(1, PAIRS_PER_GPU // 2)
+        e2e_slices = slices if len(slices) > 1 else [(a, min(PAIRS_PER_GPU, a + half)) for a in range(0, PAIRS_PER_GPU, half)]
+
         def stage(i):
-            a, b = slices[i]
+            a, b = e2e_slices[i]
             slot = i % 2
             with torch.cuda.stream(copy_s):
                 copy_s.wait_event(ev_used[slot])            # the forward that read this slot has consumed it
@@ -316,8 +321,8 @@ def pairs_section(pkg, torch, dist, dev, rank: int, world: int, steps: int, with
         def step_e2e():
             comp = torch.cuda.current_stream(dev)
             stage(0)
-            for i, (a, b) in enumerate(slices):
-                if i + 1 < len(slices):
+            for i, (a, b) in enumerate(e2e_slices):
+                if i + 1 < len(e2e_slices):
                     stage(i + 1)
                 slot = i % 2
                 comp.wait_event(ev_in[slot])
@@ -346,9 +351,7 @@ def pairs_section(pkg, torch, dist, dev, rank: int, world: int, steps: int, with
         # pinned host pointers out, no torch in the call path (inputs of sub-batch i+1 staged under forward i)
         lib = pkg.load()
 
-        # a single-forward step gives the engine nothing to overlap with: split it in two for this leg
-        half = max(1, PAIRS_PER_GPU // 2)
-        native_slices = slices if len(slices) > 1 else [(a, min(PAIRS_PER_GPU, a + half)) for a in range(0, PAIRS_PER_GPU, half)]
+        native_slices = e2e_slices
 
         def step_native():
             for a, b in native_slices:
@@ -376,6 +379,7 @@ def pairs_section(pkg, torch, dist, dev, rank: int, world: int, steps: int, with
                  "ms_per_pair_per_gpu": ms / (PAIRS_PER_GPU * n_steps), "model_tflops_per_gpu": pps / world * fl["total"] / 1e12,
                  "attention_flop_share": fl["attention"] / fl["total"], "gpu_launches_per_forward": plan.launches,
                  "e2e": {"value": world * PAIRS_PER_GPU * n_steps / (ms_e2e * 1e-3), "unit": "pairs/s",
+                         "pairs_per_forward": e2e_slices[0][1] - e2e_slices[0][0],
                          "h2d_bytes_per_step": int(kp_h.numel() * 4 + d_h.numel() * 2),
                          "d2h_bytes_per_step": int(m_h.numel() * 4 + s_h.numel() * 4)},
                  "e2e_native_engine": {"value": world * PAIRS_PER_GPU * n_steps / (ms_native * 1e-3), "unit": "pairs/s",
