@@ -50,6 +50,19 @@ def test_glue_header_symbols_are_exported(pkg, lib):
     assert lib.lg_match_posenc(None, None, None, 4, None) == pkg._binding.EINVAL
     assert lib.lg_match_rotary(None, 4, 768, 2, None, None) == pkg._binding.EINVAL
     assert lib.lg_match_layernorm_gelu(None, 4, 512, None, None, 1e-5, None) == pkg._binding.EINVAL
+    # the hand-written GEMM kernels of the matcher: bad pointers / strides / block counts are refused before any device call
+    assert lib.lg_match_ffn1_ln_gelu(None, 4, 512, None, None, None, None, 1e-5, None, 512, None) == pkg._binding.EINVAL
+    ok = ctypes.c_void_p(4096)
+    assert lib.lg_match_ffn1_ln_gelu(ok, 4, 500, ok, ok, ok, ok, 1e-5, ok, 512, None) == pkg._binding.EINVAL        # ldx < 512
+    assert lib.lg_match_ffn1_ln_gelu(ok, 4, 512, ok, ok, ok, ok, 1e-5, ctypes.c_void_p(4100), 512, None) == pkg._binding.EINVAL  # alignment
+    assert lib.lg_match_proj_rotary(None, 4, 256, None, None, 3, 2, None, None, 768, None) == pkg._binding.EINVAL
+    assert lib.lg_match_proj_rotary(ok, 4, 256, ok, ok, 4, 2, ok, ok, 1024, None) == pkg._binding.EINVAL            # more than 3 blocks
+    assert lib.lg_match_proj_rotary(ok, 4, 256, ok, ok, 3, 2, None, ok, 768, None) == pkg._binding.EINVAL           # rotary without a table
+    assert lib.lg_match_proj_rotary(ok, 4, 256, ok, ok, 3, 0, None, ok, 512, None) == pkg._binding.EINVAL           # ldo < 768
+    # shape rules answer without a device (SM count defaults to a B200's 148): whole-row tiles need enough rows to fill the GPU,
+    # except for the few-rows kernel, which needs an initialised device
+    assert lib.lg_match_ffn1_prefer_fused(262144) == 1 and lib.lg_match_ffn1_prefer_fused(8192) == 0
+    assert lib.lg_match_proj_prefer_fused(262144, 3, 2) == 1 and lib.lg_match_proj_prefer_fused(2048, 3, 2) == 0
     assert lib.lg_match_assign_workspace_bytes(0, 8, 8) == 0
     assert lib.lg_match_assign_workspace_bytes(2, 300, 200) >= 4 * 2 * (3 * 300 + 2 * 200)
     one = ctypes.c_void_p(256)
