@@ -434,6 +434,55 @@ def pairs_section(pkg, torch, dist, dev, rank: int, world: int, steps: int, with
     return out
 
 
+def matcher_kernels_section(pkg, torch, dev, peaks) -> dict:
+    """The matcher's hand-written GEMM kernels next to the launches they replace, at the row count of one bench forward
+    (131 072 keypoint rows), each against the roofline that bounds it: lg_match_ffn1_ln_gelu (tensor: 2 * rows * 512 * 512 FLOP),
+    lg_match_proj_rotary (HBM: rows * (512 + 256 + 2 * 768) bytes)."""
+    M = pkg.matcher
+    rows = 131072
+    g = torch.Generator(device=dev).manual_seed(7)
+    x = torch.randn(rows, 512, device=dev, generator=g).half()
+    w1 = (torch.randn(512, 512, device=dev, generator=g) / 22.6).half()
+    wq = (torch.randn(768, 256, device=dev, generator=g) / 16).half()
+    b1, bq = torch.randn(512, device=dev, generator=g).half(), torch.randn(768, device=dev, generator=g).half()
+    gamma, beta = torch.randn(512, device=dev, generator=g), torch.randn(512, device=dev, generator=g)
+    cs = M.posenc_table(torch.rand(rows, 2, device=dev, generator=g) * 2 - 1, torch.randn(32, 2, device=dev, generator=g))
+    hid, proj = torch.empty(rows, 512, device=dev, dtype=torch.float16), torch.empty(rows, 768, device=dev, dtype=torch.float16)
+    w1_t, wq_t = w1.t().contiguous(), wq.t().contiguous()
+
+    def best_us(fn, iters=10, reps=3):
+        for _ in range(2):
+            fn()
+        torch.cuda.synchronize()
+        best = float("inf")
+        for _ in range(reps):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(iters):
+                fn()
+            e1.record()
+            torch.cuda.synchronize()
+            best = min(best, e0.elapsed_time(e1) / iters * 1e3)
+        return best
+
+    def ffn_old():
+        torch.addmm(b1, x, w1_t, out=hid)
+        M.layernorm_gelu_(hid, gamma, beta)
+
+    def proj_old():
+        torch.addmm(bq, x[:, :256], wq_t, out=proj)
+        M.rotary_(proj, 2, cs)
+
+    t_ffn = best_us(lambda: M.ffn1_ln_gelu(x, w1, b1, gamma, beta, hid))
+    t_proj = best_us(lambda: M.proj_rotary(x[:, :256], wq, bq, 2, cs, proj))
+    fl, by = 2.0 * rows * 512 * 512, rows * (512 + 256 + 2 * 768)
+    return {"rows": rows,
+            "ffn1_ln_gelu": {"us": t_ffn, "replaces_us": best_us(ffn_old), "replaces": "library GEMM + lg_match_layernorm_gelu",
+                             "tflops": fl / t_ffn * 1e-6, "frac_burst": fl / t_ffn * 1e-6 / peaks["bf16_tflops"], "bound": "tensor (epilogue issue-bound, DESIGN.md section 8)"},
+            "proj_rotary": {"us": t_proj, "replaces_us": best_us(proj_old), "replaces": "library GEMM + lg_match_rotary",
+                            "gbs": by / t_proj * 1e-3, "frac_hbm": by / t_proj * 1e-3 / peaks["hbm_gbs"], "bound": "hbm"}}
+
+
 def time_graph_chain(torch, fn, calls: int, iters: int = 20, warm: int = 5) -> float:
     """fn(i, stream_ptr) enqueues problem i; CALLS problems captured as one dependent chain; microseconds per problem."""
     stream = torch.cuda.Stream()
@@ -731,6 +780,8 @@ def run_ours(args) -> None:
     pairs = {}
     if not args.no_pairs:
         pairs = pairs_section(pkg, torch, dist, dev, rank, world, args.steps, with_cpu=(rank == 0 and world == 1))
+        if rank == 0 and not args.no_extra:
+            pairs["matcher_kernels"] = matcher_kernels_section(pkg, torch, dev, peaks)
 
     cpu = None
     if rank == 0 and world == 1:
