@@ -150,8 +150,9 @@ ffn1_ln_gelu_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_const
     // bias (FP16 -> FP32), gamma, beta into shared memory: read as broadcast 16-byte loads by every epilogue thread
     if (threadIdx.x < kN) {
         st_shared_f32(smem + kSmemParams + 4u * threadIdx.x, __half2float(bias[threadIdx.x]));
-        st_shared_f32(smem + kSmemParams + 4u * (kN + threadIdx.x), gamma[threadIdx.x]);
-        st_shared_f32(smem + kSmemParams + 4u * (2 * kN + threadIdx.x), beta[threadIdx.x]);
+        // gamma / 2, beta / 2: the affine step then yields y / 2, which is what gelu_erf_of_half takes
+        st_shared_f32(smem + kSmemParams + 4u * (kN + threadIdx.x), 0.5f * gamma[threadIdx.x]);
+        st_shared_f32(smem + kSmemParams + 4u * (2 * kN + threadIdx.x), 0.5f * beta[threadIdx.x]);
     }
     tc_fence_before();
     __syncthreads();
@@ -336,7 +337,7 @@ ffn1_ln_gelu_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_const
                     const float4 g4 = ld_shared_v4f(p_gamma + 4u * (kRound * c + i));
                     const float4 b4 = ld_shared_v4f(p_beta + 4u * (kRound * c + i));
                     const float2 x01 = unpack_half2(pk[(kRound * c + i) / 2]), x23 = unpack_half2(pk[(kRound * c + i) / 2 + 1]);
-                    auto act = [](float v) { return LG_FFN_WHATIF == 1 ? v : lgmatch::gelu_erf(v); };
+                    auto act = [](float v) { return LG_FFN_WHATIF == 1 ? v : lgmatch::gelu_erf_of_half(v); };
                     const float y0 = act(fmaf(fmaf(x01.x, rstd, nmr), g4.x, b4.x));
                     const float y1 = act(fmaf(fmaf(x01.y, rstd, nmr), g4.y, b4.y));
                     const float y2 = act(fmaf(fmaf(x23.x, rstd, nmr), g4.z, b4.z));
@@ -454,8 +455,8 @@ ffn1_ln_gelu_small_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
     }
     if (threadIdx.x < kNC) {
         st_shared_f32(smem + kSmemParamsS + 4u * threadIdx.x, __half2float(bias[col0 + threadIdx.x]));
-        st_shared_f32(smem + kSmemParamsS + 4u * (kNC + threadIdx.x), gamma[col0 + threadIdx.x]);
-        st_shared_f32(smem + kSmemParamsS + 4u * (2 * kNC + threadIdx.x), beta[col0 + threadIdx.x]);
+        st_shared_f32(smem + kSmemParamsS + 4u * (kNC + threadIdx.x), 0.5f * gamma[col0 + threadIdx.x]);   // halved: see above
+        st_shared_f32(smem + kSmemParamsS + 4u * (2 * kNC + threadIdx.x), 0.5f * beta[col0 + threadIdx.x]);
     }
     tc_fence_before();
     __syncthreads();
@@ -568,10 +569,10 @@ ffn1_ln_gelu_small_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
         for (int i = 0; i < kColsPerWarpS; i += 4) {
             const float4 g4 = ld_shared_v4f(p_gamma + 4u * i);
             const float4 b4 = ld_shared_v4f(p_beta + 4u * i);
-            const float y0 = lgmatch::gelu_erf(fmaf(fmaf(a[i], rstd, nmr), g4.x, b4.x));
-            const float y1 = lgmatch::gelu_erf(fmaf(fmaf(a[i + 1], rstd, nmr), g4.y, b4.y));
-            const float y2 = lgmatch::gelu_erf(fmaf(fmaf(a[i + 2], rstd, nmr), g4.z, b4.z));
-            const float y3 = lgmatch::gelu_erf(fmaf(fmaf(a[i + 3], rstd, nmr), g4.w, b4.w));
+            const float y0 = lgmatch::gelu_erf_of_half(fmaf(fmaf(a[i], rstd, nmr), g4.x, b4.x));
+            const float y1 = lgmatch::gelu_erf_of_half(fmaf(fmaf(a[i + 1], rstd, nmr), g4.y, b4.y));
+            const float y2 = lgmatch::gelu_erf_of_half(fmaf(fmaf(a[i + 2], rstd, nmr), g4.z, b4.z));
+            const float y3 = lgmatch::gelu_erf_of_half(fmaf(fmaf(a[i + 3], rstd, nmr), g4.w, b4.w));
             o[i / 2] = pack_half2(y0, y1);
             o[i / 2 + 1] = pack_half2(y2, y3);
         }

@@ -21,4 +21,19 @@ __device__ __forceinline__ float gelu_erf(float x) {
     return fmaf(fabsf(hx), erf_abs, hx);
 }
 
+// The same function of hx = x / 2 (callers that produce x by an affine step halve its coefficients instead: one multiply less),
+// with the exponent's argument folded into the scale of z (z' = |x| / sqrt 2 * sqrt(log2 e), so exp(-(x / sqrt 2)^2) = 2^(-z'^2):
+// another multiply less): 8 FP32 ops + 2 MUFU.  Used by the fused ffn kernels, whose epilogue is bound by instruction issue.
+__device__ __forceinline__ float gelu_erf_of_half(float hx) {
+    constexpr float kSqrtLog2e = 1.2011224087864498f;
+    const float z = fabsf(hx) * (1.4142135623730951f * kSqrtLog2e);
+    float t, e;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.47047f / kSqrtLog2e, z, 1.0f)));
+    float p = fmaf(0.7478556f, t, -0.0958798f);
+    p = fmaf(p, t, 0.3480242f);
+    p *= t;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-z * z));
+    return fmaf(fabsf(hx), fmaf(-p, e, 1.0f), hx);
+}
+
 }  // namespace lgmatch
