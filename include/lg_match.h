@@ -63,9 +63,10 @@ int lg_match_ffn_init_device(int device);
  * else 0: its tiles are whole rows (128 x 512), so few rows leave most SMs idle (crossover on B200: about two thirds of the SM
  * count in tiles).  The matcher's callers ask this once per shape plan. */
 int lg_match_ffn1_prefer_fused(long long rows);
-/* Tuning / tests: run the persistent variant of lg_match_ffn1_ln_gelu as CTA pairs (clusters of 2, tcgen05.mma cta_group::2 with
- * M = 256, half of every weight tile per CTA).  Same results; measured equal in time on B200 (the kernel is bound by the
- * epilogue's instruction issue, not by the main loop), so it is off by default.  Also LG_MATCH_FFN_PAIR=1 in the environment. */
+/* Tuning / tests: the persistent variant of lg_match_ffn1_ln_gelu also exists as CTA pairs (clusters of 2, tcgen05.mma
+ * cta_group::2 with M = 256, half of every weight tile per CTA, double-buffered output staging).  Same results bit for bit; faster
+ * once a launch is several waves of tiles long, slightly slower below, so the launcher picks by size (>= 3 tiles per SM).
+ * enabled: 1 / 0 force it on / off, -1 = by size (default).  Also LG_MATCH_FFN_PAIR=0/1 in the environment. */
 int lg_match_debug_set_ffn_pair(int enabled);
 
 /* Input projection of a transformer block with the rotary embedding in its epilogue, ONE launch (lightglue.py:139-147: Wqkv +

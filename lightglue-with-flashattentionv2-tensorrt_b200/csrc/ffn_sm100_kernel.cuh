@@ -78,7 +78,9 @@ constexpr uint32_t kStageBytes = kABytes + 2 * kBHalfBytes;
 constexpr uint32_t kSmemRing = 0;
 constexpr uint32_t kSmemStage = kSmemRing + kStages * kStageBytes;          // 16 x 2 KiB output staging
 constexpr uint32_t kStageTile = kRound * 32 * 2;                            // 32 rows x 32 halves
-constexpr uint32_t kSmemParams = kSmemStage + kEpiWarps * kStageTile;       // bias | gamma | beta, 512 floats each
+// the CTA-pair variant's ring is 16 KiB shorter: with 16 KiB more here its staging is double-buffered (2 x 2 KiB per warp starting
+// 16 KiB below kSmemStage), so that a round only waits for the TMA store before last
+constexpr uint32_t kSmemParams = kSmemStage + kEpiWarps * kStageTile + 16384;   // bias | gamma | beta, 512 floats each
 constexpr uint32_t kSmemStats = kSmemParams + 3 * kN * 4;                   // [tile parity][column group][row] (mean, M2)
 constexpr uint32_t kSmemBar = kSmemStats + 2 * 4 * kBM * 8;
 constexpr int kMaxStages = 3;      // the CTA-pair variant has stages of 48 KiB: three fit where the one-CTA variant has two of 80 KiB
@@ -266,9 +268,11 @@ ffn1_ln_gelu_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_const
         const uint32_t t_acc = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + static_cast<uint32_t>(cg * kColsPerWarp);
         const uint32_t p_bias = smem + kSmemParams + 4u * (cg * kColsPerWarp);
         const uint32_t p_gamma = p_bias + 4u * kN, p_beta = p_bias + 8u * kN;
-        const uint32_t stg = smem + kSmemStage + static_cast<uint32_t>(warp) * kStageTile;
-        const uint32_t stg_row = stg + static_cast<uint32_t>(lane) * 64u;
+        // one-CTA variant: one 2 KiB staging tile per warp; pair variant: two (the ring's unused 16 KiB + the extra 16 KiB)
+        constexpr uint32_t kStgBufs = kPair ? 2 : 1;
+        const uint32_t stg0 = smem + kSmemStage - (kPair ? 16384u : 0u) + static_cast<uint32_t>(warp) * kStageTile * kStgBufs;
         const uint32_t swz = static_cast<uint32_t>((lane >> 1) & 3);
+        uint32_t round = 0;
 
         int it = 0;
 #ifdef LG_FFN_TRACE
@@ -347,8 +351,11 @@ ffn1_ln_gelu_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_const
                 }
                 // the previous round's TMA store must have read the staging tile.  (Coalesced global stores read back from the
                 // staging tile instead — no asynchronous read to wait for — were measured slower: 176 vs 161 us at 262 144 rows.)
-                if (elect_one()) bulk_wait_group_read0();
+                if (elect_one()) bulk_wait_group_read<kStgBufs - 1>();
                 __syncwarp();
+                const uint32_t stg = stg0 + (kPair ? (round & 1u) * kStageTile : 0u);
+                const uint32_t stg_row = stg + static_cast<uint32_t>(lane) * 64u;
+                ++round;
 #pragma unroll
                 for (int j = 0; j < 4; ++j)
                     st_shared_v4(stg_row + ((static_cast<uint32_t>(j) ^ swz) << 4), o[4 * j], o[4 * j + 1], o[4 * j + 2], o[4 * j + 3]);

@@ -32,7 +32,8 @@ int g_sms[kMaxDevices];
 int g_small_clusters[kMaxDevices];   // co-resident 4-CTA clusters of the few-rows kernel
 std::atomic<int> g_small_enabled{1}; // LG_MATCH_FFN_SMALL=0: no few-rows kernel (A/B runs)
 std::atomic<int> g_pdl{1};           // LG_ATTN_PDL=0: no programmatic dependent launch
-std::atomic<int> g_pair{0};          // LG_MATCH_FFN_PAIR=1 / lg_match_debug_set_ffn_pair: the persistent ffn kernel as CTA pairs (cta_group::2); measured equal, off
+std::atomic<int> g_pair{-1};         // persistent ffn kernel as CTA pairs (cta_group::2): -1 = by size (>= 3 waves of tiles), 0 / 1 = forced
+                                     // (LG_MATCH_FFN_PAIR, lg_match_debug_set_ffn_pair)
 
 int init_locked(int device) {
     cudaDeviceProp prop;
@@ -125,7 +126,7 @@ int lg_match_ffn_init_device(int device) {
 }
 
 int lg_match_debug_set_ffn_pair(int enabled) {
-    g_pair.store(enabled != 0 ? 1 : 0, std::memory_order_relaxed);
+    g_pair.store(enabled < 0 ? -1 : (enabled != 0 ? 1 : 0), std::memory_order_relaxed);
     return 0;
 }
 
@@ -188,7 +189,10 @@ int lg_match_ffn1_ln_gelu(const void* x_half, long long rows, int ldx, const voi
                                beta, eps);
         return static_cast<int>(e);
     }
-    if (g_pair.load(std::memory_order_relaxed)) {
+    // CTA pairs win once the launch is many waves long (262 144 rows: 154 vs 160 us, 65 536: 47.7 vs 49.8; their double-buffered output staging takes the
+    // TMA-store wait out of every round) and lose a little on short launches (32 768 rows: 29.3 vs 27.3 us)
+    const int pair_mode = g_pair.load(std::memory_order_relaxed);
+    if (pair_mode > 0 || (pair_mode < 0 && tiles >= 3 * g_sms[device])) {
         // CTA pairs (cta_group::2): W1' tiles of 128 rows per CTA, clusters of 2, a pair per 256-row super-tile
         if ((rc = encode_matrix(&tm_w, w_nk_half, kN, kK, kK, kBK, 128, CU_TENSOR_MAP_SWIZZLE_128B)) != 0) return rc;
         const int pairs_max = g_sms[device] / 2, super_tiles = (tiles + 1) / 2;

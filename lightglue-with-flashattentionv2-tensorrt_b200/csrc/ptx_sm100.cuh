@@ -158,6 +158,9 @@ __device__ __forceinline__ void tma_store_4d(const void* tmap, uint32_t src_smem
 }
 __device__ __forceinline__ void bulk_commit_group() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_group_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+// all but the newest kPending bulk groups of this thread have read their sources
+template <int kPending>
+__device__ __forceinline__ void bulk_wait_group_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(kPending) : "memory"); }
 
 // ----------------------------------------------------------------------------- tcgen05
 template <int kCols>
