@@ -179,6 +179,21 @@ proj_rotary_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
             const int a = it & 1;
             const long long row0 = static_cast<long long>(rt) * kBM + quarter * 32;   // first row of this warp's slab
             const uint32_t p_bias = smem + kSmemBias + 4u * static_cast<uint32_t>(t * kBN + head * kColsPerWarp);
+            // The warp's 32 rows x 128 B of the angle table for a 32-column chunk are loaded coalesced (4 rows per instruction) into
+            // registers one chunk AHEAD — chunk 0 before the wait for the accumulator, chunk 1 under the arithmetic of chunk 0 — so
+            // that the global-load latency is never on the epilogue's critical path (it was: ~900 clk twice per item, which made
+            // the epilogue longer than the main loop it is meant to hide under).
+            const bool rot = t < n_rot;
+            float4 pre[8];
+            auto fetch = [&](int c) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const int r_in = (lane >> 3) + 4 * j, seg = lane & 7;
+                    pre[j] = make_float4(1.f, 0.f, 1.f, 0.f);
+                    if (row0 + r_in < rows) pre[j] = __ldg(cs + (row0 + r_in) * 16 + 8 * c + seg);
+                }
+            };
+            if (rot) fetch(0);
             mbar_wait(bar(kBarAccFull + a), (it >> 1) & 1);
             tc_fence_after();
 #pragma unroll
@@ -195,25 +210,16 @@ proj_rotary_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                 // the previous round's TMA store must have read the staging tile before anything is written to it
                 if (elect_one()) bulk_wait_group_read0();
                 __syncwarp();
-                float4 ang[8];   // (cos, sin, cos, sin) of this row's rotary pairs 16 c + 2 q, 16 c + 2 q + 1
-                if (t < n_rot) {
-                    // the warp's 32 rows x 128 B of the table, coalesced (4 rows per load instruction), into the staging tile with the
-                    // 128-byte XOR swizzle; then every lane reads its own row conflict-free
+                if (rot) {
+                    // into the staging tile with the 128-byte XOR swizzle; then every lane reads its own row conflict-free
 #pragma unroll
                     for (int j = 0; j < 8; ++j) {
                         const int r_in = (lane >> 3) + 4 * j, seg = lane & 7;
-                        float4 w4 = make_float4(1.f, 0.f, 1.f, 0.f);
-                        if (row0 + r_in < rows) w4 = __ldg(cs + (row0 + r_in) * 16 + 8 * c + seg);
                         st_shared_v4(stg + static_cast<uint32_t>(r_in) * 128u + (static_cast<uint32_t>(seg ^ (r_in & 7)) << 4),
-                                     __float_as_uint(w4.x), __float_as_uint(w4.y), __float_as_uint(w4.z), __float_as_uint(w4.w));
+                                     __float_as_uint(pre[j].x), __float_as_uint(pre[j].y), __float_as_uint(pre[j].z), __float_as_uint(pre[j].w));
                     }
                     __syncwarp();
-#pragma unroll
-                    for (int q = 0; q < 8; ++q) {
-                        const uint4 u = ld_shared_v4(stg + static_cast<uint32_t>(lane) * 128u + (static_cast<uint32_t>(q ^ (lane & 7)) << 4));
-                        ang[q] = make_float4(__uint_as_float(u.x), __uint_as_float(u.y), __uint_as_float(u.z), __uint_as_float(u.w));
-                    }
-                    __syncwarp();   // the tile is rewritten with the output below
+                    if (c + 1 < kColsPerWarp / 32) fetch(c + 1);
                 }
                 uint32_t o[16];
 #pragma unroll
@@ -221,8 +227,10 @@ proj_rotary_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                     const float4 b = ld_shared_v4f(p_bias + 4u * (32 * c + i));
                     float x0 = __uint_as_float(v[i]) + b.x, x1 = __uint_as_float(v[i + 1]) + b.y;
                     float x2 = __uint_as_float(v[i + 2]) + b.z, x3 = __uint_as_float(v[i + 3]) + b.w;
-                    if (t < n_rot) {
-                        const float4 r = ang[i / 4];
+                    if (rot) {
+                        // (cos, sin, cos, sin) of this row's rotary pairs 16 c + i / 2 and the next
+                        const uint4 u = ld_shared_v4(stg + static_cast<uint32_t>(lane) * 128u + (static_cast<uint32_t>((i / 4) ^ (lane & 7)) << 4));
+                        const float4 r = make_float4(__uint_as_float(u.x), __uint_as_float(u.y), __uint_as_float(u.z), __uint_as_float(u.w));
                         const float y0 = fmaf(x0, r.x, -x1 * r.y), y1 = fmaf(x1, r.x, x0 * r.y);
                         const float y2 = fmaf(x2, r.z, -x3 * r.w), y3 = fmaf(x3, r.z, x2 * r.w);
                         x0 = y0; x1 = y1; x2 = y2; x3 = y3;
@@ -230,6 +238,7 @@ proj_rotary_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                     o[i / 2] = pack_half2(x0, x1);
                     o[i / 2 + 1] = pack_half2(x2, x3);
                 }
+                __syncwarp();   // every lane has read its angles: the tile is rewritten with the output below
 #pragma unroll
                 for (int j = 0; j < 4; ++j)
                     st_shared_v4(stg_row + ((static_cast<uint32_t>(j) ^ swz) << 4), o[4 * j], o[4 * j + 1], o[4 * j + 2], o[4 * j + 3]);
