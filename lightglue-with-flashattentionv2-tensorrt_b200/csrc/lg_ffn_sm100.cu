@@ -60,8 +60,11 @@ int init_locked(int device) {
         e = cudaFuncSetAttribute(small::ffn1_ln_gelu_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  static_cast<int>(small::kSmemBytesS));
     if (e == cudaSuccess)
-        e = cudaFuncSetAttribute(lgproj::proj_rotary_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 static_cast<int>(lgproj::kSmemBytes));
+        e = cudaFuncSetAttribute(lgproj::proj_rotary_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 static_cast<int>(lgproj::Cfg<256>::kSmemBytes));
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(lgproj::proj_rotary_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 static_cast<int>(lgproj::Cfg<128>::kSmemBytes));
     if (e == cudaSuccess) {
         // how many 4-CTA clusters of the few-rows kernel are resident at once (one tile each, no persistence: a launch must fit)
         cudaLaunchConfig_t cfg = {};
@@ -245,7 +248,8 @@ int lg_match_proj_rotary(const void* x_half, long long rows, int ldx, const void
         rows > (1LL << 31) - lgproj::kBM || n_blocks < 1 || n_blocks > lgproj::kMaxBlocks || n_rot_blocks < 0 || n_rot_blocks > n_blocks ||
         (n_rot_blocks > 0 && cs == nullptr))
         return LG_ATTN_EINVAL;
-    if (ldx < lgproj::kK || ldo < n_blocks * lgproj::kBN || (ldx & 7) != 0 || (ldo & 7) != 0) return LG_ATTN_EINVAL;
+    const int n_cols = n_blocks * 256;
+    if (ldx < lgproj::kK || ldo < n_cols || (ldx & 7) != 0 || (ldo & 7) != 0) return LG_ATTN_EINVAL;
     if (((reinterpret_cast<uintptr_t>(x_half) | reinterpret_cast<uintptr_t>(w_nk_half) | reinterpret_cast<uintptr_t>(out_half) |
           reinterpret_cast<uintptr_t>(cs)) & 15u) != 0)
         return LG_ATTN_EINVAL;
@@ -254,23 +258,34 @@ int lg_match_proj_rotary(const void* x_half, long long rows, int ldx, const void
     if (e != cudaSuccess) return static_cast<int>(e);
     int rc = lg_match_ffn_init_device(device);
     if (rc != 0) return rc;
+    // few rows (a single 1024-keypoint pair: 16 row tiles): items of 128 columns while they still fit one wave, so that more SMs
+    // work and an item's four K slabs are all in flight.  (Inside the matcher's graph this is as fast as library GEMM +
+    // lg_match_rotary, 0.483 vs 0.476 ms per pair, not faster: lg_match_proj_prefer_fused keeps the library pair there.)
+    const long long row_tiles = (rows + lgproj::kBM - 1) / lgproj::kBM;
+    const bool narrow = row_tiles * n_blocks * 2 <= g_sms[device];
+    const int bn = narrow ? 128 : 256;
     CUtensorMap tm_x, tm_w, tm_o;
     if ((rc = encode_matrix(&tm_x, x_half, rows, lgproj::kK, ldx, lgproj::kBK, lgproj::kBM, CU_TENSOR_MAP_SWIZZLE_128B)) != 0) return rc;
-    if ((rc = encode_matrix(&tm_w, w_nk_half, static_cast<long long>(n_blocks) * lgproj::kBN, lgproj::kK, lgproj::kK, lgproj::kBK, lgproj::kBN, CU_TENSOR_MAP_SWIZZLE_128B)) != 0) return rc;
-    if ((rc = encode_matrix(&tm_o, out_half, rows, n_blocks * lgproj::kBN, ldo, 32, 32, CU_TENSOR_MAP_SWIZZLE_64B)) != 0) return rc;
-    const long long items = (rows + lgproj::kBM - 1) / lgproj::kBM * n_blocks;
+    if ((rc = encode_matrix(&tm_w, w_nk_half, n_cols, lgproj::kK, lgproj::kK, lgproj::kBK, bn, CU_TENSOR_MAP_SWIZZLE_128B)) != 0) return rc;
+    if ((rc = encode_matrix(&tm_o, out_half, rows, n_cols, ldo, 32, 32, CU_TENSOR_MAP_SWIZZLE_64B)) != 0) return rc;
+    const long long items = row_tiles * (n_cols / bn);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(static_cast<unsigned>(items < g_sms[device] ? items : g_sms[device]));
     cfg.blockDim = dim3(lgproj::kThreads);
-    cfg.dynamicSmemBytes = lgproj::kSmemBytes;
+    cfg.dynamicSmemBytes = narrow ? lgproj::Cfg<128>::kSmemBytes : lgproj::Cfg<256>::kSmemBytes;
     cfg.stream = static_cast<cudaStream_t>(stream);
     cudaLaunchAttribute attrs[1];
     attrs[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attrs[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attrs;
     cfg.numAttrs = g_pdl.load(std::memory_order_relaxed) ? 1u : 0u;
-    e = cudaLaunchKernelEx(&cfg, lgproj::proj_rotary_kernel, tm_x, tm_w, tm_o, static_cast<const __half*>(bias_half),
-                           reinterpret_cast<const float4*>(cs), rows, n_blocks, n_rot_blocks, static_cast<int>(items));
+    const int early_trigger = 1;   // the next kernel (attention, a programmatic dependent launch) may set up under this one
+    if (narrow)
+        e = cudaLaunchKernelEx(&cfg, lgproj::proj_rotary_kernel<128>, tm_x, tm_w, tm_o, static_cast<const __half*>(bias_half),
+                               reinterpret_cast<const float4*>(cs), rows, n_blocks, n_rot_blocks, static_cast<int>(items), early_trigger);
+    else
+        e = cudaLaunchKernelEx(&cfg, lgproj::proj_rotary_kernel<256>, tm_x, tm_w, tm_o, static_cast<const __half*>(bias_half),
+                               reinterpret_cast<const float4*>(cs), rows, n_blocks, n_rot_blocks, static_cast<int>(items), early_trigger);
     return static_cast<int>(e);
 }
 

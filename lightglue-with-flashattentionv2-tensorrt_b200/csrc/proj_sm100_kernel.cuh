@@ -37,38 +37,53 @@ namespace lgproj {
 using namespace lgattn::ptx;
 
 constexpr int kBM = 128;          // rows per item
-constexpr int kBN = 256;          // columns per item (= 4 heads)
 constexpr int kK = 256;           // embedding width
 constexpr int kBK = 64;
 constexpr int kKSteps = kK / kBK;
-constexpr int kStages = 3;
 constexpr int kMaxBlocks = 3;
 constexpr int kEpiWarps = 16;
 constexpr int kServiceWarps = 4;
 constexpr int kThreads = 32 * (kEpiWarps + kServiceWarps);
-constexpr int kColsPerWarp = kBN / (kEpiWarps / 4);   // 64 = one head
-
 constexpr uint32_t kABytes = kBM * kBK * 2;            // 16 KiB
-constexpr uint32_t kBBytes = kBN * kBK * 2;            // 32 KiB
-constexpr uint32_t kStageBytes = kABytes + kBBytes;
-constexpr uint32_t kSmemRing = 0;
-constexpr uint32_t kStageTile = 32 * 128;                                     // per warp: 32 rows x 16 (cos, sin) pairs of a chunk, then 32 rows x 32 halves of output
-constexpr uint32_t kSmemStage = kSmemRing + kStages * kStageBytes;            // 16 x 4 KiB staging
-constexpr uint32_t kSmemBias = kSmemStage + kEpiWarps * kStageTile;           // float[768]
-constexpr uint32_t kSmemBar = kSmemBias + kMaxBlocks * kBN * 4;
-enum : uint32_t { kBarFull = 0, kBarEmpty = kStages, kBarAccFull = 2 * kStages, kBarAccEmpty = 2 * kStages + 2, kNumBars = 2 * kStages + 4 };
-constexpr uint32_t kSmemTmemSlot = kSmemBar + 8 * kNumBars;
-constexpr uint32_t kSmemBytes = kSmemTmemSlot + 16 + 1024;
-static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
+constexpr uint32_t kStageTile = 32 * 128;              // per warp: 32 rows x 16 (cos, sin) pairs of a chunk, then 32 rows x 32 halves of output
+
+// kBN = columns per work item: 256 (4 heads; the throughput shape) or 128 (few rows — a single pair is 16 row tiles: 96 items of
+// 128 columns cover the GPU where 48 of 256 do not, and all four K slabs of an item are in flight at once).
+template <int kBN>
+struct Cfg {
+    static_assert(kBN == 256 || kBN == 128, "columns per item");
+    static constexpr int kStages = kBN == 256 ? 3 : 4;
+    static constexpr int kColsPerWarp = kBN / (kEpiWarps / 4);   // 64 = one head | 32 = half a head
+    static constexpr uint32_t kBBytes = kBN * kBK * 2;            // 32 | 16 KiB
+    static constexpr uint32_t kStageBytes = kABytes + kBBytes;
+    static constexpr uint32_t kSmemRing = 0;
+    static constexpr uint32_t kSmemStage = kSmemRing + kStages * kStageBytes;            // 16 x 4 KiB staging
+    static constexpr uint32_t kSmemBias = kSmemStage + kEpiWarps * kStageTile;           // float[768]
+    static constexpr uint32_t kSmemBar = kSmemBias + kMaxBlocks * 256 * 4;
+    static constexpr uint32_t kBarFull = 0, kBarEmpty = kStages, kBarAccFull = 2 * kStages, kBarAccEmpty = 2 * kStages + 2,
+                              kNumBars = 2 * kStages + 4;
+    static constexpr uint32_t kSmemTmemSlot = kSmemBar + 8 * kNumBars;
+    static constexpr uint32_t kSmemBytes = kSmemTmemSlot + 16 + 1024;
+    static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
+    static constexpr int kTmemCols = 2 * kBN;   // two accumulators
+};
 
 constexpr int kRegsLaunch = (65536 / kThreads) / 8 * 8;   // 96
 constexpr int kRegsService = 32;
 constexpr int kRegsEpi = ((kThreads * kRegsLaunch - kServiceWarps * 32 * kRegsService) / (kEpiWarps * 32)) / 8 * 8;   // 112
 
+template <int kBN>
 __global__ void __launch_bounds__(kThreads, 1)
 proj_rotary_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w,
                    const __grid_constant__ CUtensorMap tm_o, const __half* __restrict__ bias, const float4* __restrict__ cs,
-                   long long rows, int n_blocks, int n_rot, int items) {
+                   long long rows, int n_blocks, int n_rot, int items, int early_trigger) {
+    using C = Cfg<kBN>;
+    constexpr int kStages = C::kStages, kColsPerWarp = C::kColsPerWarp;
+    constexpr uint32_t kBBytes = C::kBBytes, kStageBytes = C::kStageBytes, kSmemRing = C::kSmemRing, kSmemStage = C::kSmemStage,
+                       kSmemBias = C::kSmemBias, kSmemBar = C::kSmemBar, kBarFull = C::kBarFull, kBarEmpty = C::kBarEmpty,
+                       kBarAccFull = C::kBarAccFull, kBarAccEmpty = C::kBarAccEmpty, kSmemTmemSlot = C::kSmemTmemSlot;
+    (void)kBBytes;
+    const int per_row_tile = n_blocks * 256 / kBN;   // items per 128-row tile
     extern __shared__ uint8_t smem_raw[];
     uint32_t smem = (smem_u32(smem_raw) + 1023u) & ~1023u;
     asm volatile("mov.u32 %0, %0;" : "+r"(smem));   // pin (see attn_sm100_kernel_mq.cuh)
@@ -96,10 +111,10 @@ proj_rotary_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
         fence_mbar_init();
     }
     if (warp == kWarpMMA) {
-        tmem_alloc<512>(smem + kSmemTmemSlot);
+        tmem_alloc<C::kTmemCols>(smem + kSmemTmemSlot);
         tmem_relinquish();
     }
-    for (int i = threadIdx.x; i < n_blocks * kBN; i += kThreads) st_shared_f32(smem + kSmemBias + 4u * i, __half2float(bias[i]));
+    for (int i = threadIdx.x; i < n_blocks * 256; i += kThreads) st_shared_f32(smem + kSmemBias + 4u * i, __half2float(bias[i]));
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -108,7 +123,7 @@ proj_rotary_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
 
     // weights and own state only above; the activations belong to the previous kernel (programmatic dependent launch)
     pdl_wait_prior_grids();
-    if (threadIdx.x == 0) pdl_launch_dependents();
+    if (threadIdx.x == 0 && early_trigger) pdl_launch_dependents();
 
     const int first = blockIdx.x, stride = gridDim.x;
 
@@ -122,7 +137,7 @@ proj_rotary_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
             // ===================================================================== operand producer
             int g = 0;
             for (int item = first; item < items; item += stride) {
-                const int rt = item / n_blocks, t = item - rt * n_blocks;
+                const int rt = item / per_row_tile, t = item - rt * per_row_tile;
 #pragma unroll 1
                 for (int k = 0; k < kKSteps; ++k, ++g) {
                     const int s = g % kStages;
@@ -175,7 +190,7 @@ proj_rotary_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
 
         int it = 0;
         for (int item = first; item < items; item += stride, ++it) {
-            const int rt = item / n_blocks, t = item - rt * n_blocks;
+            const int rt = item / per_row_tile, t = item - rt * per_row_tile;
             const int a = it & 1;
             const long long row0 = static_cast<long long>(rt) * kBM + quarter * 32;   // first row of this warp's slab
             const uint32_t p_bias = smem + kSmemBias + 4u * static_cast<uint32_t>(t * kBN + head * kColsPerWarp);
@@ -183,14 +198,15 @@ proj_rotary_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
             // registers one chunk AHEAD — chunk 0 before the wait for the accumulator, chunk 1 under the arithmetic of chunk 0 — so
             // that the global-load latency is never on the epilogue's critical path (it was: ~900 clk twice per item, which made
             // the epilogue longer than the main loop it is meant to hide under).
-            const bool rot = t < n_rot;
+            const int col_base = t * kBN + head * kColsPerWarp;   // first column of this warp's slice in the output row
+            const bool rot = col_base < n_rot * 256;
             float4 pre[8];
             auto fetch = [&](int c) {
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
                     const int r_in = (lane >> 3) + 4 * j, seg = lane & 7;
                     pre[j] = make_float4(1.f, 0.f, 1.f, 0.f);
-                    if (row0 + r_in < rows) pre[j] = __ldg(cs + (row0 + r_in) * 16 + 8 * c + seg);
+                    if (row0 + r_in < rows) pre[j] = __ldg(cs + (row0 + r_in) * 16 + 8 * (((col_base >> 5) + c) & 1) + seg);   // chunk = half of a head
                 }
             };
             if (rot) fetch(0);
@@ -228,7 +244,7 @@ proj_rotary_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                     float x0 = __uint_as_float(v[i]) + b.x, x1 = __uint_as_float(v[i + 1]) + b.y;
                     float x2 = __uint_as_float(v[i + 2]) + b.z, x3 = __uint_as_float(v[i + 3]) + b.w;
                     if (rot) {
-                        // (cos, sin, cos, sin) of this row's rotary pairs 16 c + i / 2 and the next
+                        // (cos, sin, cos, sin) of this row's rotary pairs (16 per chunk) i / 2 and the next
                         const uint4 u = ld_shared_v4(stg + static_cast<uint32_t>(lane) * 128u + (static_cast<uint32_t>((i / 4) ^ (lane & 7)) << 4));
                         const float4 r = make_float4(__uint_as_float(u.x), __uint_as_float(u.y), __uint_as_float(u.z), __uint_as_float(u.w));
                         const float y0 = fmaf(x0, r.x, -x1 * r.y), y1 = fmaf(x1, r.x, x0 * r.y);
@@ -245,7 +261,7 @@ proj_rotary_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                 fence_proxy_async_smem();
                 __syncwarp();
                 if (elect_one()) {
-                    tma_store_4d(&tm_o, stg, t * kBN + head * kColsPerWarp + 32 * c, rt * kBM + quarter * 32, 0, 0);
+                    tma_store_4d(&tm_o, stg, col_base + 32 * c, rt * kBM + quarter * 32, 0, 0);
                     bulk_commit_group();
                 }
                 __syncwarp();
@@ -259,7 +275,7 @@ proj_rotary_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
     __syncthreads();
     if (warp == kWarpMMA) {
         tc_fence_after();
-        tmem_dealloc<512>(tmem_base);
+        tmem_dealloc<C::kTmemCols>(tmem_base);
     }
 }
 
