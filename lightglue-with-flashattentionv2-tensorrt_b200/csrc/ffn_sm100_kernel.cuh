@@ -21,10 +21,11 @@
 //   * output: each warp stages 32 rows x 32 columns (2 KiB, SWIZZLE_64B pattern: conflict-free 16-byte stores) and one elected
 //     lane issues a TMA store — rows past `rows` are clipped by the tensor map.
 //
-// Roofline: 2 * 128 * 512 * 512 FLOP per tile = 8 192 clk of tensor pipe; operand traffic 640 KiB per tile (W1' is re-read by
-// every tile: 512 KiB) = 80 B / clk / SM at that rate, above the ~43 B / clk / SM the L2 delivers to 148 SMs at once — so the
-// main loop is L2-bound at ~15 k clk per tile, and the epilogue (~19 instructions per element, 9.7 k issue slots per
-// sub-partition per tile) hides under it.
+// Roofline and what bounds it (measured): 2 * 128 * 512 * 512 FLOP per tile = 8 192 clk of tensor pipe, 640 KiB
+// of operands per tile out of L2 (W1' is re-read by every tile).  Neither is the limit: the phase trace (-DLG_FFN_TRACE) shows the
+// epilogue warps busy back to back — drain ~3 000 clk, apply / store ~12 000 per tile — with the next tile's MMAs issued within
+// 8 400 - 11 700 clk of the hand-back: the kernel is bound by the instruction issue of its LayerNorm + GELU arithmetic (~20
+// instructions per element at IPC 0.7), the GEMM is what hides.  ncu: tensor pipe 47 - 51 % active, issue slots 66 - 69 %.
 //
 // No CUTLASS; encodings in ptx_sm100.cuh.
 #pragma once
