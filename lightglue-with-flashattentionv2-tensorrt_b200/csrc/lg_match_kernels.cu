@@ -110,7 +110,7 @@ __global__ void __launch_bounds__(256) layernorm_gelu_kernel(__half* __restrict_
     LG_GLUE_PDL_ENTRY();
     const int lane = threadIdx.x & 31;
     const long long warp0 = blockIdx.x * 8LL + (threadIdx.x >> 5);
-    float g[16], b[16];
+    float g[16], b[16];   // gamma / 2, beta / 2: the affine step yields y / 2, which gelu_erf_of_half takes (two multiplies per element fewer)
 #pragma unroll
     for (int half_i = 0; half_i < 2; ++half_i) {
         const float4* gp = reinterpret_cast<const float4*>(gamma + half_i * 256 + lane * 8);
@@ -120,6 +120,11 @@ __global__ void __launch_bounds__(256) layernorm_gelu_kernel(__half* __restrict_
         g[8 * half_i + 4] = g1.x; g[8 * half_i + 5] = g1.y; g[8 * half_i + 6] = g1.z; g[8 * half_i + 7] = g1.w;
         b[8 * half_i + 0] = b0.x; b[8 * half_i + 1] = b0.y; b[8 * half_i + 2] = b0.z; b[8 * half_i + 3] = b0.w;
         b[8 * half_i + 4] = b1.x; b[8 * half_i + 5] = b1.y; b[8 * half_i + 6] = b1.z; b[8 * half_i + 7] = b1.w;
+    }
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        g[i] *= 0.5f;
+        b[i] *= 0.5f;
     }
     // Two rows per warp iteration: both rows' loads are issued before any arithmetic.  Measured (B200, 131072 rows): 4.2 TB/s of
     // read+write, the same as one row per iteration, as a register-double-buffered prefetch of the next two rows (4.0) and as round
@@ -168,8 +173,8 @@ __global__ void __launch_bounds__(256) layernorm_gelu_kernel(__half* __restrict_
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
                     const int k = 8 * i + 2 * e;
-                    const float y0 = gelu_erf(fmaf(fmaf(x[k], rstd, nmr), g[k], b[k]));
-                    const float y1 = gelu_erf(fmaf(fmaf(x[k + 1], rstd, nmr), g[k + 1], b[k + 1]));
+                    const float y0 = gelu_erf_of_half(fmaf(fmaf(x[k], rstd, nmr), g[k], b[k]));
+                    const float y1 = gelu_erf_of_half(fmaf(fmaf(x[k + 1], rstd, nmr), g[k + 1], b[k + 1]));
                     hp[e] = __floats2half2_rn(y0, y1);
                 }
             }
