@@ -1,4 +1,4 @@
-"""Mnemonic histogram per attention kernel of the built library (what proves a Blackwell-native kernel, B200_PROFILING.md):
+"""Mnemonic histogram per tcgen05 kernel (attention, fused ffn-up, projection) of the built library (what proves a Blackwell-native kernel, B200_PROFILING.md):
 
     python tools/sass_histogram.py > profiles/r2_sass_histogram.txt
 """
@@ -10,7 +10,7 @@ from pathlib import Path
 
 ROOT = Path(__file__).resolve().parent.parent
 LIB = ROOT / "lightglue-with-flashattentionv2-tensorrt_b200" / "csrc" / "build" / "liblightglue_attention_plugin.so"
-WANT = ["UTCHMMA", "UTCBAR", "UTMALDG", "LDTM", "STTM", "MUFU.EX2", "MUFU.RCP", "FFMA2", "FADD2", "FFMA", "FMNMX3", "F2FP", "ELECT", "BRA.U.ANY",
+WANT = ["UTCHMMA", "UTCBAR", "UTMALDG", "UTMASTG", "LDTM", "STTM", "MUFU.EX2", "MUFU.RCP", "FFMA2", "FADD2", "FFMA", "FMNMX3", "F2FP", "ELECT", "BRA.U.ANY",
         "SYNCS", "UCGABAR", "HMMA", "HGMMA", "LDL", "STL"]
 
 sass = subprocess.run(["cuobjdump", "-sass", str(LIB)], capture_output=True, text=True).stdout
@@ -35,7 +35,7 @@ print("# LDTM / STTM = tcgen05.ld / st, UTCBAR = tcgen05.commit, BRA.U.ANY = per
 print("# issue through elect.sync), HMMA / HGMMA = legacy mma.sync / wgmma (must be 0), LDL / STL = spills")
 print("kernel".ljust(78) + " ".join(w.rjust(9) for w in WANT) + "   total")
 for name, c in kernels.items():
-    if "lg_attn_hd64_fwd" not in name and "--all" not in sys.argv:
+    if not any(k in name for k in ("lg_attn_hd64_fwd", "ffn1_ln_gelu", "proj_rotary_kernel")) and "--all" not in sys.argv:
         continue
     short = re.sub(r"\(.*", "", name).replace("lgattn::", "")
     print(short[:76].ljust(78) + " ".join(str(c[w]).rjust(9) for w in WANT) + f"   {c['_total']}")
