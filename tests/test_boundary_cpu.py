@@ -102,6 +102,24 @@ def test_library_is_sm100a_native(pkg):
     for mnemonic in ("UTCHMMA", "UTMALDG", "LDTM", "STTM"):
         assert mnemonic in sass, mnemonic
     assert "HMMA." not in sass.replace("UTCHMMA", "")  # no legacy mma.sync path
+    # per kernel: every hand-written GEMM-shaped kernel of the library (attention, fused ffn-up, projection) issues tcgen05.mma fed by
+    # TMA, reads its accumulator with tcgen05.ld, and carries no local-memory spills in the one-CTA / pair ffn and attention kernels
+    per_kernel, cur = {}, None
+    for line in sass.splitlines():
+        m = re.search(r"Function : (\S+)", line)
+        if m:
+            cur = m.group(1)
+            per_kernel[cur] = set()
+        elif cur:
+            m = re.match(r"\s+/\*[0-9a-f]{4,5}\*/\s+(?:@!?U?P\d+\s+)?([A-Z0-9_]+)", line)
+            if m:
+                per_kernel[cur].add(m.group(1))
+    tc = {k: v for k, v in per_kernel.items() if any(n in k for n in ("lg_attn_hd64_fwd", "ffn1_ln_gelu", "proj_rotary_kernel"))}
+    assert len(tc) >= 16, sorted(tc)   # 11 attention instantiations + 3 ffn + 2 projection
+    for name, ops in tc.items():
+        assert {"UTCHMMA", "UTMALDG", "LDTM", "UTCBAR"} <= ops, (name, sorted(ops))
+        assert "HMMA" not in ops and "HGMMA" not in ops, name
+    assert any("UTMASTG" in ops for name, ops in tc.items() if "ffn1_ln_gelu" in name)   # TMA stores out of the staging tiles
 
 
 def test_cmake_build_drops_in(pkg, tmp_path):
